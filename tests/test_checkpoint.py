@@ -1,0 +1,132 @@
+"""Checkpoint / Recompute."""
+from functools import partial
+
+import pytest
+import torch
+from torch import nn
+
+from pipe_b200 import Pipe
+from pipe_b200.autograd.checkpoint import (Checkpointing, checkpoint, is_checkpointing,
+                                           is_recomputing)
+from pipe_b200.autograd.dependency import fork, join
+from pipe_b200.microbatch import Batch
+
+
+def test_serial_checkpoints_order():
+    """Two independent checkpointed calls ordered by fork/join replay in the
+    order a:recompute, a:backward happen after b's (b joined after a)."""
+    timeline = []
+
+    class Log(torch.autograd.Function):
+        @staticmethod
+        def forward(ctx, name, x):
+            ctx.name = name
+            timeline.append(f"{name}:forward")
+            return x.detach()
+
+        @staticmethod
+        def backward(ctx, g):
+            timeline.append(f"{ctx.name}:backward")
+            return None, g
+
+    a = torch.rand(1, requires_grad=True)
+    b = torch.rand(1, requires_grad=True)
+    a = checkpoint(partial(Log.apply, "a"), a)
+    a, phony = fork(a)
+    b = join(b, phony)
+    b = checkpoint(partial(Log.apply, "b"), b)
+    (a + b).backward()
+    assert timeline == ["a:forward", "b:forward", "b:forward", "b:backward", "a:forward", "a:backward"]
+
+
+def test_gradients_match_plain():
+    lin = nn.Linear(4, 4)
+    x = torch.rand(3, 4, requires_grad=True)
+    y = checkpoint(lambda t: lin(t).relu(), x)
+    y.sum().backward()
+    gx, gw = x.grad.clone(), lin.weight.grad.clone()
+    x.grad = None
+    lin.zero_grad()
+    lin(x).relu().sum().backward()
+    assert torch.allclose(gx, x.grad) and torch.allclose(gw, lin.weight.grad)
+
+
+def test_not_requires_grad_input_still_trains_params():
+    lin = nn.Linear(2, 2)
+    x = torch.rand(1, 2)                       # no grad on the input (stage 0 fed by tokens)
+    chk = Checkpointing(lin, Batch(x))
+    out = chk.checkpoint()
+    assert out.tensor.requires_grad            # phony keeps the node in the graph
+    chk.recompute(out)
+    out.tensor.sum().backward()
+    assert lin.weight.grad is not None
+
+
+def test_dropout_is_replayed_bit_identically():
+    torch.manual_seed(3)
+    drop = nn.Dropout(p=0.5)
+    x = torch.ones(1000, requires_grad=True)
+    y = checkpoint(drop, x)
+    y.sum().backward()
+    # grad of dropout is mask/(1-p): it must equal the forward mask
+    assert torch.equal(x.grad, y.detach())
+
+
+def test_rng_outside_is_not_disturbed_by_recompute():
+    drop = nn.Dropout(p=0.5)
+    x = torch.ones(100, requires_grad=True)
+    y = checkpoint(drop, x)
+    torch.manual_seed(7)
+    expect = torch.rand(3)
+    torch.manual_seed(7)
+    y.sum().backward()                         # recompute runs inside a forked RNG scope
+    assert torch.equal(torch.rand(3), expect)
+
+
+def test_flags():
+    seen = []
+
+    def f(x):
+        seen.append((is_checkpointing(), is_recomputing()))
+        return x * 2
+
+    x = torch.rand(1, requires_grad=True)
+    checkpoint(f, x).backward()
+    assert seen == [(True, False), (False, True)]
+    assert not is_checkpointing() and not is_recomputing()
+
+
+def test_tuple_output_with_non_float_detached():
+    def f(x):
+        return x * 2, torch.arange(3)
+
+    x = torch.rand(3, requires_grad=True)
+    chk = Checkpointing(f, Batch(x))
+    out = chk.checkpoint()
+    assert out[0].requires_grad and not out[1].requires_grad
+    chk.recompute(out)
+    out[0].sum().backward()
+    assert torch.equal(x.grad, torch.full((3,), 2.0))
+
+
+def test_inplace_after_checkpoint_detected():
+    x = torch.rand(2, requires_grad=True)
+    h = x * 1.0
+    y = checkpoint(lambda t: t * 3, h)
+    h.add_(1)                                  # invalidates what Recompute saved
+    with pytest.raises(RuntimeError, match="modified by an inplace operation"):
+        y.sum().backward()
+
+
+@pytest.mark.parametrize("mode", ["always", "except_last", "never"])
+def test_pipe_modes_same_gradients(mode):
+    torch.manual_seed(0)
+    seq = nn.Sequential(nn.Linear(4, 8), nn.Tanh(), nn.Linear(8, 2))
+    x = torch.rand(8, 4)
+    seq(x).sum().backward()
+    want = [p.grad.clone() for p in seq.parameters()]
+    seq.zero_grad()
+    pipe = Pipe(seq, chunks=4, checkpoint=mode)
+    pipe(x).local_value().sum().backward()
+    for p, w in zip(pipe.parameters(), want):
+        assert torch.allclose(p.grad, w, atol=1e-6)
