@@ -1,0 +1,378 @@
+// tcgen05 / TMEM / TMA GEMM for sm_100a:  D[M,N] = A[M,K] * B[N,K]^T  (+ fused epilogue)
+//
+// Both operands are bf16, K-major (row-major with K contiguous) — the layout of
+// activations [tokens, features] and of nn.Linear weights [out, in] — so a
+// Linear forward, its dgrad (against a pre-transposed weight copy) and its
+// wgrad (against transposed activations) are all this one kernel.
+//
+// Shape of the problem in this framework: micro-batches carry
+// 25-128 tokens against 4096-8192-wide weights, so the GEMMs are weight-streaming
+// (HBM) bound.  The kernel is therefore built "swap-AB" first: the *weight* rows
+// ride on the 128-wide UMMA M axis, the tokens on the UMMA N axis (any multiple
+// of 16 up to 256, so 75 tokens cost an N=80 instruction instead of a padded
+// 128-row tile), K is split across CTAs (split-K) until the grid covers the 148
+// SMs, and a deep TMA ring (up to 8 x 16-48 KB stages) keeps enough bytes in
+// flight per SM to saturate HBM3e.  The epilogue can store the tile transposed,
+// which turns D^T[features, tokens] back into row-major [tokens, features].
+//
+// Pipeline inside a CTA (192 threads, one output tile, one K-split):
+//   warp 0      TMA producer: cp.async.bulk.tensor -> 128B-swizzled smem ring, mbarrier complete_tx
+//   warp 1      allocates TMEM; one elected lane issues tcgen05.mma (M=128, N=block_n, K=16) x 4 per stage,
+//               tcgen05.commit releases the smem stage / signals the accumulator
+//   warps 2-5   epilogue: tcgen05.ld accumulator -> registers -> (split-K fix-up) -> bias / ReLU /
+//               Philox dropout / mask-multiply / residual add / accumulate -> global
+//
+// Split-K fix-up: every split writes its fp32 partial tile to a scratch workspace,
+// bumps a per-tile counter, and the CTA that arrives last adds the other splits'
+// partials to its own accumulator (still in TMEM) and runs the epilogue.  The
+// counter is reset by that CTA, so the workspace is reusable by the next launch
+// on the same stream without a memset.
+//
+// No counterpart in the reference: its GEMMs are cuBLAS calls behind nn.Linear /
+// nn.MultiheadAttention (main.py:45,148); SURVEY.md K2/K4/K6/K7, W5.
+#include "common.cuh"
+#include "pipe_b200.h"
+
+namespace pb2 {
+
+constexpr int kBlockM = 128;
+constexpr int kBlockK = 64;          // 64 bf16 = one 128-byte swizzle row
+constexpr int kUmmaK = 16;
+constexpr int kMaxStages = 8;
+constexpr int kThreads = 192;
+
+struct GemmArgs {
+    int M, N, K;
+    int block_n;
+    int k_blocks_total;
+    int k_blocks_per_split;
+    int splits;
+    int stages;
+    int tmem_cols;
+    // epilogue
+    void* out;
+    long long ld_out;
+    int out_f32;
+    int transpose_out;
+    const float* bias;
+    int bias_along_m;
+    int relu;
+    float drop_p;
+    unsigned long long seed, stream;
+    const __nv_bfloat16* mask_src;   // out *= (mask_src[idx] > 0) * mask_scale
+    float mask_scale;
+    const __nv_bfloat16* addend;     // out += addend[idx]
+    int accumulate;                  // fp32 out += (else overwrite)
+    float alpha;                     // scales the accumulator before anything else
+    float* sumsq;                    // optional: += sum of squares of what was written
+    float* partials;
+    unsigned int* counters;
+};
+
+struct __align__(8) SmemCtl {
+    uint64_t full[kMaxStages];
+    uint64_t empty[kMaxStages];
+    uint64_t tmem_full;
+    uint32_t tmem_base;
+    uint32_t is_last;
+};
+
+__device__ __forceinline__ float bf16_bits_to_float(unsigned short b) {
+    return __uint_as_float(static_cast<uint32_t>(b) << 16);
+}
+
+// Finish one element: everything after the raw accumulator.  (row, col) are
+// coordinates in the *output tensor*; idx = row * ld + col.
+__device__ __forceinline__ float epilogue_elem(const GemmArgs& g, const Philox& ph, uint32_t thr, float inv_keep,
+                                               float v, int m_glob, int n_glob, long long idx) {
+    v *= g.alpha;
+    if (g.bias) v += g.bias[g.bias_along_m ? m_glob : n_glob];
+    if (g.relu) v = fmaxf(v, 0.f);
+    if (g.drop_p > 0.f) v = dropout_keep(ph, g.stream, static_cast<uint64_t>(idx), thr) ? v * inv_keep : 0.f;
+    if (g.mask_src) v = (__bfloat162float(g.mask_src[idx]) > 0.f) ? v * g.mask_scale : 0.f;
+    if (g.addend) v += __bfloat162float(g.addend[idx]);
+    return v;
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                    const GemmArgs g) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    // carve: [stages][A 16 KB][B block_n*128 B] then control block
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    const uint32_t a_bytes = kBlockM * kBlockK * 2;
+    const uint32_t b_bytes = g.block_n * kBlockK * 2;
+    const uint32_t stage_bytes = a_bytes + b_bytes;
+    SmemCtl* ctl = reinterpret_cast<SmemCtl*>(smem + static_cast<size_t>(g.stages) * stage_bytes);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int m0 = blockIdx.x * kBlockM;
+    const int n0 = blockIdx.y * g.block_n;
+    const int split = blockIdx.z;
+    const int kb_begin = split * g.k_blocks_per_split;
+    int kb_count = g.k_blocks_total - kb_begin;
+    if (kb_count > g.k_blocks_per_split) kb_count = g.k_blocks_per_split;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmap_a);
+        tma_prefetch_desc(&tmap_b);
+        for (int s = 0; s < g.stages; ++s) {
+            mbar_init(&ctl->full[s], 1);
+            mbar_init(&ctl->empty[s], 1);
+        }
+        mbar_init(&ctl->tmem_full, 1);
+        fence_mbar_init();
+    }
+    if (warp == 1) {
+        tmem_alloc(&ctl->tmem_base, g.tmem_cols);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = ctl->tmem_base;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (elect_one()) {
+            for (int it = 0; it < kb_count; ++it) {
+                const int s = it % g.stages;
+                const uint32_t round = it / g.stages;
+                mbar_wait(&ctl->empty[s], (round & 1) ^ 1);
+                uint8_t* sa = smem + static_cast<size_t>(s) * stage_bytes;
+                uint8_t* sb = sa + a_bytes;
+                mbar_expect_tx(&ctl->full[s], stage_bytes);
+                const int k_elem = (kb_begin + it) * kBlockK;
+                // weights (A) are streamed once: evict-first; tokens (B) are re-read by every M tile: evict-last
+                tma_load_2d(sa, &tmap_a, &ctl->full[s], k_elem, m0, kEvictFirst);
+                tma_load_2d(sb, &tmap_b, &ctl->full[s], k_elem, n0, kEvictLast);
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        const uint32_t idesc = umma_idesc_bf16(kBlockM, g.block_n);
+        for (int it = 0; it < kb_count; ++it) {
+            const int s = it % g.stages;
+            const uint32_t round = it / g.stages;
+            mbar_wait(&ctl->full[s], round & 1);
+            tc_fence_after();
+            if (elect_one()) {
+                const uint32_t sa = smem_u32(smem + static_cast<size_t>(s) * stage_bytes);
+                const uint64_t da = umma_desc_k_sw128(sa);
+                const uint64_t db = umma_desc_k_sw128(sa + a_bytes);
+#pragma unroll
+                for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+                    // advance 16 elements = 32 bytes along K inside the swizzle row: +2 in 16-byte units
+                    umma_bf16(tmem_base, da + 2 * k, db + 2 * k, idesc, (it > 0 || k > 0) ? 1u : 0u);
+                }
+                umma_commit(&ctl->empty[s]);                      // frees the smem stage when the MMAs retire
+                if (it == kb_count - 1) umma_commit(&ctl->tmem_full);
+            }
+            __syncwarp();
+        }
+    } else {
+        // ===================== epilogue (warps 2..5) =====================
+        const int quarter = warp & 3;                 // TMEM lane quarter this warp may read
+        const int m_local = quarter * 32 + lane;
+        const int m_glob = m0 + m_local;
+        const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
+        const int ep_tid = threadIdx.x - 64;          // 0..127
+
+        mbar_wait(&ctl->tmem_full, 0);
+        tc_fence_after();
+
+        const int tile = blockIdx.y * gridDim.x + blockIdx.x;
+        bool last = true;
+        if (g.splits > 1) {
+            float* mine = g.partials + (static_cast<size_t>(tile) * g.splits + split) * g.block_n * kBlockM;
+            for (int c = 0; c < g.block_n; c += 16) {
+                uint32_t r[16];
+                tmem_ld_32x16(t_lane + c, r);
+                tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 16; ++j) mine[static_cast<size_t>(c + j) * kBlockM + m_local] = __uint_as_float(r[j]);
+            }
+            __threadfence();
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            if (ep_tid == 0) {
+                unsigned int prev = atomicAdd(&g.counters[tile], 1u);
+                ctl->is_last = (prev == static_cast<unsigned int>(g.splits - 1)) ? 1u : 0u;
+                if (prev == static_cast<unsigned int>(g.splits - 1)) g.counters[tile] = 0u;   // re-arm for the next launch
+            }
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            last = ctl->is_last != 0;
+            if (last) __threadfence();
+        }
+
+        if (last) {
+            const Philox ph(g.seed);
+            const uint32_t thr = static_cast<uint32_t>(fminf(g.drop_p, 0.999999f) * 4294967296.0f);
+            const float inv_keep = g.drop_p > 0.f ? 1.f / (1.f - g.drop_p) : 1.f;
+            float ss = 0.f;
+            const float* others = g.partials + static_cast<size_t>(tile) * g.splits * g.block_n * kBlockM;
+            for (int c = 0; c < g.block_n; c += 16) {
+                uint32_t r[16];
+                tmem_ld_32x16(t_lane + c, r);
+                tmem_ld_wait();
+                float v[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
+                for (int s = 0; s < g.splits; ++s) {
+                    if (s == split) continue;
+                    const float* p = others + static_cast<size_t>(s) * g.block_n * kBlockM;
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) v[j] += __ldcg(p + static_cast<size_t>(c + j) * kBlockM + m_local);
+                }
+                if (m_glob >= g.M) continue;
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    const int n_glob = n0 + c + j;
+                    if (n_glob >= g.N) break;
+                    const long long idx = g.transpose_out ? static_cast<long long>(n_glob) * g.ld_out + m_glob
+                                                          : static_cast<long long>(m_glob) * g.ld_out + n_glob;
+                    float o = epilogue_elem(g, ph, thr, inv_keep, v[j], m_glob, n_glob, idx);
+                    if (g.out_f32) {
+                        float* dst = static_cast<float*>(g.out) + idx;
+                        if (g.accumulate) o += *dst;
+                        *dst = o;
+                    } else {
+                        static_cast<__nv_bfloat16*>(g.out)[idx] = __float2bfloat16(o);
+                    }
+                    ss += o * o;
+                }
+            }
+            if (g.sumsq) {
+                ss = warp_sum(ss);
+                if (lane == 0) atomicAdd(g.sumsq, ss);
+            }
+        }
+        tc_fence_before();
+    }
+
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, g.tmem_cols);
+    }
+}
+
+static int next_pow2_cols(int n) {
+    int c = 32;
+    while (c < n) c <<= 1;
+    return c;
+}
+
+}  // namespace pb2
+
+using namespace pb2;
+
+extern "C" size_t pb2_gemm_workspace_bytes(void) {
+    // partials: up to 148*4 CTAs' worth of 128 x 256 fp32 tiles is never needed at once; the launcher
+    // bounds splits so that tiles*splits*block_n*128*4 <= this.  Counters live at the end.
+    return PB2_GEMM_WORKSPACE_BYTES;
+}
+
+static int gemm_launch(const pb2_gemm_desc* d, float* partials, unsigned int* counters, size_t partial_bytes,
+                       size_t counter_slots, cudaStream_t stream) {
+    if (d->M <= 0 || d->N <= 0 || d->K <= 0) {
+        set_error("pb2_gemm: non-positive shape M=%d N=%d K=%d", d->M, d->N, d->K);
+        return -1;
+    }
+    if ((d->lda % 8) || (d->ldb % 8)) {
+        set_error("pb2_gemm: lda/ldb must be multiples of 8 elements (16-byte TMA rows), got %lld / %lld", d->lda, d->ldb);
+        return -1;
+    }
+    if ((reinterpret_cast<uintptr_t>(d->a) & 15) || (reinterpret_cast<uintptr_t>(d->b) & 15)) {
+        set_error("pb2_gemm: A and B must be 16-byte aligned");
+        return -1;
+    }
+    GemmArgs g{};
+    g.M = d->M; g.N = d->N; g.K = d->K;
+    int bn = d->block_n;
+    if (bn <= 0) {
+        bn = ((d->N + 15) / 16) * 16;
+        if (bn > 256) bn = 256;
+        if (d->N > 256) {
+            // balance the N tiles
+            int tiles = (d->N + 255) / 256;
+            bn = (((d->N + tiles - 1) / tiles) + 15) / 16 * 16;
+        }
+    }
+    if (bn % 16 || bn < 16 || bn > 256) {
+        set_error("pb2_gemm: block_n must be a multiple of 16 in [16, 256], got %d", bn);
+        return -1;
+    }
+    g.block_n = bn;
+    g.k_blocks_total = (d->K + kBlockK - 1) / kBlockK;
+    const int m_tiles = (d->M + kBlockM - 1) / kBlockM;
+    const int n_tiles = (d->N + bn - 1) / bn;
+    const long long tiles = static_cast<long long>(m_tiles) * n_tiles;
+
+    int splits = d->splits;
+    if (splits <= 0) {
+        // enough CTAs for ~2 per SM-worth of memory parallelism, but keep >= 4 k-blocks per split
+        splits = 1;
+        while (tiles * splits < 148 && g.k_blocks_total / (splits * 2) >= 4 && splits < 16) splits *= 2;
+    }
+    if (splits > g.k_blocks_total) splits = g.k_blocks_total;
+    g.k_blocks_per_split = (g.k_blocks_total + splits - 1) / splits;
+    splits = (g.k_blocks_total + g.k_blocks_per_split - 1) / g.k_blocks_per_split;
+    g.splits = splits;
+    if (splits > 1) {
+        const size_t need = static_cast<size_t>(tiles) * splits * bn * kBlockM * sizeof(float);
+        if (need > partial_bytes || static_cast<size_t>(tiles) > counter_slots) {
+            set_error("pb2_gemm: split-K scratch too small (need %zu B partials for %lld tiles x %d splits, have %zu B / %zu counters)",
+                      need, tiles, splits, partial_bytes, counter_slots);
+            return -1;
+        }
+        g.partials = partials;
+        g.counters = counters;
+    }
+
+    const int stage_bytes = (kBlockM + bn) * kBlockK * 2;
+    int stages = (200 * 1024) / stage_bytes;
+    if (stages > kMaxStages) stages = kMaxStages;
+    if (stages > g.k_blocks_per_split) stages = g.k_blocks_per_split;
+    if (stages < 1) stages = 1;
+    g.stages = stages;
+    g.tmem_cols = next_pow2_cols(bn);
+
+    g.out = d->out; g.ld_out = d->ld_out; g.out_f32 = d->out_f32; g.transpose_out = d->transpose_out;
+    g.bias = d->bias; g.bias_along_m = d->bias_along_m; g.relu = d->relu;
+    g.drop_p = d->drop_p; g.seed = d->seed; g.stream = d->rng_stream;
+    g.mask_src = static_cast<const __nv_bfloat16*>(d->mask_src); g.mask_scale = d->mask_scale;
+    g.addend = static_cast<const __nv_bfloat16*>(d->addend);
+    g.accumulate = d->accumulate; g.alpha = d->alpha == 0.f ? 1.f : d->alpha;
+    g.sumsq = d->sumsq;
+
+    CUtensorMap ta, tb;
+    if (make_tmap_bf16_2d(&ta, d->a, d->M, d->K, d->lda, kBlockM, kBlockK)) return -1;
+    if (make_tmap_bf16_2d(&tb, d->b, d->N, d->K, d->ldb, bn, kBlockK)) return -1;
+
+    const size_t smem = static_cast<size_t>(stages) * stage_bytes + sizeof(SmemCtl) + 1024;
+    static int max_smem_set = 0;
+    if (!max_smem_set) {
+        // one attribute value for every launch keeps this call out of the hot path
+    }
+    PB2_CUDA(cudaFuncSetAttribute(gemm_bf16_tn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    (void)max_smem_set;
+    dim3 grid(m_tiles, n_tiles, splits);
+    gemm_bf16_tn_kernel<<<grid, kThreads, smem, stream>>>(ta, tb, g);
+    PB2_LAUNCHED("gemm_bf16_tn_kernel");
+    return 0;
+}
+
+extern "C" int pb2_gemm_bf16(const pb2_gemm_desc* d, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+    if (!d) { set_error("pb2_gemm_bf16: null descriptor"); return -1; }
+    float* partials = nullptr;
+    unsigned int* counters = nullptr;
+    size_t partial_bytes = 0, slots = 0;
+    if (workspace && workspace_bytes > PB2_GEMM_COUNTER_BYTES) {
+        partial_bytes = workspace_bytes - PB2_GEMM_COUNTER_BYTES;
+        partials = static_cast<float*>(workspace);
+        counters = reinterpret_cast<unsigned int*>(static_cast<char*>(workspace) + partial_bytes);
+        slots = PB2_GEMM_COUNTER_BYTES / sizeof(unsigned int);
+    }
+    return gemm_launch(d, partials, counters, partial_bytes, slots, stream);
+}

@@ -1,0 +1,65 @@
+// Host-side runtime shared by the kernels: error reporting, launch counter,
+// TMA tensor-map encoding through the driver entry point.
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "common.cuh"
+#include "pipe_b200.h"
+
+namespace pb2 {
+
+std::atomic<long long> g_launches{0};
+static thread_local char t_error[512] = "";
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(t_error, sizeof(t_error), fmt, ap);
+    va_end(ap);
+}
+
+int check_cuda(cudaError_t e, const char* what) {
+    if (e == cudaSuccess) return 0;
+    set_error("%s: %s", what, cudaGetErrorString(e));
+    return -1;
+}
+
+EncodeTiledFn get_encode_tiled() {
+    static EncodeTiledFn fn = nullptr;
+    if (fn) return fn;
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess) {
+        set_error("cuTensorMapEncodeTiled is not available from this driver");
+        return nullptr;
+    }
+    fn = reinterpret_cast<EncodeTiledFn>(p);
+    return fn;
+}
+
+int make_tmap_bf16_2d(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld_elems,
+                      uint32_t box_rows, uint32_t box_cols) {
+    EncodeTiledFn enc = get_encode_tiled();
+    if (!enc) return -1;
+    cuuint64_t dims[2] = {cols, rows};                       // innermost first
+    cuuint64_t strides[1] = {ld_elems * 2};                  // bytes, dims 1..
+    cuuint32_t box[2] = {box_cols, box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled failed (%d) for [%llu x %llu] ld %llu box [%u x %u]", static_cast<int>(r),
+                  (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)ld_elems, box_rows, box_cols);
+        return -1;
+    }
+    return 0;
+}
+
+}  // namespace pb2
+
+extern "C" const char* pb2_last_error(void) { return pb2::t_error; }
+extern "C" long long pb2_launch_count(void) { return pb2::g_launches.load(); }
+extern "C" int pb2_version(void) { return 1; }

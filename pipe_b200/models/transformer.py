@@ -28,7 +28,7 @@ import torch
 from torch import Tensor, nn
 
 __all__ = ["TransformerConfig", "PositionalEncoding", "Encoder", "Decoder", "build_layers",
-           "build_stages", "count_parameters", "CONFIGS"]
+           "build_layer", "build_stage", "build_stages", "count_parameters", "CONFIGS"]
 
 Device = Union[torch.device, int, str]
 
@@ -106,22 +106,39 @@ class Decoder(nn.Module):
         return self.decoder(inp).permute(1, 0, 2)
 
 
-def build_layers(cfg: TransformerConfig, impl: str = "eager") -> List[nn.Module]:
-    """Flat layer list ``[Encoder, block x nlayers, Decoder]`` on CPU."""
-    if impl == "eager":
-        layers: List[nn.Module] = [Encoder(cfg.ntokens, cfg.emsize, cfg.dropout)]
-        for _ in range(cfg.nlayers):
-            layers.append(nn.TransformerEncoderLayer(cfg.emsize, cfg.nhead, cfg.nhid, cfg.dropout))
-        layers.append(Decoder(cfg.ntokens, cfg.emsize))
-        return layers
-    if impl == "fused":
-        from .fused import FusedDecoder, FusedEncoder, FusedEncoderLayer
-        layers = [FusedEncoder(cfg.ntokens, cfg.emsize, cfg.dropout)]
-        for _ in range(cfg.nlayers):
-            layers.append(FusedEncoderLayer(cfg.emsize, cfg.nhead, cfg.nhid, cfg.dropout, causal=cfg.causal))
-        layers.append(FusedDecoder(cfg.ntokens, cfg.emsize))
-        return layers
+def build_layer(cfg: TransformerConfig, index: int, impl: str = "eager",
+                device: Optional[Device] = None, seed: int = 0) -> nn.Module:
+    """Layer ``index`` of ``[Encoder, block x nlayers, Decoder]``, created directly on
+    ``device``.  The RNG is re-seeded per layer, so a layer's initial weights do not
+    depend on which stage (or rank) builds it."""
+    dev = torch.device("cuda", device) if isinstance(device, int) else torch.device(device or "cpu")
+    if dev.type == "cuda":
+        with torch.cuda.device(dev):
+            torch.manual_seed(seed * 1000 + index)
+    else:
+        torch.manual_seed(seed * 1000 + index)
+    last = cfg.nlayers + 1
+    with torch.device(dev):
+        if impl == "eager":
+            if index == 0:
+                return Encoder(cfg.ntokens, cfg.emsize, cfg.dropout)
+            if index == last:
+                return Decoder(cfg.ntokens, cfg.emsize)
+            return nn.TransformerEncoderLayer(cfg.emsize, cfg.nhead, cfg.nhid, cfg.dropout)
+        if impl == "fused":
+            from .fused import FusedDecoder, FusedEncoder, FusedEncoderLayer
+            if index == 0:
+                return FusedEncoder(cfg.ntokens, cfg.emsize, cfg.dropout)
+            if index == last:
+                return FusedDecoder(cfg.ntokens, cfg.emsize)
+            return FusedEncoderLayer(cfg.emsize, cfg.nhead, cfg.nhid, cfg.dropout, causal=cfg.causal)
     raise ValueError(f"unknown impl '{impl}'")
+
+
+def build_layers(cfg: TransformerConfig, impl: str = "eager", device: Optional[Device] = None,
+                 seed: int = 0) -> List[nn.Module]:
+    """Flat layer list ``[Encoder, block x nlayers, Decoder]``."""
+    return [build_layer(cfg, k, impl, device, seed) for k in range(cfg.nlayers + 2)]
 
 
 def stage_balance(nlayers: int, n_stages: int) -> List[int]:
@@ -141,21 +158,26 @@ def stage_balance(nlayers: int, n_stages: int) -> List[int]:
 
 
 def build_stages(cfg: TransformerConfig, devices: Sequence[Device], impl: str = "eager",
-                 dtype: Optional[torch.dtype] = None) -> nn.Sequential:
+                 dtype: Optional[torch.dtype] = None, seed: int = 0) -> nn.Sequential:
     """One nested ``nn.Sequential`` per device, ready for ``Pipe(...)``."""
-    layers = build_layers(cfg, impl)
     balance = stage_balance(cfg.nlayers, len(devices))
     groups = []
     at = 0
     for count, device in zip(balance, devices):
-        dev = torch.device("cuda", device) if isinstance(device, int) else torch.device(device)
-        group = nn.Sequential(*layers[at:at + count])
-        group.to(dev)
+        group = nn.Sequential(*[build_layer(cfg, k, impl, device, seed) for k in range(at, at + count)])
         if dtype is not None:
             group.to(dtype)
         groups.append(group)
         at += count
     return nn.Sequential(*groups)
+
+
+def build_stage(cfg: TransformerConfig, stage: int, n_stages: int, device: Device, impl: str = "eager",
+                seed: int = 0) -> nn.Sequential:
+    """Only stage ``stage`` of ``n_stages`` (for one-rank-per-stage layouts)."""
+    balance = stage_balance(cfg.nlayers, n_stages)
+    at = sum(balance[:stage])
+    return nn.Sequential(*[build_layer(cfg, k, impl, device, seed) for k in range(at, at + balance[stage])])
 
 
 def count_parameters(module: nn.Module) -> int:

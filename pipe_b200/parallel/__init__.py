@@ -1,0 +1,3 @@
+"""Multi-process / multi-replica parallelism: DistPipe (rank-per-stage pipeline),
+the Pipe-inside-DDP hybrid and its fused NVSwitch gradient all-reduce."""
+from .dist_pipe import DistPipe  # noqa: F401
