@@ -112,8 +112,12 @@ def main() -> int:
     n_host = 4
     host_tok = [torch.randint(0, cfg.ntokens, (cfg.batch, cfg.bptt), generator=g).pin_memory() for _ in range(n_host)]
     host_tgt = [torch.randint(0, cfg.ntokens, (cfg.batch * cfg.bptt,), generator=g).pin_memory() for _ in range(n_host)]
+    # eager arm: targets go to the last stage (reference main.py:217); fused arm: they ride through
+    # the pipe next to the tokens so the last stage can fuse the loss behind the vocab projection
+    tgt_device = trainer.first_device if args.impl == "fused" else trainer.last_device
+    feeds_tgt = trainer.is_first if args.impl == "fused" else trainer.is_last
     dev_tok = [t.to(trainer.first_device) for t in host_tok] if trainer.is_first else [None] * n_host
-    dev_tgt = [t.to(trainer.last_device) for t in host_tgt] if trainer.is_last else [None] * n_host
+    dev_tgt = [t.to(tgt_device) for t in host_tgt] if feeds_tgt else [None] * n_host
 
     def step_resident(k: int):
         trainer.step(dev_tok[k % n_host], dev_tgt[k % n_host])
@@ -126,8 +130,8 @@ def main() -> int:
         tok = tgt = None
         if trainer.is_first:
             tok = host_tok[k % n_host].to(trainer.first_device, non_blocking=True)
-        if trainer.is_last:
-            tgt = host_tgt[k % n_host].to(trainer.last_device, non_blocking=True)
+        if feeds_tgt:
+            tgt = host_tgt[k % n_host].to(tgt_device, non_blocking=True)
         loss = trainer.step(tok, tgt)
         if trainer.is_last:
             last_loss[0] = float(loss.item())           # device -> host read of the step's result

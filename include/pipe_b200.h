@@ -63,6 +63,95 @@ size_t pb2_gemm_workspace_bytes(void);
  * split-K partial tiles and per-tile arrival counters; may be NULL when splits == 1. */
 int pb2_gemm_bf16(const pb2_gemm_desc* desc, void* workspace, size_t workspace_bytes, cudaStream_t stream);
 
+/* ---- residual add + LayerNorm: y = LN(x + h) (h may be NULL) ------------------------------
+ * bf16 rows of width E (multiple of 8, <= 8192), fp32 gamma/beta/statistics.
+ * Backward also returns dh = dres * dropout_mask / (1 - p): the gradient of the sub-layer output
+ * *before* the dropout that the producing GEMM epilogue applied with the same (seed, rng_stream);
+ * dgamma/dbeta are accumulated with fp32 atomics.
+ * Reference counterpart: dropout + add + nn.LayerNorm inside nn.TransformerEncoderLayer
+ * (main.py:148); SURVEY.md K5. */
+int pb2_add_layernorm_fwd(const void* x, const void* h, const float* gamma, const float* beta, void* y,
+                          float* mean, float* rstd, int rows, int E, float eps, cudaStream_t stream);
+int pb2_add_layernorm_bwd(const void* dy, const void* x, const void* h, const float* gamma, const float* mean,
+                          const float* rstd, void* dres, void* dh, float* dgamma, float* dbeta, int rows, int E,
+                          float drop_p, unsigned long long seed, unsigned long long rng_stream,
+                          cudaStream_t stream);
+
+/* ---- embedding * sqrt(E) + positional table + dropout --------------------------------------
+ * tokens int64 [N, S] (batch-first); out bf16 [S*N, E] sequence-first (row = s*N + n); weight and
+ * pe fp32.  Backward scatter-adds into the fp32 weight gradient.
+ * Reference counterpart: Encoder / PositionalEncoding (main.py:24-40,57-73); SURVEY.md K1. */
+int pb2_embed_fwd(const long long* tokens, const float* weight, const float* pe, void* out, int N, int S, int E,
+                  float scale, float drop_p, unsigned long long seed, unsigned long long rng_stream,
+                  cudaStream_t stream);
+int pb2_embed_bwd(const long long* tokens, const void* dout, float* dweight, int N, int S, int E, float scale,
+                  float drop_p, unsigned long long seed, unsigned long long rng_stream, cudaStream_t stream);
+
+/* ---- softmax cross-entropy over bf16 logits [rows, ld] with V valid columns ----------------
+ * loss_rows[r] = logsumexp - logit[target] (loss_rows may be NULL); with write_grad the logits are
+ * overwritten by (softmax - onehot) * row_scale[r] (row_scale may be NULL = 1; pad columns zeroed),
+ * ready to be the dY of the vocabulary GEMMs.
+ * Reference counterpart: nn.CrossEntropyLoss (main.py:182,217); SURVEY.md K9. */
+int pb2_cross_entropy(void* logits, const long long* targets, float* loss_rows, const float* row_scale, int rows,
+                      int V, long long ld, int write_grad, cudaStream_t stream);
+
+/* ---- bf16 transpose dst[c, r] = src[r, c] with optional fused column sums -------------------
+ * Produces the K-major operands of the weight-gradient GEMM; colsum[c] += scale * sum_r src[r, c]
+ * is the bias gradient.  dst columns [R, ld_dst) are zero-filled. */
+int pb2_transpose_colsum(const void* src, long long ld_src, void* dst, long long ld_dst, int R, int C,
+                         float* colsum, float scale, cudaStream_t stream);
+
+/* Several transposes in one launch (a layer's backward stacks all its wgrad operands at once).
+ * Unlike the single form, dst columns beyond R are left untouched. */
+#define PB2_MAX_TRANSPOSES 8
+typedef struct pb2_transpose_job {
+    const void* src;      /* bf16 [R, C], row stride ld_src */
+    void* dst;            /* bf16 [C, >= R], row stride ld_dst */
+    long long ld_src, ld_dst;
+    int R, C;
+    float* colsum;        /* optional fp32 [C]: += scale * column sums */
+    float scale;
+} pb2_transpose_job;
+typedef struct pb2_transpose_jobs {
+    pb2_transpose_job job[PB2_MAX_TRANSPOSES];
+    int count;
+} pb2_transpose_jobs;
+int pb2_transpose_multi(const pb2_transpose_jobs* jobs, cudaStream_t stream);
+
+/* ---- *out += sum(x^2)  (gradient-norm partial; x fp32, 16-byte aligned) ---------------------- */
+int pb2_sumsq(const float* x, size_t n, float* out, cudaStream_t stream);
+
+/* ---- attention core on packed QKV [T, 3E] (row = s*NB + n), out [T, E] ----------------------
+ * softmax(QK^T/sqrt(D)) V with probability dropout and optional causal mask.  S <= 128, D <= 256.
+ * Backward recomputes the probabilities and the dropout mask.
+ * Reference counterpart: nn.MultiheadAttention core (main.py:148); SURVEY.md K3. */
+int pb2_attention_fwd(const void* qkv, void* out, int NB, int S, int H, int D, int causal, float drop_p,
+                      unsigned long long seed, unsigned long long rng_stream, cudaStream_t stream);
+int pb2_attention_bwd(const void* qkv, const void* dout, void* dqkv, int NB, int S, int H, int D, int causal,
+                      float drop_p, unsigned long long seed, unsigned long long rng_stream, cudaStream_t stream);
+
+/* ---- multi-tensor fused clip + Adam ---------------------------------------------------------
+ * `table_dev` is a device array of n_tensors descriptors sorted by tile_start; a tensor of
+ * [rows, cols] owns ceil(rows/32) * ceil(cols/64) consecutive tiles.  w/g/m/v are fp32; w16
+ * (optional) is the bf16 shadow, w16t (optional) the transposed bf16 shadow with row stride ld_t.
+ * normsq_dev holds the squared global gradient norm (device scalar); the clip coefficient
+ * min(1, max_norm / (sqrt(normsq) * grad_scale + 1e-6)) is computed on the device.
+ * Reference counterpart: clip_grad_norm_ + optim.Adam (main.py:184,219-220); SURVEY.md K10, K11. */
+typedef struct pb2_adam_tensor {
+    float* w;
+    const float* g;
+    float* m;
+    float* v;
+    void* w16;
+    void* w16t;
+    int rows, cols, ld_t, tile_start;
+} pb2_adam_tensor;
+
+int pb2_adam_step(const pb2_adam_tensor* table_dev, int n_tensors, int total_tiles, const float* normsq_dev,
+                  float lr, float beta1, float beta2, float eps, float weight_decay, int step, float max_norm,
+                  float grad_scale, cudaStream_t stream);
+int pb2_refresh_shadows(const pb2_adam_tensor* table_dev, int n_tensors, int total_tiles, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,256 @@
+// Multi-head self-attention core for short sequences: softmax(Q K^T / sqrt(d)) V with
+// attention-probability dropout and an optional causal mask, forward and backward.
+//
+// Operates directly on the packed QKV projection output [T, 3E] of a sequence-first
+// micro-batch (row = s * NB + n), so no head split / permute kernels are needed; the output
+// is written head-merged as [T, E], ready for the out-projection GEMM.
+//
+// In this framework's configs attention is <= 0.2 % of the FLOPs (S = 25..128, SURVEY.md
+// §6.2): one CTA owns one (sequence, head) pair, keeps Q, K, V (and dO) in shared memory and
+// the S x S score matrix on chip for the whole pass; nothing but QKV and O touches HBM and
+// the backward recomputes the probabilities (and the Philox dropout mask) instead of
+// storing them.  Limits: S <= 128, head_dim <= 256, shared memory <= 227 KB.
+//
+// Reference counterpart: nn.MultiheadAttention inside nn.TransformerEncoderLayer
+// (main.py:148), dropout 0.2 on the probabilities, no mask passed.  SURVEY.md K3.
+#include "common.cuh"
+#include "pipe_b200.h"
+
+namespace pb2 {
+
+constexpr int kAttnThreads = 256;
+
+struct AttnShape {
+    int NB, S, H, D, E;      // sequences in the micro-batch, sequence length, heads, head dim, model dim
+    float scale;
+    int causal;
+    float drop_p;
+    unsigned long long seed, rng_stream;
+};
+
+__device__ __forceinline__ void load_head(const __nv_bfloat16* __restrict__ base, long long ld, int NB, int S, int D,
+                                          int n, __nv_bfloat16* dst, int dpad) {
+    // rows s*NB + n, D contiguous elements each; 8-element (16 B) vectors
+    const int vec_per_row = D / 8;
+    for (int t = threadIdx.x; t < S * vec_per_row; t += blockDim.x) {
+        const int s = t / vec_per_row, v = t % vec_per_row;
+        const uint4 raw = *reinterpret_cast<const uint4*>(base + (static_cast<size_t>(s) * NB + n) * ld + v * 8);
+        uint32_t* d = reinterpret_cast<uint32_t*>(dst + s * dpad + v * 8);
+        d[0] = raw.x; d[1] = raw.y; d[2] = raw.z; d[3] = raw.w;
+    }
+}
+
+__device__ __forceinline__ float dot_bf16(const __nv_bfloat16* a, const __nv_bfloat16* b, int D) {
+    float acc = 0.f;
+    const __nv_bfloat162* a2 = reinterpret_cast<const __nv_bfloat162*>(a);
+    const __nv_bfloat162* b2 = reinterpret_cast<const __nv_bfloat162*>(b);
+#pragma unroll 8
+    for (int c = 0; c < D / 2; ++c) {
+        const float2 x = __bfloat1622float2(a2[c]), y = __bfloat1622float2(b2[c]);
+        acc = fmaf(x.x, y.x, acc);
+        acc = fmaf(x.y, y.y, acc);
+    }
+    return acc;
+}
+
+// scores -> probabilities in place; returns nothing.  One warp per row.
+__device__ __forceinline__ void softmax_rows(float* sc, int S, int spad, int causal) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+    for (int i = warp; i < S; i += nwarps) {
+        float* r = sc + i * spad;
+        const int lim = causal ? i + 1 : S;
+        float mx = -INFINITY;
+        for (int j = lane; j < lim; j += 32) mx = fmaxf(mx, r[j]);
+        mx = warp_max(mx);
+        float se = 0.f;
+        for (int j = lane; j < lim; j += 32) {
+            const float e = __expf(r[j] - mx);
+            r[j] = e;
+            se += e;
+        }
+        se = warp_sum(se);
+        const float inv = 1.f / se;
+        for (int j = lane; j < S; j += 32) r[j] = j < lim ? r[j] * inv : 0.f;
+    }
+}
+
+__device__ __forceinline__ float keep_scale(const Philox& ph, const AttnShape& a, uint32_t thr, float inv_keep, int n,
+                                            int h, int i, int j) {
+    if (a.drop_p <= 0.f) return 1.f;
+    const uint64_t idx = ((static_cast<uint64_t>(n) * a.H + h) * a.S + i) * a.S + j;
+    return dropout_keep(ph, a.rng_stream, idx, thr) ? inv_keep : 0.f;
+}
+
+__global__ void __launch_bounds__(kAttnThreads)
+attn_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out, const AttnShape a) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    const int S = a.S, D = a.D, dpad = D + 8, spad = S + 1;
+    __nv_bfloat16* q = reinterpret_cast<__nv_bfloat16*>(smem);
+    __nv_bfloat16* k = q + S * dpad;
+    __nv_bfloat16* v = k + S * dpad;
+    float* sc = reinterpret_cast<float*>(v + S * dpad);
+    const int n = blockIdx.x / a.H, h = blockIdx.x % a.H;
+    const long long ld = 3LL * a.E;
+
+    load_head(qkv + h * D, ld, a.NB, S, D, n, q, dpad);
+    load_head(qkv + a.E + h * D, ld, a.NB, S, D, n, k, dpad);
+    load_head(qkv + 2 * a.E + h * D, ld, a.NB, S, D, n, v, dpad);
+    __syncthreads();
+
+    for (int p = threadIdx.x; p < S * S; p += blockDim.x) {
+        const int i = p / S, j = p % S;
+        sc[i * spad + j] = dot_bf16(q + i * dpad, k + j * dpad, D) * a.scale;
+    }
+    __syncthreads();
+    softmax_rows(sc, S, spad, a.causal);
+    __syncthreads();
+
+    if (a.drop_p > 0.f) {
+        const Philox ph(a.seed);
+        const uint32_t thr = static_cast<uint32_t>(fminf(a.drop_p, 0.999999f) * 4294967296.0f);
+        const float inv_keep = 1.f / (1.f - a.drop_p);
+        for (int p = threadIdx.x; p < S * S; p += blockDim.x) {
+            const int i = p / S, j = p % S;
+            sc[i * spad + j] *= keep_scale(ph, a, thr, inv_keep, n, h, i, j);
+        }
+        __syncthreads();
+    }
+
+    // O = P V : thread owns (i, pair of columns)
+    for (int p = threadIdx.x; p < S * (D / 2); p += blockDim.x) {
+        const int i = p / (D / 2), c2 = p % (D / 2);
+        float o0 = 0.f, o1 = 0.f;
+        const float* pr = sc + i * spad;
+        for (int j = 0; j < S; ++j) {
+            const float2 vv = __bfloat1622float2(reinterpret_cast<const __nv_bfloat162*>(v + j * dpad)[c2]);
+            o0 = fmaf(pr[j], vv.x, o0);
+            o1 = fmaf(pr[j], vv.y, o1);
+        }
+        reinterpret_cast<__nv_bfloat162*>(out + (static_cast<size_t>(i) * a.NB + n) * a.E + h * D)[c2] =
+            __floats2bfloat162_rn(o0, o1);
+    }
+}
+
+__global__ void __launch_bounds__(kAttnThreads)
+attn_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* __restrict__ dout,
+                __nv_bfloat16* __restrict__ dqkv, const AttnShape a) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    const int S = a.S, D = a.D, dpad = D + 8, spad = S + 1;
+    __nv_bfloat16* q = reinterpret_cast<__nv_bfloat16*>(smem);
+    __nv_bfloat16* k = q + S * dpad;
+    __nv_bfloat16* v = k + S * dpad;
+    __nv_bfloat16* dO = v + S * dpad;
+    float* P = reinterpret_cast<float*>(dO + S * dpad);     // softmax probabilities (pre-dropout)
+    float* dS = P + S * spad;                               // first dP (post-dropout grads), then dS
+    const int n = blockIdx.x / a.H, h = blockIdx.x % a.H;
+    const long long ld = 3LL * a.E;
+
+    load_head(qkv + h * D, ld, a.NB, S, D, n, q, dpad);
+    load_head(qkv + a.E + h * D, ld, a.NB, S, D, n, k, dpad);
+    load_head(qkv + 2 * a.E + h * D, ld, a.NB, S, D, n, v, dpad);
+    load_head(dout + h * D, a.E, a.NB, S, D, n, dO, dpad);
+    __syncthreads();
+
+    const Philox ph(a.seed);
+    const uint32_t thr = static_cast<uint32_t>(fminf(a.drop_p, 0.999999f) * 4294967296.0f);
+    const float inv_keep = a.drop_p > 0.f ? 1.f / (1.f - a.drop_p) : 1.f;
+
+    for (int p = threadIdx.x; p < S * S; p += blockDim.x) {
+        const int i = p / S, j = p % S;
+        P[i * spad + j] = dot_bf16(q + i * dpad, k + j * dpad, D) * a.scale;
+        // gradient w.r.t. the dropped-out probabilities, already mapped back through the mask
+        dS[i * spad + j] = dot_bf16(dO + i * dpad, v + j * dpad, D) * keep_scale(ph, a, thr, inv_keep, n, h, i, j);
+    }
+    __syncthreads();
+    softmax_rows(P, S, spad, a.causal);
+    __syncthreads();
+
+    // dV[j][c] = sum_i Pdrop[i][j] * dO[i][c]
+    for (int p = threadIdx.x; p < S * (D / 2); p += blockDim.x) {
+        const int j = p / (D / 2), c2 = p % (D / 2);
+        float g0 = 0.f, g1 = 0.f;
+        for (int i = 0; i < S; ++i) {
+            const float w = P[i * spad + j] * keep_scale(ph, a, thr, inv_keep, n, h, i, j);
+            const float2 d = __bfloat1622float2(reinterpret_cast<const __nv_bfloat162*>(dO + i * dpad)[c2]);
+            g0 = fmaf(w, d.x, g0);
+            g1 = fmaf(w, d.y, g1);
+        }
+        reinterpret_cast<__nv_bfloat162*>(dqkv + (static_cast<size_t>(j) * a.NB + n) * ld + 2 * a.E + h * D)[c2] =
+            __floats2bfloat162_rn(g0, g1);
+    }
+    __syncthreads();
+
+    // dS = P * (dP - sum_j dP * P) * scale          (one warp per row)
+    {
+        const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+        for (int i = warp; i < S; i += nwarps) {
+            float dlt = 0.f;
+            for (int j = lane; j < S; j += 32) dlt += dS[i * spad + j] * P[i * spad + j];
+            dlt = warp_sum(dlt);
+            for (int j = lane; j < S; j += 32)
+                dS[i * spad + j] = P[i * spad + j] * (dS[i * spad + j] - dlt) * a.scale;
+        }
+    }
+    __syncthreads();
+
+    // dQ[i][c] = sum_j dS[i][j] K[j][c];   dK[j][c] = sum_i dS[i][j] Q[i][c]
+    for (int p = threadIdx.x; p < S * (D / 2); p += blockDim.x) {
+        const int r = p / (D / 2), c2 = p % (D / 2);
+        float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
+        for (int t = 0; t < S; ++t) {
+            const float2 kk = __bfloat1622float2(reinterpret_cast<const __nv_bfloat162*>(k + t * dpad)[c2]);
+            const float2 qq = __bfloat1622float2(reinterpret_cast<const __nv_bfloat162*>(q + t * dpad)[c2]);
+            const float s_rt = dS[r * spad + t], s_tr = dS[t * spad + r];
+            a0 = fmaf(s_rt, kk.x, a0);
+            a1 = fmaf(s_rt, kk.y, a1);
+            b0 = fmaf(s_tr, qq.x, b0);
+            b1 = fmaf(s_tr, qq.y, b1);
+        }
+        __nv_bfloat16* row = dqkv + (static_cast<size_t>(r) * a.NB + n) * ld + h * D;
+        reinterpret_cast<__nv_bfloat162*>(row)[c2] = __floats2bfloat162_rn(a0, a1);
+        reinterpret_cast<__nv_bfloat162*>(row + a.E)[c2] = __floats2bfloat162_rn(b0, b1);
+    }
+}
+
+static int attn_check(const char* who, int NB, int S, int H, int D, size_t smem) {
+    if (NB <= 0 || S <= 0 || H <= 0 || D <= 0) { set_error("%s: non-positive shape", who); return -1; }
+    if (S > 128 || D > 256 || (D % 8)) {
+        set_error("%s: supports S <= 128 and head_dim <= 256 (multiple of 8); got S=%d head_dim=%d", who, S, D);
+        return -1;
+    }
+    if (smem > 227 * 1024) {
+        set_error("%s: S=%d head_dim=%d needs %zu B shared memory (> 227 KB)", who, S, D, smem);
+        return -1;
+    }
+    return 0;
+}
+
+}  // namespace pb2
+
+using namespace pb2;
+
+extern "C" int pb2_attention_fwd(const void* qkv, void* out, int NB, int S, int H, int D, int causal, float drop_p,
+                                 unsigned long long seed, unsigned long long rng_stream, cudaStream_t stream) {
+    const size_t smem = static_cast<size_t>(3) * S * (D + 8) * 2 + static_cast<size_t>(S) * (S + 1) * 4;
+    if (attn_check("pb2_attention_fwd", NB, S, H, D, smem)) return -1;
+    AttnShape a{NB, S, H, D, H * D, 1.f / sqrtf(static_cast<float>(D)), causal, drop_p, seed, rng_stream};
+    PB2_CUDA(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attn_fwd_kernel<<<NB * H, kAttnThreads, smem, stream>>>(static_cast<const __nv_bfloat16*>(qkv),
+                                                            static_cast<__nv_bfloat16*>(out), a);
+    PB2_LAUNCHED("attn_fwd_kernel");
+    return 0;
+}
+
+extern "C" int pb2_attention_bwd(const void* qkv, const void* dout, void* dqkv, int NB, int S, int H, int D,
+                                 int causal, float drop_p, unsigned long long seed, unsigned long long rng_stream,
+                                 cudaStream_t stream) {
+    const size_t smem = static_cast<size_t>(4) * S * (D + 8) * 2 + static_cast<size_t>(2) * S * (S + 1) * 4;
+    if (attn_check("pb2_attention_bwd", NB, S, H, D, smem)) return -1;
+    AttnShape a{NB, S, H, D, H * D, 1.f / sqrtf(static_cast<float>(D)), causal, drop_p, seed, rng_stream};
+    PB2_CUDA(cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attn_bwd_kernel<<<NB * H, kAttnThreads, smem, stream>>>(static_cast<const __nv_bfloat16*>(qkv),
+                                                            static_cast<const __nv_bfloat16*>(dout),
+                                                            static_cast<__nv_bfloat16*>(dqkv), a);
+    PB2_LAUNCHED("attn_bwd_kernel");
+    return 0;
+}

@@ -1,0 +1,401 @@
+"""The tutorial Transformer's blocks on the sm_100a kernels of :mod:`pipe_b200.ops`.
+
+Drop-in bodies for :class:`~pipe_b200.models.transformer.Encoder`,
+``nn.TransformerEncoderLayer`` and :class:`~pipe_b200.models.transformer.Decoder`
+with the *same parameter names* (``self_attn.in_proj_weight``, ``linear1.weight``,
+``norm1.weight``, ``encoder.weight``, ``decoder.weight`` ...), so a state dict
+moves freely between the eager and the fused model.
+
+Precision policy: parameters are fp32 masters (what the optimizer and the state
+dict see); every GEMM reads a bf16 *shadow* of its weight (and the dgrad GEMM a
+transposed bf16 shadow), accumulates in fp32 in TMEM, and activations travel
+between layers in bf16.  :class:`~pipe_b200.ops.optim.FusedClipAdam` rewrites
+master and both shadows in one pass; any other in-place update of a master is
+noticed through the tensor version counter and the shadows are re-derived.
+
+Per encoder layer the forward is 7 launches (QKV GEMM, attention, out-proj GEMM
+with bias+dropout epilogue, add+LayerNorm, FFN1 GEMM with bias+ReLU+dropout, FFN2
+GEMM with bias+dropout, add+LayerNorm) and the backward 8 (two LayerNorm
+backwards that also undo the dropout, four dgrad GEMMs with fused
+ReLU/dropout-mask and residual-add epilogues, attention backward, one
+multi-transpose that stacks all wgrad operands); weight gradients are one GEMM per
+Linear per *mini-batch* (:mod:`pipe_b200.ops.wgrad`).
+
+Parity: reference ``main.py:24-73,115-120,139-157``; SURVEY.md K1-K9.
+"""
+from __future__ import annotations
+
+import math
+from typing import Any, Dict, List, Optional, Tuple
+
+import torch
+from torch import Tensor, nn
+
+from ..ops import functional as F2
+from ..ops.gemm import gemm_nt
+from ..ops.wgrad import LinearGrad, ensure_grad
+
+__all__ = ["FusedEncoder", "FusedEncoderLayer", "FusedDecoder", "Shadow"]
+
+
+def _round_up(x: int, m: int) -> int:
+    return (x + m - 1) // m * m
+
+
+class Shadow:
+    """bf16 copy ``w16 [out, in]`` and transposed copy ``w16t [in, ld_t]`` of an
+    fp32 master weight, kept in sync lazily."""
+
+    def __init__(self, param: nn.Parameter) -> None:
+        self.param = param
+        self.w16: Optional[Tensor] = None
+        self.w16t: Optional[Tensor] = None
+        self.version = -1
+
+    def allocate(self) -> None:
+        p = self.param
+        if self.w16 is None or self.w16.device != p.device:
+            rows, cols = p.shape
+            self.w16 = torch.empty((rows, cols), dtype=torch.bfloat16, device=p.device)
+            self.w16t = torch.zeros((cols, _round_up(rows, 8)), dtype=torch.bfloat16, device=p.device)
+            self.version = -1
+
+    def ensure(self) -> Tuple[Tensor, Tensor]:
+        p = self.param
+        self.allocate()
+        if p._version != self.version:
+            with torch.no_grad():
+                self.w16.copy_(p)
+                self.w16t[:, : p.size(0)].copy_(p.t())
+            self.version = p._version
+        return self.w16, self.w16t
+
+    def mark_synced(self) -> None:
+        self.version = self.param._version
+
+
+class _Linear(nn.Module):
+    """Parameter holder with nn.Linear's names and init (no forward of its own)."""
+
+    def __init__(self, in_features: int, out_features: int):
+        super().__init__()
+        ref = nn.Linear(in_features, out_features)
+        self.weight = nn.Parameter(ref.weight.detach().clone())
+        self.bias = nn.Parameter(ref.bias.detach().clone())
+
+
+class _Attention(nn.Module):
+    """Parameter holder with nn.MultiheadAttention's names and init."""
+
+    def __init__(self, embed_dim: int):
+        super().__init__()
+        self.in_proj_weight = nn.Parameter(torch.empty(3 * embed_dim, embed_dim))
+        self.in_proj_bias = nn.Parameter(torch.zeros(3 * embed_dim))
+        self.out_proj = _Linear(embed_dim, embed_dim)
+        nn.init.xavier_uniform_(self.in_proj_weight)
+        nn.init.zeros_(self.out_proj.bias)
+
+
+class _Norm(nn.Module):
+    def __init__(self, dim: int, eps: float = 1e-5):
+        super().__init__()
+        self.weight = nn.Parameter(torch.ones(dim))
+        self.bias = nn.Parameter(torch.zeros(dim))
+        self.eps = eps
+
+
+class _FusedBase(nn.Module):
+    """Common bookkeeping: shadows and deferred-wgrad objects per weight."""
+
+    def _register_linear(self, key: str, weight: nn.Parameter, bias: Optional[nn.Parameter]) -> None:
+        if "_pb2_lin" not in self.__dict__:
+            self.__dict__["_pb2_lin"] = {}
+        self.__dict__["_pb2_lin"][key] = (Shadow(weight), LinearGrad(weight, bias))
+
+    def pb2_shadows(self) -> List[Shadow]:
+        return [s for s, _ in self.__dict__.get("_pb2_lin", {}).values()]
+
+    def pb2_linear_grads(self) -> List[LinearGrad]:
+        return [g for _, g in self.__dict__.get("_pb2_lin", {}).values()]
+
+    def _sh(self, key: str) -> Tuple[Tensor, Tensor]:
+        return self.__dict__["_pb2_lin"][key][0].ensure()
+
+    def _lg(self, key: str) -> LinearGrad:
+        return self.__dict__["_pb2_lin"][key][1]
+
+    def _apply(self, fn, *args, **kwargs):
+        out = super()._apply(fn, *args, **kwargs)
+        # masters may have been replaced / moved: re-bind shadows and wgrad stashes
+        self._rebind()
+        return out
+
+    def _rebind(self) -> None:
+        pass
+
+
+# ======================================================================================
+# encoder layer
+# ======================================================================================
+class _EncoderLayerFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x: Tensor, layer: "FusedEncoderLayer", *params: Tensor) -> Tensor:  # type: ignore[override]
+        S, NB, E = x.shape
+        T = S * NB
+        x2 = x.contiguous().view(T, E)
+        if x2.dtype != torch.bfloat16:
+            x2 = x2.to(torch.bfloat16)
+        p = layer.dropout if layer.training else 0.0
+        seed = F2.draw_seed() if p > 0 else 0
+        at, l1, l2, n1, n2 = layer.self_attn, layer.linear1, layer.linear2, layer.norm1, layer.norm2
+
+        w_qkv, _ = layer._sh("qkv")
+        w_o, _ = layer._sh("o")
+        w_1, _ = layer._sh("l1")
+        w_2, _ = layer._sh("l2")
+
+        qkv = gemm_nt(w_qkv, x2, transpose_out=True, bias=at.in_proj_bias, bias_along_m=True)
+        a = F2.attention_fwd(qkv, NB, S, layer.nhead, causal=layer.causal, drop_p=p, seed=seed, rng_stream=0)
+        o = gemm_nt(w_o, a, transpose_out=True, bias=at.out_proj.bias, bias_along_m=True,
+                    drop_p=p, seed=seed, rng_stream=1)
+        x1, mean1, rstd1 = F2.add_layernorm_fwd(x2, o, n1.weight, n1.bias, n1.eps)
+        hmid = gemm_nt(w_1, x1, transpose_out=True, bias=l1.bias, bias_along_m=True, relu=True,
+                       drop_p=p, seed=seed, rng_stream=2)
+        f = gemm_nt(w_2, hmid, transpose_out=True, bias=l2.bias, bias_along_m=True,
+                    drop_p=p, seed=seed, rng_stream=3)
+        y, mean2, rstd2 = F2.add_layernorm_fwd(x1, f, n2.weight, n2.bias, n2.eps)
+
+        ctx.layer = layer
+        ctx.meta = (S, NB, E, p, seed)
+        ctx.save_for_backward(x2, qkv, a, o, x1, mean1, rstd1, hmid, f, mean2, rstd2)
+        return y.view(S, NB, E)
+
+    @staticmethod
+    def backward(ctx, dy: Tensor):  # type: ignore[override]
+        layer: FusedEncoderLayer = ctx.layer
+        S, NB, E, p, seed = ctx.meta
+        T = S * NB
+        x2, qkv, a, o, x1, mean1, rstd1, hmid, f, mean2, rstd2 = ctx.saved_tensors
+        at, l1, l2, n1, n2 = layer.self_attn, layer.linear1, layer.linear2, layer.norm1, layer.norm2
+        inv_keep = 1.0 / (1.0 - p) if p > 0 else 1.0
+        dy2 = dy.contiguous().view(T, E)
+        if dy2.dtype != torch.bfloat16:
+            dy2 = dy2.to(torch.bfloat16)
+
+        _, wt_qkv = layer._sh("qkv")
+        _, wt_o = layer._sh("o")
+        _, wt_1 = layer._sh("l1")
+        _, wt_2 = layer._sh("l2")
+        H = l1.weight.size(0)
+
+        # y = LN2(x1 + dropout(ffn))
+        dr2, df = F2.add_layernorm_bwd(dy2, x1, f, n2.weight, mean2, rstd2, ensure_grad(n2.weight),
+                                       ensure_grad(n2.bias), want_dh=True, drop_p=p, seed=seed, rng_stream=3)
+        # through linear2, then ReLU + dropout (mask recovered from the saved activation)
+        dz1 = gemm_nt(wt_2[:, :E], df, transpose_out=True, mask_src=hmid, mask_scale=inv_keep)
+        # through linear1, plus the residual branch
+        dx1 = gemm_nt(wt_1[:, :H], dz1, transpose_out=True, addend=dr2)
+        # x1 = LN1(x + dropout(attn_out))
+        dr1, do = F2.add_layernorm_bwd(dx1, x2, o, n1.weight, mean1, rstd1, ensure_grad(n1.weight),
+                                       ensure_grad(n1.bias), want_dh=True, drop_p=p, seed=seed, rng_stream=1)
+        da = gemm_nt(wt_o[:, :E], do, transpose_out=True)
+        dqkv = F2.attention_bwd(qkv, da, NB, S, layer.nhead, causal=layer.causal, drop_p=p, seed=seed, rng_stream=0)
+        dx = gemm_nt(wt_qkv[:, : 3 * E], dqkv, transpose_out=True, addend=dr1)
+
+        # stack every wgrad operand of this layer (and the bias gradients) in one launch
+        jobs = (layer._lg("qkv").jobs(x2, dqkv) + layer._lg("o").jobs(a, do)
+                + layer._lg("l1").jobs(x1, dz1) + layer._lg("l2").jobs(hmid, df))
+        F2.transpose_multi(jobs)
+
+        return (dx.view(S, NB, E), None) + (None,) * (len(ctx.needs_input_grad) - 2)
+
+
+class FusedEncoderLayer(_FusedBase):
+    """Post-norm Transformer encoder layer (ReLU FFN, sequence-first input
+    ``(S, N, E)``) — ``nn.TransformerEncoderLayer(d_model, nhead, dim_feedforward,
+    dropout)`` on hand-written kernels.  Extra positional inputs are passed
+    through untouched (used to carry targets to a fused loss on the last stage)."""
+
+    def __init__(self, d_model: int, nhead: int, dim_feedforward: int = 2048, dropout: float = 0.1,
+                 causal: bool = False, layer_norm_eps: float = 1e-5):
+        super().__init__()
+        if d_model % nhead:
+            raise ValueError("d_model must be divisible by nhead")
+        self.d_model, self.nhead, self.dropout, self.causal = d_model, nhead, float(dropout), bool(causal)
+        self.self_attn = _Attention(d_model)
+        self.linear1 = _Linear(d_model, dim_feedforward)
+        self.linear2 = _Linear(dim_feedforward, d_model)
+        self.norm1 = _Norm(d_model, layer_norm_eps)
+        self.norm2 = _Norm(d_model, layer_norm_eps)
+        self._rebind()
+
+    def _rebind(self) -> None:
+        if not hasattr(self, "norm2"):
+            return
+        self._register_linear("qkv", self.self_attn.in_proj_weight, self.self_attn.in_proj_bias)
+        self._register_linear("o", self.self_attn.out_proj.weight, self.self_attn.out_proj.bias)
+        self._register_linear("l1", self.linear1.weight, self.linear1.bias)
+        self._register_linear("l2", self.linear2.weight, self.linear2.bias)
+
+    def forward(self, x: Tensor, *extra: Any):
+        y = _EncoderLayerFn.apply(x, self, *self.parameters())
+        return (y, *extra) if extra else y
+
+
+# ======================================================================================
+# embedding + positions + dropout
+# ======================================================================================
+class _EmbedFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, tokens: Tensor, module: "FusedEncoder", weight: Tensor) -> Tensor:  # type: ignore[override]
+        p = module.dropout if module.training else 0.0
+        seed = F2.draw_seed() if p > 0 else 0
+        tokens = tokens.contiguous()
+        out = F2.embed_fwd(tokens, weight, module.pos_encoder.pe, math.sqrt(module.ninp), p, seed, 0)
+        ctx.module = module
+        ctx.meta = (p, seed)
+        ctx.save_for_backward(tokens)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout: Tensor):  # type: ignore[override]
+        (tokens,) = ctx.saved_tensors
+        p, seed = ctx.meta
+        module: FusedEncoder = ctx.module
+        d = dout.contiguous()
+        if d.dtype != torch.bfloat16:
+            d = d.to(torch.bfloat16)
+        F2.embed_bwd(tokens, d, ensure_grad(module.encoder.weight), math.sqrt(module.ninp), p, seed, 0)
+        return None, None, None
+
+
+class _PE(nn.Module):
+    def __init__(self, d_model: int, max_len: int = 5000):
+        super().__init__()
+        position = torch.arange(max_len, dtype=torch.float32).unsqueeze(1)
+        freq = torch.exp(torch.arange(0, d_model, 2, dtype=torch.float32) * (-math.log(10000.0) / d_model))
+        pe = torch.zeros(max_len, 1, d_model)
+        pe[:, 0, 0::2] = torch.sin(position * freq)
+        pe[:, 0, 1::2] = torch.cos(position * freq)
+        self.register_buffer("pe", pe)
+
+
+class FusedEncoder(nn.Module):
+    """``(N, S)`` int64 tokens -> ``(S, N, E)`` bf16: embedding * sqrt(E) + sinusoidal
+    positions + dropout in one kernel (reference ``main.py:24-40,57-73``).  A second
+    input (e.g. ``(N, S)`` targets) is passed through."""
+
+    def __init__(self, ntoken: int, ninp: int, dropout: float = 0.5):
+        super().__init__()
+        self.pos_encoder = _PE(ninp)
+        self.encoder = nn.Embedding(ntoken, ninp)
+        self.ninp = ninp
+        self.dropout = float(dropout)
+        nn.init.uniform_(self.encoder.weight, -0.1, 0.1)
+
+    def forward(self, src: Tensor, *extra: Any):
+        if src.size(1) > self.pos_encoder.pe.size(0):
+            raise ValueError("sequence longer than the positional table")
+        out = _EmbedFn.apply(src, self, self.encoder.weight)
+        return (out, *extra) if extra else out
+
+
+# ======================================================================================
+# vocabulary projection (+ fused cross-entropy)
+# ======================================================================================
+class _DecoderFn(torch.autograd.Function):
+    """logits = x W^T + b, returned batch-first like the reference's Decoder."""
+
+    @staticmethod
+    def forward(ctx, x: Tensor, module: "FusedDecoder", *params: Tensor) -> Tensor:  # type: ignore[override]
+        S, NB, E = x.shape
+        T = S * NB
+        x2 = x.contiguous().view(T, E)
+        if x2.dtype != torch.bfloat16:
+            x2 = x2.to(torch.bfloat16)
+        V = module.ntoken
+        ld = _round_up(V, 64)
+        w16, _ = module._sh("dec")
+        buf = torch.empty((T, ld), dtype=torch.bfloat16, device=x.device)
+        gemm_nt(w16, x2, out=buf[:, :V], transpose_out=True, bias=module.decoder.bias, bias_along_m=True)
+        ctx.module = module
+        ctx.meta = (S, NB, E, V, ld)
+        ctx.save_for_backward(x2)
+        return buf[:, :V].view(S, NB, V).permute(1, 0, 2)
+
+    @staticmethod
+    def backward(ctx, dlogits: Tensor):  # type: ignore[override]
+        module: FusedDecoder = ctx.module
+        S, NB, E, V, ld = ctx.meta
+        T = S * NB
+        (x2,) = ctx.saved_tensors
+        buf = torch.zeros((T, ld), dtype=torch.bfloat16, device=x2.device)
+        buf[:, :V].view(S, NB, V).copy_(dlogits.permute(1, 0, 2))
+        dl = buf[:, :V]
+        _, w16t = module._sh("dec")
+        dx = gemm_nt(w16t[:, :V], dl, transpose_out=True)
+        F2.transpose_multi(module._lg("dec").jobs(x2, dl))
+        return (dx.view(S, NB, E), None) + (None,) * (len(ctx.needs_input_grad) - 2)
+
+
+class _DecoderLossFn(torch.autograd.Function):
+    """Vocabulary projection fused with softmax cross-entropy: returns the summed
+    loss of each sequence, ``[N]`` fp32.  The bf16 logits live only in a scratch
+    buffer that the backward turns into dlogits in place."""
+
+    @staticmethod
+    def forward(ctx, x: Tensor, targets: Tensor, module: "FusedDecoder", *params: Tensor) -> Tensor:  # type: ignore[override]
+        S, NB, E = x.shape
+        T = S * NB
+        x2 = x.contiguous().view(T, E)
+        if x2.dtype != torch.bfloat16:
+            x2 = x2.to(torch.bfloat16)
+        V = module.ntoken
+        ld = _round_up(V, 64)
+        w16, _ = module._sh("dec")
+        buf = torch.empty((T, ld), dtype=torch.bfloat16, device=x.device)
+        gemm_nt(w16, x2, out=buf[:, :V], transpose_out=True, bias=module.decoder.bias, bias_along_m=True)
+        tgt_rows = targets.t().contiguous().view(-1)            # row = s * NB + n
+        loss_rows = F2.cross_entropy(buf, tgt_rows, V, write_grad=False)
+        ctx.module = module
+        ctx.meta = (S, NB, E, V)
+        ctx.save_for_backward(x2, buf, tgt_rows)
+        return loss_rows.view(S, NB).sum(0)
+
+    @staticmethod
+    def backward(ctx, g: Tensor):  # type: ignore[override]
+        module: FusedDecoder = ctx.module
+        S, NB, E, V = ctx.meta
+        x2, buf, tgt_rows = ctx.saved_tensors
+        row_scale = g.float().contiguous().repeat(S)
+        F2.cross_entropy(buf, tgt_rows, V, write_grad=True, row_scale=row_scale, want_loss=False)
+        dl = buf[:, :V]
+        _, w16t = module._sh("dec")
+        dx = gemm_nt(w16t[:, :V], dl, transpose_out=True)
+        F2.transpose_multi(module._lg("dec").jobs(x2, dl))
+        return (dx.view(S, NB, E), None, None) + (None,) * (len(ctx.needs_input_grad) - 3)
+
+
+class FusedDecoder(_FusedBase):
+    """``(S, N, E)`` -> batch-first logits ``(N, S, V)`` (reference ``main.py:42-55``).
+    Called with a second input ``targets (N, S)`` it instead returns each sequence's
+    summed cross-entropy ``[N]`` with the loss fused behind the projection (the
+    logits are never handed to PyTorch)."""
+
+    def __init__(self, ntoken: int, ninp: int):
+        super().__init__()
+        self.ntoken = ntoken
+        self.decoder = _Linear(ninp, ntoken)
+        nn.init.zeros_(self.decoder.bias)
+        nn.init.uniform_(self.decoder.weight, -0.1, 0.1)
+        self._rebind()
+
+    def _rebind(self) -> None:
+        if not hasattr(self, "decoder"):
+            return
+        self._register_linear("dec", self.decoder.weight, self.decoder.bias)
+
+    def forward(self, inp: Tensor, targets: Optional[Tensor] = None):
+        if targets is None:
+            return _DecoderFn.apply(inp, self, *self.parameters())
+        return _DecoderLossFn.apply(inp, targets, self, *self.parameters())

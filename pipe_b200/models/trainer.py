@@ -105,8 +105,7 @@ class LMTrainer:
             self.rank, self.world = 0, 1
             devices = list(range(n_stages))
             model = build_stages(cfg, devices, impl, seed=seed)
-            if not (impl == "eager" and precision != "bf16"):
-                model = nn.Sequential(*[self._wrap(stage) for stage in model])
+            model = nn.Sequential(*[self._wrap(stage) for stage in model])
             self.pipe = Pipe(model, chunks=self.chunks, checkpoint=checkpoint)
             self.first_device = self.pipe.devices[0]
             self.last_device = self.pipe.devices[-1]
@@ -136,9 +135,15 @@ class LMTrainer:
 
     # -- one training step -------------------------------------------------------
     def step(self, tokens: Optional[Tensor], targets: Optional[Tensor]) -> Optional[Tensor]:
-        """``tokens``: ``(N, S)`` int64 on the first stage's device (first rank);
-        ``targets``: ``(N*S,)`` int64 on the last stage's device (last rank).
-        Returns the loss tensor on the last stage (``None`` elsewhere)."""
+        """``tokens``: ``(N, S)`` int64 on the first stage's device (first rank).
+        ``targets``: ``(N*S,)`` int64, batch-major like the gathered logits.  The eager
+        arm wants them on the *last* stage's device (last rank), as in the reference
+        (``main.py:217``); the fused arm feeds them through the pipe next to the
+        tokens (first stage's device / first rank) so that the last stage can fuse the
+        loss behind the vocabulary projection.  Returns the mean loss on the last
+        stage (``None`` on other ranks)."""
+        if self.impl == "fused":
+            return self._step_fused(tokens, targets)
         V = self.cfg.ntokens
         self.opt.zero_grad(set_to_none=True)
         if self.distributed:
@@ -152,10 +157,25 @@ class LMTrainer:
             logits = self.pipe(tokens).local_value()
             loss = F.cross_entropy(logits.reshape(-1, V).float(), targets)
             loss.backward()
+        clip_grad_norm_(self.params, self.max_norm, distributed=self.distributed)
+        self.opt.step()
+        return loss
 
-        if self.impl == "fused":
-            self.opt.step()
+    def _step_fused(self, tokens: Optional[Tensor], targets: Optional[Tensor]) -> Optional[Tensor]:
+        cfg = self.cfg
+        self.opt.zero_grad()
+        loss = None
+        if self.distributed:
+            if self.is_first:
+                out = self.pipe(tokens, targets.view(cfg.batch, cfg.bptt))
+            else:
+                out = self.pipe()
+            if self.is_last:
+                loss = out.local_value().sum() / float(cfg.batch * cfg.bptt)
+            self.pipe.backward(loss)
         else:
-            clip_grad_norm_(self.params, self.max_norm, distributed=self.distributed)
-            self.opt.step()
+            per_seq = self.pipe(tokens, targets.view(cfg.batch, cfg.bptt)).local_value()
+            loss = per_seq.sum() / float(cfg.batch * cfg.bptt)
+            loss.backward()
+        self.opt.step()
         return loss

@@ -1,0 +1,196 @@
+"""Thin, shape-checked Python wrappers over the C entry points (no autograd here)."""
+from __future__ import annotations
+
+import ctypes
+from typing import List, Optional, Sequence, Tuple
+
+import torch
+from torch import Tensor
+
+from . import _lib
+from ._lib import ptr
+
+__all__ = ["add_layernorm_fwd", "add_layernorm_bwd", "embed_fwd", "embed_bwd", "cross_entropy",
+           "transpose_colsum", "transpose_multi", "sumsq", "attention_fwd", "attention_bwd", "draw_seed"]
+
+c_f = ctypes.c_float
+c_i = ctypes.c_int
+c_ll = ctypes.c_longlong
+c_ull = ctypes.c_ulonglong
+c_p = ctypes.c_void_p
+
+
+def draw_seed() -> int:
+    """A 63-bit seed from torch's *CPU* generator.  Checkpointing captures and
+    replays that generator, so a recompute draws the same seed and the Philox
+    dropout masks come out bit-identical."""
+    return int(torch.empty((), dtype=torch.int64).random_().item())
+
+
+def _s(t: Tensor) -> c_p:
+    return _lib.stream_ptr(t.device)
+
+
+def _bf16_rows(t: Tensor, E: int) -> None:
+    assert t.dtype == torch.bfloat16 and t.is_contiguous() and t.size(-1) == E, (t.dtype, t.shape, t.stride())
+
+
+def add_layernorm_fwd(x: Tensor, h: Optional[Tensor], gamma: Tensor, beta: Tensor, eps: float
+                      ) -> Tuple[Tensor, Tensor, Tensor]:
+    E = x.size(-1)
+    rows = x.numel() // E
+    _bf16_rows(x, E)
+    if h is not None:
+        _bf16_rows(h, E)
+    y = torch.empty_like(x)
+    mean = torch.empty(rows, dtype=torch.float32, device=x.device)
+    rstd = torch.empty(rows, dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        rc = _lib.load().pb2_add_layernorm_fwd(c_p(x.data_ptr()), c_p(ptr(h)), c_p(gamma.data_ptr()),
+                                               c_p(beta.data_ptr()), c_p(y.data_ptr()), c_p(mean.data_ptr()),
+                                               c_p(rstd.data_ptr()), c_i(rows), c_i(E), c_f(eps), _s(x))
+    _lib.check(rc, "pb2_add_layernorm_fwd")
+    return y, mean, rstd
+
+
+def add_layernorm_bwd(dy: Tensor, x: Tensor, h: Optional[Tensor], gamma: Tensor, mean: Tensor, rstd: Tensor,
+                      dgamma: Tensor, dbeta: Tensor, *, want_dh: bool, drop_p: float = 0.0, seed: int = 0,
+                      rng_stream: int = 0) -> Tuple[Tensor, Optional[Tensor]]:
+    E = x.size(-1)
+    rows = x.numel() // E
+    _bf16_rows(dy, E)
+    dres = torch.empty_like(x)
+    dh = torch.empty_like(x) if want_dh else None
+    assert dgamma.dtype == torch.float32 and dbeta.dtype == torch.float32
+    with torch.cuda.device(x.device):
+        rc = _lib.load().pb2_add_layernorm_bwd(c_p(dy.data_ptr()), c_p(x.data_ptr()), c_p(ptr(h)),
+                                               c_p(gamma.data_ptr()), c_p(mean.data_ptr()), c_p(rstd.data_ptr()),
+                                               c_p(dres.data_ptr()), c_p(ptr(dh)), c_p(dgamma.data_ptr()),
+                                               c_p(dbeta.data_ptr()), c_i(rows), c_i(E), c_f(drop_p), c_ull(seed),
+                                               c_ull(rng_stream), _s(x))
+    _lib.check(rc, "pb2_add_layernorm_bwd")
+    return dres, dh
+
+
+def embed_fwd(tokens: Tensor, weight: Tensor, pe: Tensor, scale: float, drop_p: float, seed: int,
+              rng_stream: int) -> Tensor:
+    assert tokens.dtype == torch.int64 and tokens.dim() == 2 and tokens.is_contiguous()
+    N, S = tokens.shape
+    E = weight.size(1)
+    assert weight.dtype == torch.float32 and weight.is_contiguous()
+    assert pe.dtype == torch.float32 and pe.is_contiguous() and pe.size(-1) == E and pe.numel() // E >= S
+    out = torch.empty((S, N, E), dtype=torch.bfloat16, device=tokens.device)
+    with torch.cuda.device(tokens.device):
+        rc = _lib.load().pb2_embed_fwd(c_p(tokens.data_ptr()), c_p(weight.data_ptr()), c_p(pe.data_ptr()),
+                                       c_p(out.data_ptr()), c_i(N), c_i(S), c_i(E), c_f(scale), c_f(drop_p),
+                                       c_ull(seed), c_ull(rng_stream), _s(tokens))
+    _lib.check(rc, "pb2_embed_fwd")
+    return out
+
+
+def embed_bwd(tokens: Tensor, dout: Tensor, dweight: Tensor, scale: float, drop_p: float, seed: int,
+              rng_stream: int) -> None:
+    N, S = tokens.shape
+    E = dweight.size(1)
+    assert dout.dtype == torch.bfloat16 and dout.is_contiguous() and dweight.dtype == torch.float32
+    with torch.cuda.device(tokens.device):
+        rc = _lib.load().pb2_embed_bwd(c_p(tokens.data_ptr()), c_p(dout.data_ptr()), c_p(dweight.data_ptr()),
+                                       c_i(N), c_i(S), c_i(E), c_f(scale), c_f(drop_p), c_ull(seed),
+                                       c_ull(rng_stream), _s(tokens))
+    _lib.check(rc, "pb2_embed_bwd")
+
+
+def cross_entropy(logits: Tensor, targets: Tensor, V: int, *, write_grad: bool,
+                  row_scale: Optional[Tensor] = None, want_loss: bool = True) -> Optional[Tensor]:
+    """Per-row losses for bf16 ``logits [rows, ld]``; with ``write_grad`` the
+    logits are overwritten by ``(softmax - onehot) * row_scale``."""
+    assert logits.dtype == torch.bfloat16 and logits.dim() == 2 and logits.stride(1) == 1
+    assert targets.dtype == torch.int64 and targets.is_contiguous() and targets.numel() == logits.size(0)
+    rows = logits.size(0)
+    loss = torch.empty(rows, dtype=torch.float32, device=logits.device) if want_loss else None
+    if row_scale is not None:
+        assert row_scale.dtype == torch.float32 and row_scale.is_contiguous() and row_scale.numel() == rows
+    with torch.cuda.device(logits.device):
+        rc = _lib.load().pb2_cross_entropy(c_p(logits.data_ptr()), c_p(targets.data_ptr()), c_p(ptr(loss)),
+                                           c_p(ptr(row_scale)), c_i(rows), c_i(V), c_ll(logits.stride(0)),
+                                           c_i(int(write_grad)), _s(logits))
+    _lib.check(rc, "pb2_cross_entropy")
+    return loss
+
+
+def transpose_colsum(src: Tensor, dst: Tensor, colsum: Optional[Tensor] = None, scale: float = 1.0) -> None:
+    """``dst[c, r] = src[r, c]``; ``dst`` is ``[C, ld]`` with ``ld >= R`` (zero-filled beyond R)."""
+    assert src.dtype == torch.bfloat16 and dst.dtype == torch.bfloat16 and src.dim() == 2 and dst.dim() == 2
+    R, C = src.shape
+    assert dst.size(0) == C and dst.stride(1) == 1 and src.stride(1) == 1
+    with torch.cuda.device(src.device):
+        rc = _lib.load().pb2_transpose_colsum(c_p(src.data_ptr()), c_ll(src.stride(0)), c_p(dst.data_ptr()),
+                                              c_ll(dst.stride(0)), c_i(R), c_i(C), c_p(ptr(colsum)), c_f(scale),
+                                              _s(src))
+    _lib.check(rc, "pb2_transpose_colsum")
+
+
+class _TransposeJob(ctypes.Structure):
+    _fields_ = [("src", c_p), ("dst", c_p), ("ld_src", c_ll), ("ld_dst", c_ll), ("R", c_i), ("C", c_i),
+                ("colsum", c_p), ("scale", c_f)]
+
+
+class _TransposeJobs(ctypes.Structure):
+    _fields_ = [("job", _TransposeJob * 8), ("count", c_i)]
+
+
+def transpose_multi(jobs: Sequence[Tuple[Tensor, Tensor, int, Optional[Tensor], float]]) -> None:
+    """Each job is ``(src [R, C], dst_base [C, ld], dst_col_offset, colsum or None, scale)``:
+    writes ``dst_base[c, off + r] = src[r, c]`` for all jobs in one launch."""
+    assert 0 < len(jobs) <= 8
+    packed = _TransposeJobs()
+    packed.count = len(jobs)
+    dev = jobs[0][0].device
+    for k, (src, dst, off, colsum, scale) in enumerate(jobs):
+        assert src.dtype == torch.bfloat16 and dst.dtype == torch.bfloat16 and src.stride(1) == 1 and dst.stride(1) == 1
+        R, C = src.shape
+        assert dst.size(0) == C and off + R <= dst.size(1), (src.shape, dst.shape, off)
+        j = packed.job[k]
+        j.src, j.dst = src.data_ptr(), dst.data_ptr() + off * 2
+        j.ld_src, j.ld_dst = src.stride(0), dst.stride(0)
+        j.R, j.C = R, C
+        j.colsum = ptr(colsum)
+        j.scale = scale
+    with torch.cuda.device(dev):
+        rc = _lib.load().pb2_transpose_multi(ctypes.byref(packed), _lib.stream_ptr(dev))
+    _lib.check(rc, "pb2_transpose_multi")
+
+
+def sumsq(x: Tensor, out: Tensor) -> None:
+    assert x.dtype == torch.float32 and x.is_contiguous() and out.dtype == torch.float32
+    with torch.cuda.device(x.device):
+        rc = _lib.load().pb2_sumsq(c_p(x.data_ptr()), ctypes.c_size_t(x.numel()), c_p(out.data_ptr()), _s(x))
+    _lib.check(rc, "pb2_sumsq")
+
+
+def attention_fwd(qkv: Tensor, NB: int, S: int, H: int, *, causal: bool, drop_p: float, seed: int,
+                  rng_stream: int) -> Tensor:
+    T, E3 = qkv.shape
+    E = E3 // 3
+    assert qkv.dtype == torch.bfloat16 and qkv.is_contiguous() and T == NB * S and E % H == 0
+    out = torch.empty((T, E), dtype=torch.bfloat16, device=qkv.device)
+    with torch.cuda.device(qkv.device):
+        rc = _lib.load().pb2_attention_fwd(c_p(qkv.data_ptr()), c_p(out.data_ptr()), c_i(NB), c_i(S), c_i(H),
+                                           c_i(E // H), c_i(int(causal)), c_f(drop_p), c_ull(seed),
+                                           c_ull(rng_stream), _s(qkv))
+    _lib.check(rc, "pb2_attention_fwd")
+    return out
+
+
+def attention_bwd(qkv: Tensor, dout: Tensor, NB: int, S: int, H: int, *, causal: bool, drop_p: float, seed: int,
+                  rng_stream: int) -> Tensor:
+    T, E3 = qkv.shape
+    E = E3 // 3
+    assert dout.dtype == torch.bfloat16 and dout.is_contiguous() and dout.shape == (T, E)
+    dqkv = torch.empty_like(qkv)
+    with torch.cuda.device(qkv.device):
+        rc = _lib.load().pb2_attention_bwd(c_p(qkv.data_ptr()), c_p(dout.data_ptr()), c_p(dqkv.data_ptr()), c_i(NB),
+                                           c_i(S), c_i(H), c_i(E // H), c_i(int(causal)), c_f(drop_p), c_ull(seed),
+                                           c_ull(rng_stream), _s(qkv))
+    _lib.check(rc, "pb2_attention_bwd")
+    return dqkv

@@ -1,0 +1,174 @@
+"""``FusedClipAdam``: global-norm clipping + Adam for every stage, one launch per device.
+
+What the reference does with three passes over the parameters
+(``clip_grad_norm_`` = norm pass + scale pass, then ``Adam.step``;
+``main.py:219-220``) is one kernel here (``csrc/optim.cu``): the squared gradient
+norm is already on the device when backward ends — the wgrad GEMM epilogues add
+their tiles' squares to a scalar, one small kernel covers biases / LayerNorm /
+embedding — and the Adam kernel derives the clip factor from that scalar itself,
+updates the fp32 master weights and moments, and rewrites the bf16 (and
+transposed bf16) shadows the GEMMs read.  No host synchronisation anywhere in
+the step.
+
+Gradient storage: matrix gradients are persistent fp32 buffers that the deferred
+wgrad GEMM *overwrites* once per step (no zeroing, no read-modify-write); all
+small gradients (biases, LayerNorm, embedding rows) live in one flat buffer per
+device that is cleared with one memset.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Dict, Iterable, List, Optional
+
+import numpy as np
+import torch
+import torch.distributed as dist
+from torch import Tensor, nn
+
+from . import _lib, wgrad
+from . import functional as F2
+
+__all__ = ["FusedClipAdam"]
+
+_DESC = np.dtype([("w", "<u8"), ("g", "<u8"), ("m", "<u8"), ("v", "<u8"), ("w16", "<u8"), ("w16t", "<u8"),
+                  ("rows", "<i4"), ("cols", "<i4"), ("ld_t", "<i4"), ("tile_start", "<i4")])
+assert _DESC.itemsize == 64
+
+
+class _DeviceState:
+    def __init__(self, device: torch.device) -> None:
+        self.device = device
+        self.params: List[nn.Parameter] = []
+        self.table: Optional[Tensor] = None
+        self.n_tensors = 0
+        self.total_tiles = 0
+        self.flat_small: Optional[Tensor] = None
+        self.normsq = torch.zeros((), dtype=torch.float32, device=device)
+        self.total_normsq = torch.zeros((), dtype=torch.float32, device=device)
+        self.keep: List[Tensor] = []
+
+
+class FusedClipAdam:
+    """Args mirror ``torch.optim.Adam`` plus ``max_norm`` (<= 0 disables clipping),
+    ``grad_scale`` (multiplies every gradient, e.g. ``1/replicas``) and
+    ``distributed`` (sum the squared norm over the ranks of ``group`` — one stage
+    per rank)."""
+
+    def __init__(self, module: nn.Module, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
+                 weight_decay: float = 0.0, max_norm: float = 0.0, grad_scale: float = 1.0,
+                 distributed: bool = False, group=None) -> None:
+        self.lr, self.betas, self.eps, self.weight_decay = lr, betas, eps, weight_decay
+        self.max_norm, self.grad_scale = max_norm, grad_scale
+        self.distributed, self.group = distributed, group
+        self.step_count = 0
+        self.module = module
+
+        shadows = {}
+        gemm_written = set()
+        for sub in module.modules():
+            for sh in getattr(sub, "pb2_shadows", lambda: [])():
+                shadows[id(sh.param)] = sh
+            for lg in getattr(sub, "pb2_linear_grads", lambda: [])():
+                gemm_written.add(id(lg.weight))
+        self._shadows = shadows
+
+        self.devs: Dict[torch.device, _DeviceState] = {}
+        seen = set()
+        for p in module.parameters():
+            if id(p) in seen or not p.requires_grad:
+                continue
+            seen.add(id(p))
+            if p.dtype != torch.float32 or not p.is_cuda:
+                raise TypeError("FusedClipAdam needs fp32 CUDA parameters (masters)")
+            st = self.devs.setdefault(p.device, _DeviceState(p.device))
+            st.params.append(p)
+
+        for st in self.devs.values():
+            small = [p for p in st.params if id(p) not in gemm_written]
+            n_small = sum((p.numel() + 3) // 4 * 4 for p in small)
+            st.flat_small = torch.zeros(max(n_small, 4), dtype=torch.float32, device=st.device)
+            at = 0
+            for p in small:
+                p.grad = st.flat_small[at:at + p.numel()].view_as(p)
+                at += (p.numel() + 3) // 4 * 4
+            rows_desc = np.zeros(len(st.params), dtype=_DESC)
+            tile = 0
+            for k, p in enumerate(st.params):
+                if id(p) in gemm_written:
+                    p.grad = torch.zeros_like(p)
+                    p._pb2_normsq = st.normsq
+                    p._pb2_fresh = True
+                    p._pb2_sumsq_done = False
+                m = torch.zeros_like(p)
+                v = torch.zeros_like(p)
+                st.keep += [m, v]
+                rows, cols = (p.shape[0], p.numel() // p.shape[0]) if p.dim() >= 2 else (1, p.numel())
+                d = rows_desc[k]
+                d["w"], d["g"], d["m"], d["v"] = p.data_ptr(), p.grad.data_ptr(), m.data_ptr(), v.data_ptr()
+                sh = shadows.get(id(p))
+                if sh is not None:
+                    sh.ensure()
+                    d["w16"], d["w16t"], d["ld_t"] = sh.w16.data_ptr(), sh.w16t.data_ptr(), sh.w16t.stride(0)
+                d["rows"], d["cols"], d["tile_start"] = rows, cols, tile
+                tile += ((rows + 31) // 32) * ((cols + 63) // 64)
+            st.table = torch.from_numpy(rows_desc.view(np.uint8).copy()).to(st.device)
+            st.n_tensors = len(st.params)
+            st.total_tiles = tile
+        self._gemm_written = gemm_written
+
+    # -- torch.optim-like surface --------------------------------------------------
+    def zero_grad(self, set_to_none: bool = True) -> None:
+        """Small gradients: one memset.  Matrix gradients: nothing — the next wgrad
+        GEMM overwrites them (``set_to_none`` is accepted for API compatibility;
+        buffers are always kept)."""
+        for st in self.devs.values():
+            st.flat_small.zero_()
+            st.normsq.zero_()
+            for p in st.params:
+                if id(p) in self._gemm_written:
+                    p._pb2_fresh = True
+                    p._pb2_sumsq_done = False
+
+    def _total_normsq(self) -> None:
+        """Finish the squared norm on every device, then share the total."""
+        for st in self.devs.values():
+            with torch.cuda.device(st.device):
+                F2.sumsq(st.flat_small, st.normsq)
+                for p in st.params:
+                    if id(p) in self._gemm_written and not getattr(p, "_pb2_sumsq_done", False):
+                        F2.sumsq(p.grad.view(-1), st.normsq)
+        states = list(self.devs.values())
+        first = states[0]
+        total = first.total_normsq
+        total.copy_(first.normsq)
+        for st in states[1:]:
+            total.add_(st.normsq.to(first.device, non_blocking=True))
+        if self.distributed:
+            dist.all_reduce(total, group=self.group)
+        for st in states[1:]:
+            st.total_normsq.copy_(total, non_blocking=True)
+
+    @torch.no_grad()
+    def step(self) -> None:
+        wgrad.flush_pending()
+        self.step_count += 1
+        if self.max_norm > 0:
+            self._total_normsq()
+        lib = _lib.load()
+        for st in self.devs.values():
+            with torch.cuda.device(st.device):
+                rc = lib.pb2_adam_step(ctypes.c_void_p(st.table.data_ptr()), ctypes.c_int(st.n_tensors),
+                                       ctypes.c_int(st.total_tiles), ctypes.c_void_p(st.total_normsq.data_ptr()),
+                                       ctypes.c_float(self.lr), ctypes.c_float(self.betas[0]),
+                                       ctypes.c_float(self.betas[1]), ctypes.c_float(self.eps),
+                                       ctypes.c_float(self.weight_decay), ctypes.c_int(self.step_count),
+                                       ctypes.c_float(self.max_norm), ctypes.c_float(self.grad_scale),
+                                       _lib.stream_ptr(st.device))
+            _lib.check(rc, "pb2_adam_step")
+        for sh in self._shadows.values():
+            sh.mark_synced()
+
+    def grad_norm(self) -> float:
+        """The global gradient norm used by the last ``step`` (synchronises)."""
+        first = next(iter(self.devs.values()))
+        return float(first.total_normsq.sqrt().item()) * self.grad_scale

@@ -1,0 +1,148 @@
+"""Deferred weight gradients: one wgrad GEMM per Linear per mini-batch.
+
+A pipeline runs every Linear ``m`` times per step, once per micro-batch, with
+25-128 tokens each.  Computing ``dW += dY_i^T X_i`` per micro-batch would
+read-modify-write the whole fp32 ``dW`` ``m`` times (8 bytes/param each) — more
+HBM traffic than the forward and dgrad weight reads put together.  Instead each
+backward only *stacks* its operands: ``X_i`` and ``dY_i`` are transposed into
+column blocks of two persistent K-major buffers ``X^T [in, tokens]`` and
+``dY^T [out, tokens]`` (one fused multi-transpose launch per layer, which also
+column-sums ``dY`` into the bias gradient).  When the backward pass ends, a single
+tcgen05 GEMM with K = all tokens of the mini-batch writes ``dW`` once (and folds
+its squared norm into the clip scalar).  Same math up to fp32 reassociation
+(SURVEY.md §7.4 item 1).
+
+Flush points: automatically at the end of the autograd pass that stacked
+something (engine callback), or — inside ``with deferred():`` — when the block
+exits (``DistPipe.backward`` runs one engine pass per micro-batch and flushes
+once at its end).
+"""
+from __future__ import annotations
+
+import threading
+from contextlib import contextmanager
+from typing import Dict, Iterator, List, Optional, Set, Tuple
+
+import torch
+from torch import Tensor, nn
+
+from .gemm import gemm_nt
+
+__all__ = ["LinearGrad", "deferred", "flush_pending", "ensure_grad"]
+
+_lock = threading.RLock()
+_pending: "Dict[int, LinearGrad]" = {}
+_defer_depth = 0
+_callback_queued = False
+
+
+def ensure_grad(p: nn.Parameter) -> Tensor:
+    """``p.grad`` as a zero-initialised fp32 buffer if it does not exist yet."""
+    if p.grad is None:
+        p.grad = torch.zeros_like(p, memory_format=torch.contiguous_format)
+    return p.grad
+
+
+class LinearGrad:
+    """Stacked operands and the deferred wgrad GEMM of one weight ``[out, in]``."""
+
+    def __init__(self, weight: nn.Parameter, bias: Optional[nn.Parameter]) -> None:
+        self.weight = weight
+        self.bias = bias
+        self.xt: Optional[Tensor] = None      # [in, cap]  bf16
+        self.dyt: Optional[Tensor] = None     # [out, cap] bf16
+        self.used = 0
+        self.stream: Optional[torch.cuda.Stream] = None
+
+    def _reserve(self, tokens: int) -> int:
+        out_f, in_f = self.weight.shape
+        need = self.used + tokens
+        cap = 0 if self.xt is None else self.xt.size(1)
+        if need > cap or self.xt.device != self.weight.device:
+            new_cap = max(64, cap)
+            while new_cap < need:
+                new_cap *= 2
+            dev = self.weight.device
+            xt = torch.zeros((in_f, new_cap), dtype=torch.bfloat16, device=dev)
+            dyt = torch.zeros((out_f, new_cap), dtype=torch.bfloat16, device=dev)
+            if self.used:
+                xt[:, : self.used].copy_(self.xt[:, : self.used])
+                dyt[:, : self.used].copy_(self.dyt[:, : self.used])
+            self.xt, self.dyt = xt, dyt
+        off = self.used
+        self.used = need
+        return off
+
+    def jobs(self, x: Tensor, dy: Tensor) -> List[Tuple[Tensor, Tensor, int, Optional[Tensor], float]]:
+        """Reserve a column block for one micro-batch and return the two transpose
+        jobs that fill it (``dy``'s job also accumulates the bias gradient)."""
+        tokens = x.size(0)
+        assert dy.size(0) == tokens
+        with _lock:
+            off = self._reserve(tokens)
+            self.stream = torch.cuda.current_stream(x.device)
+            _pending[id(self)] = self
+            _arm()
+        bias_grad = ensure_grad(self.bias) if self.bias is not None else None
+        return [(x, self.xt, off, None, 1.0), (dy, self.dyt, off, bias_grad, 1.0)]
+
+    def flush(self) -> None:
+        if not self.used:
+            return
+        w = self.weight
+        grad = ensure_grad(w)
+        fresh = getattr(w, "_pb2_fresh", False)
+        normsq = getattr(w, "_pb2_normsq", None) if fresh else None
+        with torch.cuda.stream(self.stream):
+            gemm_nt(self.dyt[:, : self.used], self.xt[:, : self.used], out=grad, accumulate=not fresh,
+                    sumsq=normsq)
+        if fresh:
+            w._pb2_fresh = False
+            w._pb2_sumsq_done = normsq is not None
+        self.used = 0
+
+
+def _arm() -> None:
+    """Make sure something will flush: queue an engine callback unless an outer
+    ``deferred()`` block owns the flush."""
+    global _callback_queued
+    if _defer_depth > 0 or _callback_queued:
+        return
+    try:
+        torch.autograd.Variable._execution_engine.queue_callback(_engine_done)
+        _callback_queued = True
+    except RuntimeError:
+        # not inside a backward pass (direct call): the caller flushes explicitly
+        pass
+
+
+def _engine_done() -> None:
+    global _callback_queued
+    with _lock:
+        _callback_queued = False
+    flush_pending()
+
+
+def flush_pending() -> None:
+    """Run the deferred wgrad GEMM of every Linear that stacked operands."""
+    with _lock:
+        todo = list(_pending.values())
+        _pending.clear()
+    for lg in todo:
+        lg.flush()
+
+
+@contextmanager
+def deferred() -> Iterator[None]:
+    """Hold all wgrad flushes until the block exits (nestable)."""
+    global _defer_depth
+    with _lock:
+        _defer_depth += 1
+    try:
+        yield
+    finally:
+        with _lock:
+            _defer_depth -= 1
+            last = _defer_depth == 0
+        if last:
+            flush_pending()

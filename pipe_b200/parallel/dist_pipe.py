@@ -318,6 +318,11 @@ class DistPipe(nn.Module):
     def backward(self, loss: Optional[Tensor] = None) -> None:
         """Run the backward half.  On the last stage pass the loss computed from
         ``forward``'s output; elsewhere pass nothing."""
+        from ..ops import wgrad          # pure-Python bookkeeping; no GPU needed to import
+        with wgrad.deferred():           # one wgrad GEMM per Linear for the whole mini-batch
+            self._backward(loss)
+
+    def _backward(self, loss: Optional[Tensor]) -> None:
         cells = self._cells
         if self.is_last:
             if loss is None:

@@ -1,0 +1,146 @@
+"""Fused modules vs their stock torch.nn counterparts (same weights), alone and inside Pipe."""
+import copy
+
+import pytest
+import torch
+import torch.nn.functional as F
+from torch import nn
+
+pytestmark = pytest.mark.gpu
+dev = "cuda"
+
+
+def rel(got, want):
+    got, want = got.float(), want.float()
+    return ((got - want).norm() / (want.norm() + 1e-12)).item()
+
+
+def test_encoder_layer_matches_torch_layer():
+    from pipe_b200.models.fused import FusedEncoderLayer
+    from pipe_b200.ops import wgrad
+    torch.manual_seed(0)
+    E, H, FF, S, NB = 512, 8, 1024, 25, 3
+    ref = nn.TransformerEncoderLayer(E, H, FF, 0.0).to(dev)
+    fused = FusedEncoderLayer(E, H, FF, 0.0).to(dev)
+    fused.load_state_dict(ref.state_dict())                    # same parameter names
+    x = torch.randn(S, NB, E, device=dev)
+    xr = x.clone().requires_grad_()
+    xf = x.bfloat16().requires_grad_()
+    yr = ref(xr)
+    yf = fused(xf)
+    assert yf.shape == yr.shape and yf.dtype == torch.bfloat16
+    assert rel(yf, yr) < 2e-2
+    g = torch.randn_like(yr)
+    yr.backward(g)
+    yf.backward(g.bfloat16())
+    wgrad.flush_pending()
+    assert rel(xf.grad, xr.grad) < 4e-2
+    for (name, pf), pr in zip(fused.named_parameters(), ref.parameters()):
+        assert pf.grad is not None, name
+        assert rel(pf.grad, pr.grad) < 5e-2, (name, rel(pf.grad, pr.grad))
+
+
+def test_causal_flag():
+    from pipe_b200.models.fused import FusedEncoderLayer
+    torch.manual_seed(0)
+    E, H, S, NB = 256, 4, 16, 2
+    ref = nn.TransformerEncoderLayer(E, H, 512, 0.0).to(dev)
+    fused = FusedEncoderLayer(E, H, 512, 0.0, causal=True).to(dev)
+    fused.load_state_dict(ref.state_dict())
+    x = torch.randn(S, NB, E, device=dev)
+    mask = nn.Transformer.generate_square_subsequent_mask(S, device=dev)
+    assert rel(fused(x.bfloat16()), ref(x, src_mask=mask)) < 2e-2
+
+
+def _tiny_cfg(dropout):
+    from pipe_b200.models import TransformerConfig
+    return TransformerConfig(ntokens=1000, emsize=256, nhid=512, nlayers=2, nhead=4, dropout=dropout,
+                             bptt=25, batch=20, chunks=8)
+
+
+def test_full_model_in_pipe_matches_eager_model():
+    from pipe_b200 import Pipe
+    from pipe_b200.models import build_stages
+    cfg = _tiny_cfg(0.0)
+    eager = build_stages(cfg, [0], impl="eager")
+    fused = build_stages(cfg, [0], impl="fused")
+    fused.load_state_dict(eager.state_dict())
+    tokens = torch.randint(0, cfg.ntokens, (cfg.batch, cfg.bptt), device=dev)
+    targets = torch.randint(0, cfg.ntokens, (cfg.batch, cfg.bptt), device=dev)
+
+    want = eager(tokens)
+    loss_ref = F.cross_entropy(want.reshape(-1, cfg.ntokens), targets.reshape(-1))
+    loss_ref.backward()
+
+    pipe = Pipe(fused, chunks=cfg.chunks, checkpoint="never")
+    # (a) logits path: API parity with the reference's Decoder
+    got = pipe(tokens).local_value()
+    assert got.shape == want.shape
+    assert rel(got, want) < 3e-2
+    # (b) fused-loss path: targets ride through the pipe
+    per_seq = pipe(tokens, targets).local_value()
+    assert per_seq.shape == (cfg.batch,)
+    loss = per_seq.sum() / (cfg.batch * cfg.bptt)
+    assert abs(loss.item() - loss_ref.item()) < 2e-2 * abs(loss_ref.item())
+    loss.backward()
+    for (name, pf), pr in zip(pipe.named_parameters(), eager.parameters()):
+        assert pf.grad is not None, name
+        assert rel(pf.grad, pr.grad) < 8e-2, (name, rel(pf.grad, pr.grad))
+
+
+def test_logits_path_backward():
+    from pipe_b200 import Pipe
+    from pipe_b200.models import build_stages
+    cfg = _tiny_cfg(0.0)
+    eager = build_stages(cfg, [0], impl="eager")
+    fused = build_stages(cfg, [0], impl="fused")
+    fused.load_state_dict(eager.state_dict())
+    tokens = torch.randint(0, cfg.ntokens, (cfg.batch, cfg.bptt), device=dev)
+    targets = torch.randint(0, cfg.ntokens, (cfg.batch * cfg.bptt,), device=dev)
+    F.cross_entropy(eager(tokens).reshape(-1, cfg.ntokens), targets).backward()
+    pipe = Pipe(fused, chunks=4, checkpoint="except_last")
+    out = pipe(tokens).local_value()
+    F.cross_entropy(out.reshape(-1, cfg.ntokens).float(), targets).backward()
+    for (name, pf), pr in zip(pipe.named_parameters(), eager.parameters()):
+        assert rel(pf.grad, pr.grad) < 8e-2, (name, rel(pf.grad, pr.grad))
+
+
+def test_dropout_recompute_is_bit_identical():
+    """checkpoint='always' must reproduce the 'never' gradients with dropout on: the Philox seeds
+    come from the CPU generator that checkpointing captures and replays."""
+    from pipe_b200 import Pipe
+    from pipe_b200.models import build_stages
+    cfg = _tiny_cfg(0.2)
+    grads = {}
+    for mode in ("never", "always"):
+        model = build_stages(cfg, [0], impl="fused", seed=3)
+        pipe = Pipe(model, chunks=4, checkpoint=mode)
+        torch.manual_seed(123)
+        tokens = torch.randint(0, cfg.ntokens, (cfg.batch, cfg.bptt), device=dev)
+        targets = torch.randint(0, cfg.ntokens, (cfg.batch, cfg.bptt), device=dev)
+        per_seq = pipe(tokens, targets).local_value()
+        (per_seq.sum() / 500).backward()
+        grads[mode] = {n: p.grad.clone() for n, p in pipe.named_parameters()}
+    for n in grads["never"]:
+        assert rel(grads["always"][n], grads["never"][n]) < 1e-3, n       # atomics reorder sums; masks identical
+
+
+def test_training_reduces_loss_with_fused_optimizer():
+    from pipe_b200.models.trainer import LMTrainer
+    cfg = _tiny_cfg(0.1)
+    tr = LMTrainer(cfg, n_stages=1, impl="fused", checkpoint="except_last", lr=2e-3)
+    tokens = torch.randint(0, cfg.ntokens, (cfg.batch, cfg.bptt), device=dev)
+    targets = torch.randint(0, cfg.ntokens, (cfg.batch * cfg.bptt,), device=dev)
+    losses = [tr.step(tokens, targets).item() for _ in range(12)]
+    assert all(l == l for l in losses)
+    assert losses[-1] < losses[0] - 0.3, losses
+
+
+def test_state_dict_moves_between_eager_and_fused():
+    from pipe_b200.models import build_stages
+    cfg = _tiny_cfg(0.0)
+    eager = build_stages(cfg, [0], impl="eager")
+    fused = build_stages(cfg, [0], impl="fused")
+    assert list(eager.state_dict().keys()) == list(fused.state_dict().keys())
+    fused.load_state_dict(eager.state_dict())
+    eager.load_state_dict(fused.state_dict())

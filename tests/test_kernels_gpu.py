@@ -1,0 +1,196 @@
+"""Every non-GEMM kernel vs a plain fp32 PyTorch reference of the same op."""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+from torch import nn
+
+pytestmark = pytest.mark.gpu
+
+dev = "cuda"
+
+
+def close(got, want, tol=2e-2):
+    got, want = got.float(), want.float()
+    scale = max(want.abs().max().item(), 1e-6)
+    err = (got - want).abs().max().item()
+    assert err <= tol * scale, f"max err {err} vs scale {scale}"
+
+
+@pytest.mark.parametrize("rows,E", [(75, 4096), (50, 8192), (7, 64), (3, 1000)])
+def test_add_layernorm_fwd_bwd(rows, E):
+    from pipe_b200.ops import functional as F2
+    x = torch.randn(rows, E, device=dev).bfloat16()
+    h = torch.randn(rows, E, device=dev).bfloat16()
+    gamma = torch.rand(E, device=dev) + 0.5
+    beta = torch.randn(E, device=dev)
+    y, mean, rstd = F2.add_layernorm_fwd(x, h, gamma, beta, 1e-5)
+    z = (x.float() + h.float()).requires_grad_()
+    want = F.layer_norm(z, (E,), gamma, beta, 1e-5)
+    close(y, want)
+    dy = torch.randn(rows, E, device=dev).bfloat16()
+    g_ref = gamma.clone().requires_grad_()
+    b_ref = beta.clone().requires_grad_()
+    F.layer_norm(z, (E,), g_ref, b_ref, 1e-5).backward(dy.float())
+    dgamma = torch.zeros(E, device=dev)
+    dbeta = torch.zeros(E, device=dev)
+    dres, dh = F2.add_layernorm_bwd(dy, x, h, gamma, mean, rstd, dgamma, dbeta, want_dh=True)
+    close(dres, z.grad)
+    close(dh, z.grad)                       # p = 0: identical to the residual gradient
+    close(dgamma, g_ref.grad)
+    close(dbeta, b_ref.grad)
+    # plain LayerNorm (no residual operand)
+    y2, _, _ = F2.add_layernorm_fwd(x, None, gamma, beta, 1e-5)
+    close(y2, F.layer_norm(x.float(), (E,), gamma, beta, 1e-5))
+
+
+def test_layernorm_bwd_regenerates_the_gemm_dropout_mask():
+    from pipe_b200.ops import functional as F2
+    from pipe_b200.ops.gemm import linear_forward
+    T, E, p = 64, 512, 0.3
+    a = torch.randn(T, 256, device=dev).bfloat16()
+    w = torch.randn(E, 256, device=dev).bfloat16()
+    h = linear_forward(a, w, drop_p=p, seed=77, rng_stream=5)       # dropped-out sub-layer output
+    x = torch.randn(T, E, device=dev).bfloat16()
+    gamma, beta = torch.ones(E, device=dev), torch.zeros(E, device=dev)
+    y, mean, rstd = F2.add_layernorm_fwd(x, h, gamma, beta, 1e-5)
+    dy = torch.randn(T, E, device=dev).bfloat16()
+    dres, dh = F2.add_layernorm_bwd(dy, x, h, gamma, mean, rstd, torch.zeros(E, device=dev),
+                                    torch.zeros(E, device=dev), want_dh=True, drop_p=p, seed=77, rng_stream=5)
+    dropped = h == 0
+    assert 0.25 < dropped.float().mean().item() < 0.35
+    assert torch.all(dh[dropped] == 0)
+    close(dh[~dropped], dres[~dropped].float() / (1 - p))
+
+
+def test_embedding_fwd_bwd():
+    from pipe_b200.ops import functional as F2
+    N, S, E, V = 3, 25, 256, 1000
+    tok = torch.randint(0, V, (N, S), device=dev)
+    w = torch.randn(V, E, device=dev)
+    pe = torch.randn(64, 1, E, device=dev)
+    out = F2.embed_fwd(tok, w, pe, math.sqrt(E), 0.0, 0, 0)
+    want = w[tok.t()] * math.sqrt(E) + pe[:S]
+    assert out.shape == (S, N, E)
+    close(out, want)
+    dout = torch.randn(S, N, E, device=dev).bfloat16()
+    dw = torch.zeros(V, E, device=dev)
+    F2.embed_bwd(tok, dout, dw, math.sqrt(E), 0.0, 0, 0)
+    wr = w.clone().requires_grad_()
+    (wr[tok.t()] * math.sqrt(E)).backward(dout.float())
+    close(dw, wr.grad)
+    # dropout: deterministic, right rate, backward uses the same mask
+    a = F2.embed_fwd(tok, w, pe, 1.0, 0.5, 9, 1)
+    b = F2.embed_fwd(tok, w, pe, 1.0, 0.5, 9, 1)
+    assert torch.equal(a, b) and 0.45 < (a == 0).float().mean().item() < 0.55
+
+
+@pytest.mark.parametrize("rows,V", [(75, 28782), (8, 1000)])
+def test_cross_entropy(rows, V):
+    from pipe_b200.ops import functional as F2
+    ld = (V + 63) // 64 * 64
+    buf = torch.zeros(rows, ld, device=dev, dtype=torch.bfloat16)
+    buf[:, :V] = torch.randn(rows, V, device=dev) * 3
+    tgt = torch.randint(0, V, (rows,), device=dev)
+    ref_in = buf[:, :V].float().requires_grad_()
+    want = F.cross_entropy(ref_in, tgt, reduction="none")
+    loss = F2.cross_entropy(buf, tgt, V, write_grad=False)
+    close(loss, want, 1e-3)
+    scale = torch.rand(rows, device=dev) + 0.5
+    (want * scale).sum().backward()
+    F2.cross_entropy(buf, tgt, V, write_grad=True, row_scale=scale, want_loss=False)
+    close(buf[:, :V], ref_in.grad, 2e-2)
+    assert torch.all(buf[:, V:] == 0)
+
+
+def test_transpose_colsum_and_multi():
+    from pipe_b200.ops import functional as F2
+    src = torch.randn(75, 300, device=dev).bfloat16()
+    dst = torch.full((300, 128), 7.0, device=dev, dtype=torch.bfloat16)
+    cs = torch.zeros(300, device=dev)
+    F2.transpose_colsum(src, dst, cs, 2.0)
+    assert torch.equal(dst[:, :75], src.t()) and torch.all(dst[:, 75:] == 0)
+    close(cs, src.float().sum(0) * 2.0, 1e-2)
+    a = torch.randn(50, 64, device=dev).bfloat16()
+    b = torch.randn(50, 200, device=dev).bfloat16()
+    da = torch.zeros(64, 128, device=dev, dtype=torch.bfloat16)
+    db = torch.zeros(200, 128, device=dev, dtype=torch.bfloat16)
+    csb = torch.zeros(200, device=dev)
+    F2.transpose_multi([(a, da, 10, None, 1.0), (b, db, 10, csb, 1.0)])
+    assert torch.equal(da[:, 10:60], a.t()) and torch.equal(db[:, 10:60], b.t())
+    assert torch.all(da[:, :10] == 0) and torch.all(db[:, 60:] == 0)
+    close(csb, b.float().sum(0), 1e-2)
+
+
+def test_sumsq():
+    from pipe_b200.ops import functional as F2
+    for n in (5, 4096, 1_000_003):
+        x = torch.randn(n + 4, device=dev)[:n]
+        x = x.contiguous()
+        out = torch.zeros((), device=dev)
+        F2.sumsq(x, out)
+        want = (x.double() ** 2).sum().item()
+        assert abs(out.item() - want) / want < 1e-4
+
+
+@pytest.mark.parametrize("NB,S,H,D,causal", [(3, 25, 16, 256, False), (2, 25, 4, 64, True), (2, 128, 2, 64, False),
+                                             (1, 25, 64, 128, False)])
+def test_attention_fwd_bwd(NB, S, H, D, causal):
+    from pipe_b200.ops import functional as F2
+    E = H * D
+    qkv = (torch.randn(S * NB, 3 * E, device=dev) * 0.5).bfloat16()
+    out = F2.attention_fwd(qkv, NB, S, H, causal=causal, drop_p=0.0, seed=0, rng_stream=0)
+
+    ref = qkv.float().requires_grad_()
+    t = ref.view(S, NB, 3, H, D)
+    q, k, v = (t[:, :, i].permute(1, 2, 0, 3) for i in range(3))          # (NB, H, S, D)
+    o = F.scaled_dot_product_attention(q, k, v, is_causal=causal)
+    want = o.permute(2, 0, 1, 3).reshape(S * NB, E)
+    close(out, want)
+    dout = torch.randn(S * NB, E, device=dev).bfloat16()
+    want.backward(dout.float())
+    dqkv = F2.attention_bwd(qkv, dout, NB, S, H, causal=causal, drop_p=0.0, seed=0, rng_stream=0)
+    close(dqkv, ref.grad, 3e-2)
+
+
+def test_attention_dropout_consistent_between_fwd_and_bwd():
+    """Finite-difference-free check: with dropout on, d(sum(out * g))/dV computed by the backward
+    kernel must match the closed form P_drop^T g, where P_drop is recovered from a forward with V = I."""
+    from pipe_b200.ops import functional as F2
+    NB, S, H, D, p = 1, 16, 1, 16, 0.5
+    E = H * D
+    qkv = torch.zeros(S * NB, 3 * E, device=dev)
+    qkv[:, :2 * E] = torch.randn(S, 2 * E, device=dev)
+    qkv[:, 2 * E:] = torch.eye(S, D, device=dev)              # V = I  ->  out = P_drop
+    qkv = qkv.bfloat16()
+    pd = F2.attention_fwd(qkv, NB, S, H, causal=False, drop_p=p, seed=5, rng_stream=2).float()
+    assert 0.3 < (pd == 0).float().mean().item() < 0.7
+    g = torch.randn(S, E, device=dev).bfloat16()
+    dqkv = F2.attention_bwd(qkv, g, NB, S, H, causal=False, drop_p=p, seed=5, rng_stream=2)
+    close(dqkv[:, 2 * E:], pd.t() @ g.float(), 3e-2)
+
+
+def test_fused_clip_adam_matches_torch():
+    from pipe_b200.models.fused import FusedEncoderLayer
+    from pipe_b200.ops.optim import FusedClipAdam
+    torch.manual_seed(0)
+    layer = FusedEncoderLayer(256, 4, 512, 0.0).to(dev)
+    ref = [p.detach().clone().requires_grad_() for p in layer.parameters()]
+    opt = FusedClipAdam(layer, lr=1e-2, max_norm=0.5)
+    ropt = torch.optim.Adam(ref, lr=1e-2)
+    for step in range(3):
+        opt.zero_grad()
+        for p, r in zip(layer.parameters(), ref):
+            g = torch.randn_like(p)
+            p.grad.copy_(g)
+            r.grad = g.clone()
+        torch.nn.utils.clip_grad_norm_(ref, 0.5)
+        ropt.step()
+        opt.step()
+        for (name, p), r in zip(layer.named_parameters(), ref):
+            assert torch.allclose(p, r, rtol=1e-4, atol=1e-5), (step, name, (p - r).abs().max().item())
+    # shadows follow the masters
+    for sh in layer.pb2_shadows():
+        assert torch.equal(sh.w16, sh.param.detach().bfloat16())
+        assert torch.equal(sh.w16t[:, : sh.param.size(0)], sh.param.detach().t().bfloat16())
