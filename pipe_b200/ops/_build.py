@@ -70,7 +70,10 @@ def build(force: bool = False, verbose: bool = False) -> str:
         list(pool.map(run, jobs))
 
     if jobs or not os.path.exists(LIB):
-        run([nvcc, "-shared", "-o", LIB, *objs, "-gencode", "arch=compute_100a,code=sm_100a", "-lcudart"])
+        # --cudart shared: use the one libcudart.so.12 already in the process (torch's) instead of
+        # embedding a second, static runtime whose teardown order at exit is undefined
+        run([nvcc, "-shared", "--cudart", "shared", "-o", LIB, *objs,
+             "-gencode", "arch=compute_100a,code=sm_100a"])
     return LIB
 
 

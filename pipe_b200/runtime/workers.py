@@ -14,8 +14,10 @@ SURVEY.md A2.
 """
 from __future__ import annotations
 
+import atexit
 import sys
 import threading
+import weakref
 from queue import Queue
 from types import TracebackType
 from typing import Callable, Dict, List, Optional, Tuple, Type, Union
@@ -82,6 +84,19 @@ def _normalize(device: torch.device) -> torch.device:
     return device
 
 
+_live_pools: "weakref.WeakSet[WorkerPool]" = weakref.WeakSet()
+
+
+@atexit.register
+def _close_all_pools() -> None:
+    # Stop worker threads before the interpreter (and the CUDA runtime) tear down.
+    for pool in list(_live_pools):
+        try:
+            pool.close(timeout=2.0)
+        except Exception:
+            pass
+
+
 class WorkerPool:
     """Owns the threads; exposes per-*stage* queue lists (aliased when stages
     share a device)."""
@@ -107,6 +122,7 @@ class WorkerPool:
                 self._unique_in.append(pair[0])
             self.in_queues.append(pair[0])
             self.out_queues.append(pair[1])
+        _live_pools.add(self)
 
     def close(self, timeout: Optional[float] = 5.0) -> None:
         """Stop the worker threads.  Idempotent."""
