@@ -63,6 +63,21 @@ size_t pb2_gemm_workspace_bytes(void);
  * split-K partial tiles and per-tile arrival counters; may be NULL when splits == 1. */
 int pb2_gemm_bf16(const pb2_gemm_desc* desc, void* workspace, size_t workspace_bytes, cudaStream_t stream);
 
+/* Same GEMM, for callers that cannot supply (or allocate) a workspace: hosts whose memory is owned by
+ * someone else's pool, loops that must stay clear of cudaMalloc, plain C callers without an allocator.
+ * No counterpart in the reference (it has no native code and no scratch to manage).
+ * The split-K scratch is a fixed array inside the library image: PB2_GEMM_STATIC_SCRATCH_BYTES of
+ * partial tiles plus the arrival counters, resident on every GPU that loads the library until the
+ * process exits.  A problem whose partial tiles need more is refused with an error that names the
+ * limit (choose fewer `splits`, or use pb2_gemm_bf16).  Inputs and outputs are still the caller's.
+ * The first call on each device also resolves the array's device address (cudaGetSymbolAddress with
+ * that device current): issue it at start-up, before any stream capture begins.  Every call uses the
+ * same array and inherits its previous contents; the counters are cleared on `stream` before each
+ * launch.  Calls that may overlap on the GPU race on it: serialise them.  Allocates nothing. */
+#define PB2_GEMM_STATIC_SCRATCH_BYTES (16u * 1024u * 1024u)
+size_t pb2_gemm_noalloc_max_scratch_bytes(void);
+int pb2_gemm_bf16_noalloc(const pb2_gemm_desc* desc, cudaStream_t stream);
+
 /* ---- residual add + LayerNorm: y = LN(x + h) (h may be NULL) ------------------------------
  * bf16 rows of width E (multiple of 8, <= 8192), fp32 gamma/beta/statistics.
  * Backward also returns dh = dres * dropout_mask / (1 - p): the gradient of the sub-layer output

@@ -30,6 +30,9 @@
 //
 // No counterpart in the reference: its GEMMs are cuBLAS calls behind nn.Linear /
 // nn.MultiheadAttention (main.py:45,148); SURVEY.md K2/K4/K6/K7, W5.
+#include <stdio.h>
+#include <string.h>
+
 #include "common.cuh"
 #include "pipe_b200.h"
 
@@ -375,4 +378,89 @@ extern "C" int pb2_gemm_bf16(const pb2_gemm_desc* d, void* workspace, size_t wor
         slots = PB2_GEMM_COUNTER_BYTES / sizeof(unsigned int);
     }
     return gemm_launch(d, partials, counters, partial_bytes, slots, stream);
+}
+
+// ---------------------------------------------------------------------------------------
+// pb2_gemm_bf16_noalloc: the same GEMM for callers that cannot obtain scratch memory.
+//
+// Some hosts of this library have no way to hand over a workspace: a plug-in running inside
+// a server that reserved all of HBM for its own pool at start-up, a control loop that is not
+// allowed to touch cudaMalloc because of the device-wide synchronisation it implies, a C
+// caller with no tensor library to allocate through.  For them the split-K scratch lives
+// in the library image itself: a file-scope __device__ array of PB2_GEMM_STATIC_SCRATCH_BYTES
+// (+ the arrival counters).  Every GPU that loads the library carries this array until the
+// process exits, which is why it is kept modest; problems whose partial tiles do not fit
+// are rejected, not silently shrunk.
+//
+// The array's name is only a host-side handle.  Its device address is looked up once per
+// device with cudaGetSymbolAddress while that device is current, and it is that address
+// the kernel receives.  The look-up happens inside the first call on each device, so make
+// that first call during start-up, outside any stream capture.
+//
+// All calls share the one array and it keeps whatever the previous call left behind.  The
+// arrival counters — the only part that must start at zero — are cleared on the caller's
+// stream ahead of every launch; the partial tiles are always written before they are read.
+// Two calls that can overlap on the GPU (different streams, or different host threads on
+// different streams) would race on the array: serialise them.
+//
+// Nothing here calls cudaMalloc, cudaFree or any allocating library routine.
+// ---------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_static_scratch[PB2_GEMM_STATIC_SCRATCH_BYTES + PB2_GEMM_COUNTER_BYTES];
+
+namespace {
+constexpr int kMaxDevices = 64;
+void* s_scratch_addr[kMaxDevices];            // device address of g_static_scratch, per device
+std::atomic<int> s_scratch_state[kMaxDevices];  // 0 = not looked up, 1 = ready
+std::atomic_flag s_scratch_lock = ATOMIC_FLAG_INIT;
+}  // namespace
+
+extern "C" size_t pb2_gemm_noalloc_max_scratch_bytes(void) { return PB2_GEMM_STATIC_SCRATCH_BYTES; }
+
+extern "C" int pb2_gemm_bf16_noalloc(const pb2_gemm_desc* d, cudaStream_t stream) {
+    if (!d) { set_error("pb2_gemm_bf16_noalloc: null descriptor"); return -1; }
+    int dev = -1;
+    PB2_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) {
+        set_error("pb2_gemm_bf16_noalloc: device ordinal %d outside [0, %d)", dev, kMaxDevices);
+        return -1;
+    }
+    if (s_scratch_state[dev].load(std::memory_order_acquire) == 0) {
+        // one-time set-up for this device (the current one): resolve the symbol to a device address
+        while (s_scratch_lock.test_and_set(std::memory_order_acquire)) {
+        }
+        int rc = 0;
+        if (s_scratch_state[dev].load(std::memory_order_relaxed) == 0) {
+            void* p = nullptr;
+            cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+            if (e != cudaSuccess || p == nullptr) {
+                set_error("pb2_gemm_bf16_noalloc: cudaGetSymbolAddress(static scratch) on device %d: %s", dev,
+                          cudaGetErrorString(e));
+                rc = -1;
+            } else {
+                s_scratch_addr[dev] = p;
+                s_scratch_state[dev].store(1, std::memory_order_release);
+            }
+        }
+        s_scratch_lock.clear(std::memory_order_release);
+        if (rc) return rc;
+    }
+    char* base = static_cast<char*>(s_scratch_addr[dev]);
+    float* partials = reinterpret_cast<float*>(base);
+    unsigned int* counters = reinterpret_cast<unsigned int*>(base + PB2_GEMM_STATIC_SCRATCH_BYTES);
+    // the counters must be zero when the kernel starts, whatever the last call (or a failed one) left
+    PB2_CUDA(cudaMemsetAsync(counters, 0, PB2_GEMM_COUNTER_BYTES, stream));
+    int rc = gemm_launch(d, partials, counters, PB2_GEMM_STATIC_SCRATCH_BYTES,
+                         PB2_GEMM_COUNTER_BYTES / sizeof(unsigned int), stream);
+    if (rc) {
+        // make the limit explicit for the one failure mode that is specific to this entry point
+        const char* why = pb2_last_error();
+        if (why && strstr(why, "scratch too small")) {
+            char buf[400];
+            snprintf(buf, sizeof(buf), "%s", why);
+            set_error("pb2_gemm_bf16_noalloc: the built-in scratch is limited to %u bytes of split-K partials; "
+                      "lower `splits`/`block_n` or use pb2_gemm_bf16 with your own workspace [%s]",
+                      static_cast<unsigned>(PB2_GEMM_STATIC_SCRATCH_BYTES), buf);
+        }
+    }
+    return rc;
 }
