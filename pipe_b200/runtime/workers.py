@@ -131,19 +131,20 @@ class WorkerPool:
         self._closed = True
         for q in self._unique_in:
             q.put(None)
+        me = threading.current_thread()
         for t in self._threads:
-            t.join(timeout)
+            if t is not me:
+                t.join(timeout)
 
     @property
     def alive(self) -> int:
         return sum(t.is_alive() for t in self._threads)
 
-    def __del__(self) -> None:  # best effort; daemon threads die with the process anyway
+    def __del__(self) -> None:
+        # Join, do not just signal: a worker that is still unwinding its CUDA device guard while the
+        # interpreter finalises gets killed inside C++ frames, which aborts the process.
         try:
-            if not self._closed:
-                self._closed = True
-                for q in self._unique_in:
-                    q.put(None)
+            self.close(timeout=2.0)
         except Exception:
             pass
 
