@@ -7,10 +7,11 @@
  * the caller.  The Python package binds these with ctypes (pipe_b200/ops/_lib.py);
  * other runtimes can link the library directly.
  *
- * Dropout everywhere is counter-based: Philox4x32-10 keyed by `seed`, with the
- * element's flat index in the output tensor as counter and `rng_stream`
- * separating call sites, so a backward kernel (or a checkpoint recompute) given
- * the same (seed, rng_stream) regenerates the identical mask.
+ * Dropout everywhere is counter-based: a stateless generator (two SplitMix64
+ * finalisers) keyed by `seed`, with the element's flat index in the output tensor
+ * as counter and `rng_stream` separating call sites, so a backward kernel (or a
+ * checkpoint recompute) given the same (seed, rng_stream) regenerates the
+ * identical mask.
  */
 #ifndef PIPE_B200_H_
 #define PIPE_B200_H_
@@ -56,6 +57,7 @@ typedef struct pb2_gemm_desc {
     float* sumsq;         /* optional device scalar: += sum of squares of the stored values (grad-norm fusion) */
     int block_n;          /* N tile, multiple of 16 in [16,256]; 0 = choose */
     int splits;           /* split-K factor; 0 = choose */
+    int stages;           /* TMA ring depth; 0 = choose */
 } pb2_gemm_desc;
 
 size_t pb2_gemm_workspace_bytes(void);

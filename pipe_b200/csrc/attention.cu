@@ -8,7 +8,7 @@
 // In this framework's configs attention is <= 0.2 % of the FLOPs (S = 25..128, SURVEY.md
 // §6.2): one CTA owns one (sequence, head) pair, keeps Q, K, V (and dO) in shared memory and
 // the S x S score matrix on chip for the whole pass; nothing but QKV and O touches HBM and
-// the backward recomputes the probabilities (and the Philox dropout mask) instead of
+// the backward recomputes the probabilities (and the counter-RNG dropout mask) instead of
 // storing them.  Limits: S <= 128, head_dim <= 256, shared memory <= 227 KB.
 //
 // Reference counterpart: nn.MultiheadAttention inside nn.TransformerEncoderLayer
@@ -74,7 +74,7 @@ __device__ __forceinline__ void softmax_rows(float* sc, int S, int spad, int cau
     }
 }
 
-__device__ __forceinline__ float keep_scale(const Philox& ph, const AttnShape& a, uint32_t thr, float inv_keep, int n,
+__device__ __forceinline__ float keep_scale(const CounterRng& ph, const AttnShape& a, uint32_t thr, float inv_keep, int n,
                                             int h, int i, int j) {
     if (a.drop_p <= 0.f) return 1.f;
     const uint64_t idx = ((static_cast<uint64_t>(n) * a.H + h) * a.S + i) * a.S + j;
@@ -106,7 +106,7 @@ attn_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict
     __syncthreads();
 
     if (a.drop_p > 0.f) {
-        const Philox ph(a.seed);
+        const CounterRng ph(a.seed);
         const uint32_t thr = static_cast<uint32_t>(fminf(a.drop_p, 0.999999f) * 4294967296.0f);
         const float inv_keep = 1.f / (1.f - a.drop_p);
         for (int p = threadIdx.x; p < S * S; p += blockDim.x) {
@@ -151,7 +151,7 @@ attn_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* __re
     load_head(dout + h * D, a.E, a.NB, S, D, n, dO, dpad);
     __syncthreads();
 
-    const Philox ph(a.seed);
+    const CounterRng ph(a.seed);
     const uint32_t thr = static_cast<uint32_t>(fminf(a.drop_p, 0.999999f) * 4294967296.0f);
     const float inv_keep = a.drop_p > 0.f ? 1.f / (1.f - a.drop_p) : 1.f;
 

@@ -1,7 +1,7 @@
 // Shared device/host helpers for the pipe_b200 sm_100a kernels.
 //
 // Everything here is inline PTX for Blackwell (tcgen05 / TMEM / TMA / mbarrier)
-// plus a Philox4x32-10 generator used by every fused-dropout epilogue.  No
+// plus the counter-based generator used by every fused-dropout epilogue.  No
 // CUTLASS/CuTe dependency: descriptor encodings follow the PTX ISA bit layouts.
 #pragma once
 
@@ -208,30 +208,33 @@ __host__ __device__ __forceinline__ uint32_t umma_idesc_bf16(uint32_t m, uint32_
     return d;
 }
 
-// ---- Philox4x32-10 ---------------------------------------------------------------
-struct Philox {
-    uint32_t k0, k1;
-    __device__ __forceinline__ Philox(uint64_t seed) : k0(static_cast<uint32_t>(seed)), k1(static_cast<uint32_t>(seed >> 32)) {}
-    // 4 x 32 random bits for counter (lo, hi); `stream` separates call sites.
+// ---- counter-based random bits -------------------------------------------------------
+// Stateless generator: 128 random bits as a pure function of (seed, stream, counter), built from
+// two SplitMix64 finalisers (2 x 64-bit multiply-xorshift).  Dropout needs reproducibility — the
+// backward and a checkpoint recompute must regenerate the forward's mask from (seed, stream) alone —
+// and decent uniformity, not cryptographic quality; this costs ~30 integer instructions per four
+// elements, which matters in GEMM epilogues that sit on a kernel's critical path.
+struct CounterRng {
+    uint64_t key;
+    __device__ __forceinline__ explicit CounterRng(uint64_t seed)
+        : key(seed * 0x9E3779B97F4A7C15ull + 0xD1B54A32D192ED03ull) {}
+    __device__ __forceinline__ static uint64_t mix(uint64_t z) {
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+        z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+        return z ^ (z >> 31);
+    }
+    // 4 x 32 random bits for `counter`; `stream` separates call sites.
     __device__ __forceinline__ uint4 operator()(uint64_t counter, uint64_t stream) const {
-        uint32_t c0 = static_cast<uint32_t>(counter), c1 = static_cast<uint32_t>(counter >> 32);
-        uint32_t c2 = static_cast<uint32_t>(stream), c3 = static_cast<uint32_t>(stream >> 32);
-        uint32_t a = k0, b = k1;
-#pragma unroll
-        for (int r = 0; r < 10; ++r) {
-            uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
-            uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
-            uint32_t n0 = hi1 ^ c1 ^ a, n1 = lo1, n2 = hi0 ^ c3 ^ b, n3 = lo0;
-            c0 = n0; c1 = n1; c2 = n2; c3 = n3;
-            a += 0x9E3779B9u; b += 0xBB67AE85u;
-        }
-        return make_uint4(c0, c1, c2, c3);
+        const uint64_t x = (key ^ (stream * 0xC2B2AE3D27D4EB4Full)) + counter * 0x9E3779B97F4A7C15ull;
+        const uint64_t a = mix(x), b = mix(x ^ 0xA5A5A5A5A5A5A5A5ull);
+        return make_uint4(static_cast<uint32_t>(a), static_cast<uint32_t>(a >> 32), static_cast<uint32_t>(b),
+                          static_cast<uint32_t>(b >> 32));
     }
 };
 
-// Dropout keep-decision for element `idx` of a tensor: one Philox call serves the
+// Dropout keep-decision for element `idx` of a tensor: one generator call serves the
 // four elements idx&~3 .. idx|3.  keep iff u32 >= threshold (threshold = p * 2^32).
-__device__ __forceinline__ bool dropout_keep(const Philox& ph, uint64_t stream, uint64_t idx, uint32_t threshold) {
+__device__ __forceinline__ bool dropout_keep(const CounterRng& ph, uint64_t stream, uint64_t idx, uint32_t threshold) {
     uint4 r = ph(idx >> 2, stream);
     uint32_t v = (idx & 3) == 0 ? r.x : (idx & 3) == 1 ? r.y : (idx & 3) == 2 ? r.z : r.w;
     return v >= threshold;

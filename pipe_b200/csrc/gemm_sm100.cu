@@ -15,12 +15,12 @@
 // flight per SM to saturate HBM3e.  The epilogue can store the tile transposed,
 // which turns D^T[features, tokens] back into row-major [tokens, features].
 //
-// Pipeline inside a CTA (192 threads, one output tile, one K-split):
+// Pipeline inside a CTA (320 threads, one output tile, one K-split):
 //   warp 0      TMA producer: cp.async.bulk.tensor -> 128B-swizzled smem ring, mbarrier complete_tx
 //   warp 1      allocates TMEM; one elected lane issues tcgen05.mma (M=128, N=block_n, K=16) x 4 per stage,
 //               tcgen05.commit releases the smem stage / signals the accumulator
-//   warps 2-5   epilogue: tcgen05.ld accumulator -> registers -> (split-K fix-up) -> bias / ReLU /
-//               Philox dropout / mask-multiply / residual add / accumulate -> global
+//   warps 2-9   epilogue: tcgen05.ld accumulator -> registers -> (split-K fix-up) -> bias / ReLU /
+//               counter-RNG dropout / mask-multiply / residual add / accumulate -> global
 //
 // Split-K fix-up: every split writes its fp32 partial tile to a scratch workspace,
 // bumps a per-tile counter, and the CTA that arrives last adds the other splits'
@@ -42,7 +42,8 @@ constexpr int kBlockM = 128;
 constexpr int kBlockK = 64;          // 64 bf16 = one 128-byte swizzle row
 constexpr int kUmmaK = 16;
 constexpr int kMaxStages = 8;
-constexpr int kThreads = 192;
+constexpr int kEpilogueWarps = 8;       // two per TMEM lane quarter, alternating 16-column chunks
+constexpr int kThreads = 64 + 32 * kEpilogueWarps;
 
 struct GemmArgs {
     int M, N, K;
@@ -70,7 +71,19 @@ struct GemmArgs {
     float* sumsq;                    // optional: += sum of squares of what was written
     float* partials;
     unsigned int* counters;
+    unsigned long long* debug_ts;    // optional: per-CTA phase timestamps (globaltimer ns), 8 per CTA
 };
+
+__device__ __forceinline__ unsigned long long gtime() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#define PB2_TS(slot)                                                                                   \
+    do {                                                                                               \
+        if (g.debug_ts)                                                                                \
+            g.debug_ts[((blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * 16 + (slot)] = gtime(); \
+    } while (0)
 
 struct __align__(8) SmemCtl {
     uint64_t full[kMaxStages];
@@ -84,17 +97,119 @@ __device__ __forceinline__ float bf16_bits_to_float(unsigned short b) {
     return __uint_as_float(static_cast<uint32_t>(b) << 16);
 }
 
-// Finish one element: everything after the raw accumulator.  (row, col) are
-// coordinates in the *output tensor*; idx = row * ld + col.
-__device__ __forceinline__ float epilogue_elem(const GemmArgs& g, const Philox& ph, uint32_t thr, float inv_keep,
-                                               float v, int m_glob, int n_glob, long long idx) {
-    v *= g.alpha;
-    if (g.bias) v += g.bias[g.bias_along_m ? m_glob : n_glob];
-    if (g.relu) v = fmaxf(v, 0.f);
-    if (g.drop_p > 0.f) v = dropout_keep(ph, g.stream, static_cast<uint64_t>(idx), thr) ? v * inv_keep : 0.f;
-    if (g.mask_src) v = (__bfloat162float(g.mask_src[idx]) > 0.f) ? v * g.mask_scale : 0.f;
-    if (g.addend) v += __bfloat162float(g.addend[idx]);
-    return v;
+// Everything after the raw accumulator for one 16-column chunk of one accumulator row, written as
+// straight-line predicated code: the epilogue runs with one or two warps per scheduler, so every
+// dependent instruction or divergent branch is exposed latency; sixteen independent elements in
+// flight hide it.  (m, n) are accumulator coordinates; the output element lives at
+// out[n * ld + m] when the store is transposed, else out[m * ld + n].
+struct EpiCtx {
+    CounterRng rng;
+    uint32_t thr;
+    float inv_keep;
+    float bias_m;        // bias for this thread's row when bias_along_m
+    bool row_ok;
+};
+
+__device__ __forceinline__ void epilogue_chunk(const GemmArgs& g, const EpiCtx& e, float (&v)[16], int m_glob,
+                                               int n_first, float& ss) {
+    const bool tr = g.transpose_out != 0;
+    const long long stride = tr ? g.ld_out : 1;
+    const long long idx0 = tr ? static_cast<long long>(n_first) * g.ld_out + m_glob
+                              : static_cast<long long>(m_glob) * g.ld_out + n_first;
+    const int n_valid = g.N - n_first;                 // columns of this chunk inside the matrix (may exceed 16)
+
+#pragma unroll
+    for (int j = 0; j < 16; ++j) v[j] *= g.alpha;
+    if (g.bias) {
+        if (g.bias_along_m) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) v[j] += e.bias_m;
+        } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) v[j] += (j < n_valid) ? g.bias[n_first + j] : 0.f;
+        }
+    }
+    if (g.relu) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j], 0.f);
+    }
+    if (g.drop_p > 0.f) {
+        if (tr) {
+            // element index n * ld + m: lanes m..m+3 share a counter, each column needs its own call
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                const uint64_t idx = static_cast<uint64_t>(idx0 + j * stride);
+                const uint4 r = e.rng(idx >> 2, g.stream);
+                const uint32_t sel = (idx & 3) == 0 ? r.x : (idx & 3) == 1 ? r.y : (idx & 3) == 2 ? r.z : r.w;
+                v[j] = sel >= e.thr ? v[j] * e.inv_keep : 0.f;
+            }
+        } else {
+            // 16 consecutive indices: 4 (aligned) or 5 counters
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                const uint64_t idx = static_cast<uint64_t>(idx0 + j);
+                const uint4 r = e.rng(idx >> 2, g.stream);
+                const uint32_t sel = (idx & 3) == 0 ? r.x : (idx & 3) == 1 ? r.y : (idx & 3) == 2 ? r.z : r.w;
+                v[j] = sel >= e.thr ? v[j] * e.inv_keep : 0.f;
+            }
+        }
+    }
+    if (!e.row_ok) return;
+    if (g.mask_src) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            const float mk = (j < n_valid) ? __bfloat162float(g.mask_src[idx0 + j * stride]) : 0.f;
+            v[j] = mk > 0.f ? v[j] * g.mask_scale : 0.f;
+        }
+    }
+    if (g.addend) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j)
+            if (j < n_valid) v[j] += __bfloat162float(g.addend[idx0 + j * stride]);
+    }
+
+    if (g.out_f32) {
+        float* dst = static_cast<float*>(g.out) + idx0;
+        if (!tr && n_valid >= 16 && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+            float4* d4 = reinterpret_cast<float4*>(dst);
+            if (g.accumulate) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const float4 o = d4[q];
+                    v[4 * q] += o.x; v[4 * q + 1] += o.y; v[4 * q + 2] += o.z; v[4 * q + 3] += o.w;
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) d4[q] = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                if (j < n_valid) {
+                    if (g.accumulate) v[j] += dst[j * stride];
+                    dst[j * stride] = v[j];
+                }
+            }
+        }
+    } else {
+        __nv_bfloat16* dst = static_cast<__nv_bfloat16*>(g.out) + idx0;
+        if (!tr && n_valid >= 16 && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+            uint4 pk[2];
+            __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(pk);
+#pragma unroll
+            for (int q = 0; q < 8; ++q) h2[q] = __floats2bfloat162_rn(v[2 * q], v[2 * q + 1]);
+            reinterpret_cast<uint4*>(dst)[0] = pk[0];
+            reinterpret_cast<uint4*>(dst)[1] = pk[1];
+        } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+                if (j < n_valid) dst[j * stride] = __float2bfloat16(v[j]);
+        }
+    }
+    if (g.sumsq) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j)
+            if (j < n_valid) ss += v[j] * v[j];
+    }
 }
 
 __global__ void __launch_bounds__(kThreads, 1)
@@ -117,6 +232,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     int kb_count = g.k_blocks_total - kb_begin;
     if (kb_count > g.k_blocks_per_split) kb_count = g.k_blocks_per_split;
 
+    if (threadIdx.x == 0) PB2_TS(0);
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmap_a);
         tma_prefetch_desc(&tmap_b);
@@ -135,6 +251,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = ctl->tmem_base;
+    if (threadIdx.x == 0) PB2_TS(1);
 
     if (warp == 0) {
         // ===================== TMA producer =====================
@@ -160,6 +277,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
             const uint32_t round = it / g.stages;
             mbar_wait(&ctl->full[s], round & 1);
             tc_fence_after();
+            if (it == 0 && lane == 0) PB2_TS(2);
             if (elect_one()) {
                 const uint32_t sa = smem_u32(smem + static_cast<size_t>(s) * stage_bytes);
                 const uint64_t da = umma_desc_k_sw128(sa);
@@ -170,86 +288,79 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                     umma_bf16(tmem_base, da + 2 * k, db + 2 * k, idesc, (it > 0 || k > 0) ? 1u : 0u);
                 }
                 umma_commit(&ctl->empty[s]);                      // frees the smem stage when the MMAs retire
-                if (it == kb_count - 1) umma_commit(&ctl->tmem_full);
+                if (it == kb_count - 1) { umma_commit(&ctl->tmem_full); PB2_TS(3); }
             }
             __syncwarp();
         }
     } else {
-        // ===================== epilogue (warps 2..5) =====================
+        // ===================== epilogue (warps 2..9) =====================
         const int quarter = warp & 3;                 // TMEM lane quarter this warp may read
+        const int half = (warp - 2) >> 2;             // which of the two warps of that quarter
         const int m_local = quarter * 32 + lane;
         const int m_glob = m0 + m_local;
         const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
-        const int ep_tid = threadIdx.x - 64;          // 0..127
+        const int ep_tid = threadIdx.x - 64;          // 0..255
 
         mbar_wait(&ctl->tmem_full, 0);
         tc_fence_after();
+        if (ep_tid == 0) PB2_TS(4);
 
         const int tile = blockIdx.y * gridDim.x + blockIdx.x;
+        const size_t tile_elems = static_cast<size_t>(g.block_n) * kBlockM;
         bool last = true;
         if (g.splits > 1) {
-            float* mine = g.partials + (static_cast<size_t>(tile) * g.splits + split) * g.block_n * kBlockM;
-            for (int c = 0; c < g.block_n; c += 16) {
+            // partial tile layout [column][row]: a warp writes 32 consecutive floats per column
+            float* mine = g.partials + (static_cast<size_t>(tile) * g.splits + split) * tile_elems + m_local;
+            for (int c = half * 16; c < g.block_n; c += 32) {
                 uint32_t r[16];
                 tmem_ld_32x16(t_lane + c, r);
                 tmem_ld_wait();
 #pragma unroll
-                for (int j = 0; j < 16; ++j) mine[static_cast<size_t>(c + j) * kBlockM + m_local] = __uint_as_float(r[j]);
+                for (int j = 0; j < 16; ++j) __stcg(mine + static_cast<size_t>(c + j) * kBlockM, __uint_as_float(r[j]));
             }
             __threadfence();
-            asm volatile("bar.sync 1, 128;" ::: "memory");
+            asm volatile("bar.sync 1, 256;" ::: "memory");
             if (ep_tid == 0) {
                 unsigned int prev = atomicAdd(&g.counters[tile], 1u);
                 ctl->is_last = (prev == static_cast<unsigned int>(g.splits - 1)) ? 1u : 0u;
                 if (prev == static_cast<unsigned int>(g.splits - 1)) g.counters[tile] = 0u;   // re-arm for the next launch
             }
-            asm volatile("bar.sync 1, 128;" ::: "memory");
+            asm volatile("bar.sync 1, 256;" ::: "memory");
             last = ctl->is_last != 0;
             if (last) __threadfence();
         }
 
         if (last) {
-            const Philox ph(g.seed);
-            const uint32_t thr = static_cast<uint32_t>(fminf(g.drop_p, 0.999999f) * 4294967296.0f);
-            const float inv_keep = g.drop_p > 0.f ? 1.f / (1.f - g.drop_p) : 1.f;
+            EpiCtx e{CounterRng(g.seed), static_cast<uint32_t>(fminf(g.drop_p, 0.999999f) * 4294967296.0f),
+                     g.drop_p > 0.f ? 1.f / (1.f - g.drop_p) : 1.f, 0.f, m_glob < g.M};
+            if (g.bias && g.bias_along_m && e.row_ok) e.bias_m = g.bias[m_glob];
             float ss = 0.f;
-            const float* others = g.partials + static_cast<size_t>(tile) * g.splits * g.block_n * kBlockM;
-            for (int c = 0; c < g.block_n; c += 16) {
+            const float* others = g.partials + static_cast<size_t>(tile) * g.splits * tile_elems + m_local;
+            for (int c = half * 16; c < g.block_n; c += 32) {
+                if (ep_tid == 0 && c < 64) PB2_TS(7 + (c >> 4) * 2);
                 uint32_t r[16];
                 tmem_ld_32x16(t_lane + c, r);
                 tmem_ld_wait();
                 float v[16];
 #pragma unroll
                 for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
-                for (int s = 0; s < g.splits; ++s) {
-                    if (s == split) continue;
-                    const float* p = others + static_cast<size_t>(s) * g.block_n * kBlockM;
+                for (int sp = 0; sp < g.splits; ++sp) {
+                    if (sp == split) continue;
+                    const float* p = others + static_cast<size_t>(sp) * tile_elems + static_cast<size_t>(c) * kBlockM;
+                    float t[16];
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) v[j] += __ldcg(p + static_cast<size_t>(c + j) * kBlockM + m_local);
-                }
-                if (m_glob >= g.M) continue;
+                    for (int j = 0; j < 16; ++j) t[j] = __ldcg(p + j * kBlockM);
 #pragma unroll
-                for (int j = 0; j < 16; ++j) {
-                    const int n_glob = n0 + c + j;
-                    if (n_glob >= g.N) break;
-                    const long long idx = g.transpose_out ? static_cast<long long>(n_glob) * g.ld_out + m_glob
-                                                          : static_cast<long long>(m_glob) * g.ld_out + n_glob;
-                    float o = epilogue_elem(g, ph, thr, inv_keep, v[j], m_glob, n_glob, idx);
-                    if (g.out_f32) {
-                        float* dst = static_cast<float*>(g.out) + idx;
-                        if (g.accumulate) o += *dst;
-                        *dst = o;
-                    } else {
-                        static_cast<__nv_bfloat16*>(g.out)[idx] = __float2bfloat16(o);
-                    }
-                    ss += o * o;
+                    for (int j = 0; j < 16; ++j) v[j] += t[j];
                 }
+                if (n0 + c < g.N) epilogue_chunk(g, e, v, m_glob, n0 + c, ss);
             }
             if (g.sumsq) {
                 ss = warp_sum(ss);
                 if (lane == 0) atomicAdd(g.sumsq, ss);
             }
         }
+        if (ep_tid == 0) PB2_TS(5);
         tc_fence_before();
     }
 
@@ -258,6 +369,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         tc_fence_after();
         tmem_dealloc(tmem_base, g.tmem_cols);
     }
+    if (threadIdx.x == 32) PB2_TS(6);
 }
 
 static int next_pow2_cols(int n) {
@@ -275,6 +387,11 @@ extern "C" size_t pb2_gemm_workspace_bytes(void) {
     // bounds splits so that tiles*splits*block_n*128*4 <= this.  Counters live at the end.
     return PB2_GEMM_WORKSPACE_BYTES;
 }
+
+static unsigned long long* g_debug_ts = nullptr;
+// Debug hook (not part of the supported ABI): phase timestamps of subsequent launches go to `buf`
+// (8 x u64 per CTA, CTA-linear order); pass NULL to switch off.
+extern "C" void pb2_debug_gemm_timestamps(unsigned long long* buf) { g_debug_ts = buf; }
 
 static int gemm_launch(const pb2_gemm_desc* d, float* partials, unsigned int* counters, size_t partial_bytes,
                        size_t counter_slots, cudaStream_t stream) {
@@ -336,6 +453,7 @@ static int gemm_launch(const pb2_gemm_desc* d, float* partials, unsigned int* co
     const int stage_bytes = (kBlockM + bn) * kBlockK * 2;
     int stages = (200 * 1024) / stage_bytes;
     if (stages > kMaxStages) stages = kMaxStages;
+    if (d->stages > 0 && d->stages < stages) stages = d->stages;
     if (stages > g.k_blocks_per_split) stages = g.k_blocks_per_split;
     if (stages < 1) stages = 1;
     g.stages = stages;
@@ -348,6 +466,7 @@ static int gemm_launch(const pb2_gemm_desc* d, float* partials, unsigned int* co
     g.addend = static_cast<const __nv_bfloat16*>(d->addend);
     g.accumulate = d->accumulate; g.alpha = d->alpha == 0.f ? 1.f : d->alpha;
     g.sumsq = d->sumsq;
+    g.debug_ts = g_debug_ts;
 
     CUtensorMap ta, tb;
     if (make_tmap_bf16_2d(&ta, d->a, d->M, d->K, d->lda, kBlockM, kBlockK)) return -1;

@@ -1,6 +1,6 @@
 // Row-wise fused kernels of the Transformer block that are not GEMMs:
 //   * residual add + LayerNorm forward / backward (post-norm: y = LN(x + h)), with the
-//     dropout that produced h re-generated from Philox in the backward
+//     dropout that produced h re-generated from the counter RNG in the backward
 //   * token embedding * sqrt(E) + sinusoidal position + dropout forward, scatter-add backward
 //   * softmax cross-entropy over (padded) bf16 logits, forward + dlogits in one pass
 //   * bf16 transpose with fused column sums (wgrad operands + bias gradients)
@@ -177,7 +177,7 @@ add_ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __r
     }
     const float m1 = block_sum(s1, red) / E;
     const float m2 = block_sum(s2, red) / E;
-    const Philox ph(seed);
+    const CounterRng ph(seed);
     const uint32_t thr = static_cast<uint32_t>(fminf(drop_p, 0.999999f) * 4294967296.0f);
     const float inv_keep = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
 #pragma unroll
@@ -190,7 +190,7 @@ add_ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __r
             store8(dres + row * E + c, dz);
             if (dh) {
                 if (drop_p > 0.f) {
-                    // 8 consecutive elements = two Philox calls
+                    // 8 consecutive elements = two generator calls
                     const uint64_t idx = row * static_cast<uint64_t>(E) + c;
                     const uint4 r0 = ph(idx >> 2, rng_stream), r1 = ph((idx >> 2) + 1, rng_stream);
                     const uint32_t rr[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
@@ -218,7 +218,7 @@ embed_fwd_kernel(const long long* __restrict__ tokens, const float* __restrict__
     const long long tok = tokens[static_cast<size_t>(n) * S + s];
     const float* w = weight + static_cast<size_t>(tok) * E;
     const float* p = pe + static_cast<size_t>(s) * E;
-    const Philox ph(seed);
+    const CounterRng ph(seed);
     const uint32_t thr = static_cast<uint32_t>(fminf(drop_p, 0.999999f) * 4294967296.0f);
     const float inv_keep = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
     for (int c = threadIdx.x * 4; c < E; c += blockDim.x * 4) {
@@ -246,7 +246,7 @@ embed_bwd_kernel(const long long* __restrict__ tokens, const __nv_bfloat16* __re
     const int s = row / N, n = row % N;
     const long long tok = tokens[static_cast<size_t>(n) * S + s];
     float* dw = dweight + static_cast<size_t>(tok) * E;
-    const Philox ph(seed);
+    const CounterRng ph(seed);
     const uint32_t thr = static_cast<uint32_t>(fminf(drop_p, 0.999999f) * 4294967296.0f);
     const float k = scale * (drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f);
     for (int c = threadIdx.x * 4; c < E; c += blockDim.x * 4) {

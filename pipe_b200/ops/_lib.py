@@ -33,7 +33,7 @@ class GemmDesc(ctypes.Structure):
         ("addend", ctypes.c_void_p),
         ("accumulate", ctypes.c_int), ("alpha", ctypes.c_float),
         ("sumsq", ctypes.c_void_p),
-        ("block_n", ctypes.c_int), ("splits", ctypes.c_int),
+        ("block_n", ctypes.c_int), ("splits", ctypes.c_int), ("stages", ctypes.c_int),
     ]
 
 

@@ -44,7 +44,7 @@ def gemm_nt(a: Tensor, b: Tensor, *, out: Optional[Tensor] = None, out_dtype: to
             relu: bool = False, drop_p: float = 0.0, seed: int = 0, rng_stream: int = 0,
             mask_src: Optional[Tensor] = None, mask_scale: float = 1.0, addend: Optional[Tensor] = None,
             accumulate: bool = False, alpha: float = 1.0, sumsq: Optional[Tensor] = None,
-            block_n: int = 0, splits: int = 0) -> Tensor:
+            block_n: int = 0, splits: int = 0, stages: int = 0) -> Tensor:
     lib = _lib.load()
     assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16, "gemm_nt takes bf16 operands"
     assert a.dim() == 2 and b.dim() == 2 and a.size(1) == b.size(1)
@@ -80,7 +80,7 @@ def gemm_nt(a: Tensor, b: Tensor, *, out: Optional[Tensor] = None, out_dtype: to
     d.accumulate = int(accumulate)
     d.alpha = float(alpha)
     d.sumsq = _lib.ptr(sumsq)
-    d.block_n, d.splits = block_n, splits
+    d.block_n, d.splits, d.stages = block_n, splits, stages
 
     ws = workspace(a.device)
     with torch.cuda.device(a.device):

@@ -1,0 +1,35 @@
+"""Phase timestamps inside the GEMM kernel (debug hook): where does a CTA's time go?"""
+import ctypes, os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from pipe_b200.ops import _lib
+from pipe_b200.ops.gemm import gemm_nt
+lib = _lib.load()
+dev = "cuda"
+flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
+names = ["start", "setup done", "first stage landed", "last MMA issued", "accum ready", "epilogue done", "end", "c0 pre-ld", "c0 post-ld", "c16 pre-ld", "c16 post-ld", "c32 pre", "c32 post", "c48 pre", "c48 post"]
+
+def run(M, N, K, **kw):
+    a = torch.randn(M, K, device=dev).bfloat16(); b = torch.randn(N, K, device=dev).bfloat16()
+    out = torch.empty(N, M, dtype=torch.bfloat16, device=dev)
+    ctas = ((M + 127) // 128) * kw.get("splits", 1)
+    ts = torch.zeros(ctas * 16, dtype=torch.int64, device=dev)
+    gemm_nt(a, b, out=out, transpose_out=True, **kw)
+    flush.zero_()
+    lib.pb2_debug_gemm_timestamps(ctypes.c_void_p(ts.data_ptr()))
+    gemm_nt(a, b, out=out, transpose_out=True, **kw)
+    lib.pb2_debug_gemm_timestamps(ctypes.c_void_p(0))
+    torch.cuda.synchronize()
+    t = ts.view(ctas, 16).cpu()
+    t0 = t[:, 0].min()
+    print(f"--- M={M} N={N} K={K} {kw} ctas={ctas}: kernel span {(t[:, 6].max() - t0).item() / 1e3:.1f} us")
+    for k, nm in enumerate(names):
+        col = (t[:, k] - t0).float() / 1e3
+        print(f"   {nm:20s} min {col.min():7.2f}  median {col.median():7.2f}  max {col.max():7.2f} us")
+
+run(128, 80, 512, splits=1)
+run(128, 80, 512, splits=1, bias=torch.randn(128, device=dev), bias_along_m=True)
+run(4096, 80, 4096, splits=1)
+run(4096, 80, 4096, splits=4)
+run(4096, 80, 4096, splits=4, bias=torch.randn(4096, device=dev), bias_along_m=True, relu=True, drop_p=0.2, seed=5)
+run(12288, 80, 4096, splits=1)
