@@ -58,6 +58,7 @@ typedef struct pb2_gemm_desc {
     int block_n;          /* N tile, multiple of 16 in [16,256]; 0 = choose */
     int splits;           /* split-K factor; 0 = choose */
     int stages;           /* TMA ring depth; 0 = choose */
+    int reduce_mode;      /* split-K reduction: 0 = choose, 1 = global scratch workspace, 2 = cluster / DSMEM */
 } pb2_gemm_desc;
 
 size_t pb2_gemm_workspace_bytes(void);
@@ -168,6 +169,50 @@ int pb2_adam_step(const pb2_adam_tensor* table_dev, int n_tensors, int total_til
                   float lr, float beta1, float beta2, float eps, float weight_decay, int step, float max_norm,
                   float grad_scale, cudaStream_t stream);
 int pb2_refresh_shadows(const pb2_adam_tensor* table_dev, int n_tensors, int total_tiles, cudaStream_t stream);
+
+/* ---- whole encoder layer: one host call launches the layer's kernel sequence -----------------
+ * The framework's host-side critical path is the per-kernel launch cost:
+ * a 75-token micro-batch gives each kernel 5-20 us of GPU work.  These two entry points run the
+ * forward (7 launches) and backward (8 launches) of a post-norm Transformer encoder layer from C++,
+ * so the Python layer pays one call per layer per pass.  All buffers are the caller's.
+ * Forward:  qkv = x Wqkv^T + b;  a = attn(qkv);  o = drop(a Wo^T + b);  x1 = LN1(x + o);
+ *           h = drop(relu(x1 W1^T + b));  f = drop(h W2^T + b);  y = LN2(x1 + f)
+ * Backward: the reverse, with dgrad GEMMs against the transposed weight shadows, and every wgrad
+ *           operand transposed into the caller's stacked K-major stash at column `stash_off`
+ *           (the wgrad GEMMs themselves run once per mini-batch, see pb2_gemm_bf16).
+ * Reference counterpart: nn.TransformerEncoderLayer forward/backward (main.py:148); SURVEY.md K2-K6. */
+typedef struct pb2_encoder_layer {
+    int T, NB, S, E, heads, FF;      /* T = S * NB tokens (row = s * NB + n) */
+    int causal;
+    float drop_p, eps;
+    unsigned long long seed;
+    /* bf16 weight shadows [out, in] and transposed shadows [in, ld >= out] */
+    const void *w_qkv, *w_o, *w_1, *w_2;
+    const void *wt_qkv, *wt_o, *wt_1, *wt_2;
+    long long ldt_qkv, ldt_o, ldt_1, ldt_2;
+    /* fp32 biases and LayerNorm parameters */
+    const float *b_qkv, *b_o, *b_1, *b_2, *g1, *be1, *g2, *be2;
+    /* forward activations (bf16 unless noted) */
+    const void* x;                   /* [T, E] */
+    void *qkv, *a, *o, *x1, *hmid, *f, *y;   /* [T,3E] [T,E] [T,E] [T,E] [T,FF] [T,E] [T,E] */
+    float *mean1, *rstd1, *mean2, *rstd2;    /* [T] each */
+    /* backward */
+    const void* dy;                  /* [T, E] */
+    void* dx;                        /* [T, E] */
+    void *dr2, *df, *dz1, *dx1, *dr1, *do_, *da, *dqkv;   /* scratch: [T,E] [T,E] [T,FF] [T,E] [T,E] [T,E] [T,E] [T,3E] */
+    float *dg1, *dbe1, *dg2, *dbe2;  /* LayerNorm gradients (accumulated) */
+    float *db_qkv, *db_o, *db_1, *db_2;       /* bias gradients (accumulated) */
+    /* stacked wgrad operands: x^T [in, ld] and dy^T [out, ld] per linear, written at column stash_off */
+    void *xt_qkv, *dyt_qkv, *xt_o, *dyt_o, *xt_1, *dyt_1, *xt_2, *dyt_2;
+    long long ld_stash_qkv, ld_stash_o, ld_stash_1, ld_stash_2;
+    int stash_off_qkv, stash_off_o, stash_off_1, stash_off_2;
+    /* split-K workspace of pb2_gemm_workspace_bytes() bytes (see pb2_gemm_bf16) */
+    void* workspace;
+    size_t workspace_bytes;
+} pb2_encoder_layer;
+
+int pb2_encoder_layer_fwd(const pb2_encoder_layer* L, cudaStream_t stream);
+int pb2_encoder_layer_bwd(const pb2_encoder_layer* L, cudaStream_t stream);
 
 #ifdef __cplusplus
 }

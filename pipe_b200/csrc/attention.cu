@@ -35,7 +35,7 @@ __device__ __forceinline__ void load_head(const __nv_bfloat16* __restrict__ base
     for (int t = threadIdx.x; t < S * vec_per_row; t += blockDim.x) {
         const int s = t / vec_per_row, v = t % vec_per_row;
         const uint4 raw = *reinterpret_cast<const uint4*>(base + (static_cast<size_t>(s) * NB + n) * ld + v * 8);
-        uint32_t* d = reinterpret_cast<uint32_t*>(dst + s * dpad + v * 8);
+        uint32_t* d = reinterpret_cast<uint32_t*>(dst + s * dpad + v * 8);     // rows are only 4-byte aligned
         d[0] = raw.x; d[1] = raw.y; d[2] = raw.z; d[3] = raw.w;
     }
 }
@@ -84,7 +84,7 @@ __device__ __forceinline__ float keep_scale(const CounterRng& ph, const AttnShap
 __global__ void __launch_bounds__(kAttnThreads)
 attn_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out, const AttnShape a) {
     extern __shared__ __align__(16) uint8_t smem[];
-    const int S = a.S, D = a.D, dpad = D + 8, spad = S + 1;
+    const int S = a.S, D = a.D, dpad = D + 2, spad = S + 1;   // odd word stride: lanes on different rows hit different banks
     __nv_bfloat16* q = reinterpret_cast<__nv_bfloat16*>(smem);
     __nv_bfloat16* k = q + S * dpad;
     __nv_bfloat16* v = k + S * dpad;
@@ -135,13 +135,14 @@ __global__ void __launch_bounds__(kAttnThreads)
 attn_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* __restrict__ dout,
                 __nv_bfloat16* __restrict__ dqkv, const AttnShape a) {
     extern __shared__ __align__(16) uint8_t smem[];
-    const int S = a.S, D = a.D, dpad = D + 8, spad = S + 1;
+    const int S = a.S, D = a.D, dpad = D + 2, spad = S + 1;   // odd word stride: lanes on different rows hit different banks
     __nv_bfloat16* q = reinterpret_cast<__nv_bfloat16*>(smem);
     __nv_bfloat16* k = q + S * dpad;
     __nv_bfloat16* v = k + S * dpad;
     __nv_bfloat16* dO = v + S * dpad;
     float* P = reinterpret_cast<float*>(dO + S * dpad);     // softmax probabilities (pre-dropout)
     float* dS = P + S * spad;                               // first dP (post-dropout grads), then dS
+    uint8_t* keep = reinterpret_cast<uint8_t*>(dS + S * spad);   // dropout keep mask, one byte per (i, j)
     const int n = blockIdx.x / a.H, h = blockIdx.x % a.H;
     const long long ld = 3LL * a.E;
 
@@ -158,8 +159,11 @@ attn_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* __re
     for (int p = threadIdx.x; p < S * S; p += blockDim.x) {
         const int i = p / S, j = p % S;
         P[i * spad + j] = dot_bf16(q + i * dpad, k + j * dpad, D) * a.scale;
+        // the mask is generated once here; every later use reads the byte
+        const float ks = keep_scale(ph, a, thr, inv_keep, n, h, i, j);
+        keep[i * S + j] = ks != 0.f;
         // gradient w.r.t. the dropped-out probabilities, already mapped back through the mask
-        dS[i * spad + j] = dot_bf16(dO + i * dpad, v + j * dpad, D) * keep_scale(ph, a, thr, inv_keep, n, h, i, j);
+        dS[i * spad + j] = dot_bf16(dO + i * dpad, v + j * dpad, D) * ks;
     }
     __syncthreads();
     softmax_rows(P, S, spad, a.causal);
@@ -170,7 +174,7 @@ attn_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* __re
         const int j = p / (D / 2), c2 = p % (D / 2);
         float g0 = 0.f, g1 = 0.f;
         for (int i = 0; i < S; ++i) {
-            const float w = P[i * spad + j] * keep_scale(ph, a, thr, inv_keep, n, h, i, j);
+            const float w = keep[i * S + j] ? P[i * spad + j] * inv_keep : 0.f;
             const float2 d = __bfloat1622float2(reinterpret_cast<const __nv_bfloat162*>(dO + i * dpad)[c2]);
             g0 = fmaf(w, d.x, g0);
             g1 = fmaf(w, d.y, g1);
@@ -231,10 +235,10 @@ using namespace pb2;
 
 extern "C" int pb2_attention_fwd(const void* qkv, void* out, int NB, int S, int H, int D, int causal, float drop_p,
                                  unsigned long long seed, unsigned long long rng_stream, cudaStream_t stream) {
-    const size_t smem = static_cast<size_t>(3) * S * (D + 8) * 2 + static_cast<size_t>(S) * (S + 1) * 4;
+    const size_t smem = static_cast<size_t>(3) * S * (D + 2) * 2 + static_cast<size_t>(S) * (S + 1) * 4;
     if (attn_check("pb2_attention_fwd", NB, S, H, D, smem)) return -1;
     AttnShape a{NB, S, H, D, H * D, 1.f / sqrtf(static_cast<float>(D)), causal, drop_p, seed, rng_stream};
-    PB2_CUDA(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    if (ensure_max_smem(reinterpret_cast<const void*>(attn_fwd_kernel), 227 * 1024)) return -1;
     attn_fwd_kernel<<<NB * H, kAttnThreads, smem, stream>>>(static_cast<const __nv_bfloat16*>(qkv),
                                                             static_cast<__nv_bfloat16*>(out), a);
     PB2_LAUNCHED("attn_fwd_kernel");
@@ -244,10 +248,10 @@ extern "C" int pb2_attention_fwd(const void* qkv, void* out, int NB, int S, int 
 extern "C" int pb2_attention_bwd(const void* qkv, const void* dout, void* dqkv, int NB, int S, int H, int D,
                                  int causal, float drop_p, unsigned long long seed, unsigned long long rng_stream,
                                  cudaStream_t stream) {
-    const size_t smem = static_cast<size_t>(4) * S * (D + 8) * 2 + static_cast<size_t>(2) * S * (S + 1) * 4;
+    const size_t smem = static_cast<size_t>(4) * S * (D + 2) * 2 + static_cast<size_t>(2) * S * (S + 1) * 4 + static_cast<size_t>(S) * S + 16;
     if (attn_check("pb2_attention_bwd", NB, S, H, D, smem)) return -1;
     AttnShape a{NB, S, H, D, H * D, 1.f / sqrtf(static_cast<float>(D)), causal, drop_p, seed, rng_stream};
-    PB2_CUDA(cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    if (ensure_max_smem(reinterpret_cast<const void*>(attn_bwd_kernel), 227 * 1024)) return -1;
     attn_bwd_kernel<<<NB * H, kAttnThreads, smem, stream>>>(static_cast<const __nv_bfloat16*>(qkv),
                                                             static_cast<const __nv_bfloat16*>(dout),
                                                             static_cast<__nv_bfloat16*>(dqkv), a);

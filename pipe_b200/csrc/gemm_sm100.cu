@@ -71,6 +71,8 @@ struct GemmArgs {
     float* sumsq;                    // optional: += sum of squares of what was written
     float* partials;
     unsigned int* counters;
+    int cluster_reduce;              // splits CTAs of a tile form a cluster and reduce through DSMEM
+    int local_chunks;                // 16-column chunks each cluster rank owns (ceil(n_chunks / splits))
     unsigned long long* debug_ts;    // optional: per-CTA phase timestamps (globaltimer ns), 8 per CTA
 };
 
@@ -269,6 +271,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                 tma_load_2d(sb, &tmap_b, &ctl->full[s], k_elem, n0, kEvictLast);
             }
         }
+        __syncwarp();       // reconverge before any warp-aligned barrier below
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
         const uint32_t idesc = umma_idesc_bf16(kBlockM, g.block_n);
@@ -293,20 +296,79 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
             __syncwarp();
         }
     } else {
-        // ===================== epilogue (warps 2..9) =====================
-        const int quarter = warp & 3;                 // TMEM lane quarter this warp may read
-        const int half = (warp - 2) >> 2;             // which of the two warps of that quarter
-        const int m_local = quarter * 32 + lane;
-        const int m_glob = m0 + m_local;
-        const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
-        const int ep_tid = threadIdx.x - 64;          // 0..255
-
+        // ===================== epilogue (warps 2..9): wait for the accumulator =====================
         mbar_wait(&ctl->tmem_full, 0);
         tc_fence_after();
-        if (ep_tid == 0) PB2_TS(4);
+        if (threadIdx.x == 64) PB2_TS(4);
+    }
 
-        const int tile = blockIdx.y * gridDim.x + blockIdx.x;
-        const size_t tile_elems = static_cast<size_t>(g.block_n) * kBlockM;
+    const bool is_epi = warp >= 2;
+    const int quarter = warp & 3;                 // TMEM lane quarter this warp may read
+    const int half = is_epi ? (warp - 2) >> 2 : 0;  // which of the two warps of that quarter
+    const int m_local = quarter * 32 + lane;
+    const int m_glob = m0 + m_local;
+    const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
+    const int ep_tid = threadIdx.x - 64;          // 0..255 for epilogue threads
+    const int tile = blockIdx.y * gridDim.x + blockIdx.x;
+    const size_t tile_elems = static_cast<size_t>(g.block_n) * kBlockM;
+    const int n_chunks = g.block_n >> 4;
+
+    if (g.cluster_reduce) {
+        // ---- split-K reduction inside the cluster, through distributed shared memory ----
+        // Chunk k (16 accumulator columns) is owned by cluster rank k % splits.  Every CTA sends its
+        // partial of each foreign chunk into the owner's staging area (the now idle TMA ring):
+        //   staging[src rank][owner-local chunk][column 0..15][row 0..127]  fp32
+        // and each owner then finishes only its own chunks, so the fix-up and the epilogue are
+        // spread over all CTAs of the tile and no partial tile ever goes to global memory.
+        const uint32_t rank = cluster_ctarank();
+        cluster_sync_all();                                   // (1) every CTA's ring is idle
+        if (is_epi) {
+            const uint32_t stage_base = smem_u32(smem);
+            for (int k = half; k < n_chunks; k += 2) {
+                const uint32_t owner = static_cast<uint32_t>(k % g.splits);
+                if (owner == rank) continue;
+                uint32_t r[16];
+                tmem_ld_32x16(t_lane + k * 16, r);
+                tmem_ld_wait();
+                const uint32_t local = stage_base +
+                    (((rank * g.local_chunks + (k / g.splits)) * 16) * kBlockM + m_local) * 4u;
+                const uint32_t remote = dsmem_addr(local, owner);
+#pragma unroll
+                for (int j = 0; j < 16; ++j) dsmem_st_f32(remote + j * kBlockM * 4, __uint_as_float(r[j]));
+            }
+        }
+        cluster_sync_all();                                   // (2) all partials delivered
+        if (is_epi) {
+            EpiCtx e{CounterRng(g.seed), static_cast<uint32_t>(fminf(g.drop_p, 0.999999f) * 4294967296.0f),
+                     g.drop_p > 0.f ? 1.f / (1.f - g.drop_p) : 1.f, 0.f, m_glob < g.M};
+            if (g.bias && g.bias_along_m && e.row_ok) e.bias_m = g.bias[m_glob];
+            float ss = 0.f;
+            const float* staging = reinterpret_cast<const float*>(smem);
+            for (int kl = half; kl < g.local_chunks; kl += 2) {
+                const int k = kl * g.splits + static_cast<int>(rank);
+                if (k >= n_chunks) break;
+                uint32_t r[16];
+                tmem_ld_32x16(t_lane + k * 16, r);
+                tmem_ld_wait();
+                float v[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
+                for (int src = 0; src < g.splits; ++src) {
+                    if (src == static_cast<int>(rank)) continue;
+                    const float* p = staging + ((static_cast<size_t>(src) * g.local_chunks + kl) * 16) * kBlockM + m_local;
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) v[j] += p[j * kBlockM];
+                }
+                if (n0 + k * 16 < g.N) epilogue_chunk(g, e, v, m_glob, n0 + k * 16, ss);
+            }
+            if (g.sumsq) {
+                ss = warp_sum(ss);
+                if (lane == 0) atomicAdd(g.sumsq, ss);
+            }
+            if (ep_tid == 0) PB2_TS(5);
+            tc_fence_before();
+        }
+    } else if (is_epi) {
         bool last = true;
         if (g.splits > 1) {
             // partial tile layout [column][row]: a warp writes 32 consecutive floats per column
@@ -337,7 +399,6 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
             float ss = 0.f;
             const float* others = g.partials + static_cast<size_t>(tile) * g.splits * tile_elems + m_local;
             for (int c = half * 16; c < g.block_n; c += 32) {
-                if (ep_tid == 0 && c < 64) PB2_TS(7 + (c >> 4) * 2);
                 uint32_t r[16];
                 tmem_ld_32x16(t_lane + c, r);
                 tmem_ld_wait();
@@ -394,7 +455,7 @@ static unsigned long long* g_debug_ts = nullptr;
 extern "C" void pb2_debug_gemm_timestamps(unsigned long long* buf) { g_debug_ts = buf; }
 
 static int gemm_launch(const pb2_gemm_desc* d, float* partials, unsigned int* counters, size_t partial_bytes,
-                       size_t counter_slots, cudaStream_t stream) {
+                       size_t counter_slots, cudaStream_t stream, bool force_scratch = false) {
     if (d->M <= 0 || d->N <= 0 || d->K <= 0) {
         set_error("pb2_gemm: non-positive shape M=%d N=%d K=%d", d->M, d->N, d->K);
         return -1;
@@ -431,15 +492,45 @@ static int gemm_launch(const pb2_gemm_desc* d, float* partials, unsigned int* co
 
     int splits = d->splits;
     if (splits <= 0) {
-        // enough CTAs for ~2 per SM-worth of memory parallelism, but keep >= 4 k-blocks per split
+        // aim for roughly one CTA per SM (a CTA streams ~130 GB/s, so ~64 already saturate HBM), keep
+        // at least 4 k-blocks per split, and stay within one cluster (<= 8) so the reduction can
+        // run through distributed shared memory
         splits = 1;
-        while (tiles * splits < 148 && g.k_blocks_total / (splits * 2) >= 4 && splits < 16) splits *= 2;
+        while (tiles * splits * 2 <= 160 && g.k_blocks_total / (splits * 2) >= 4 && splits < 8) splits *= 2;
     }
     if (splits > g.k_blocks_total) splits = g.k_blocks_total;
     g.k_blocks_per_split = (g.k_blocks_total + splits - 1) / splits;
     splits = (g.k_blocks_total + g.k_blocks_per_split - 1) / g.k_blocks_per_split;
     g.splits = splits;
-    if (splits > 1) {
+
+    const int stage_bytes = (kBlockM + bn) * kBlockK * 2;
+    int stages = (200 * 1024) / stage_bytes;
+    if (tiles * splits > 148) {
+        // more CTAs than SMs: size the ring so two CTAs fit per SM and both waves stream at once
+        const int two = (110 * 1024) / stage_bytes;
+        if (two >= 2) stages = two;
+    }
+    if (stages > kMaxStages) stages = kMaxStages;
+    if (d->stages > 0 && d->stages < stages) stages = d->stages;
+    if (stages > g.k_blocks_per_split) stages = g.k_blocks_per_split;
+    if (stages < 1) stages = 1;
+    g.stages = stages;
+    g.tmem_cols = next_pow2_cols(bn);
+
+    // split-K reduction: inside a cluster through DSMEM when the splits fit one (2..8 CTAs) and the
+    // staging area fits the idle TMA ring; otherwise through the global scratch workspace
+    const int n_chunks = bn / 16;
+    g.local_chunks = (n_chunks + splits - 1) / splits;
+    const size_t staging = static_cast<size_t>(splits) * g.local_chunks * 16 * kBlockM * sizeof(float);
+    const bool pow2 = (splits & (splits - 1)) == 0;
+    g.cluster_reduce = (splits > 1 && splits <= 8 && pow2 && !force_scratch && d->reduce_mode != 1 &&
+                        staging <= static_cast<size_t>(stages) * stage_bytes) ? 1 : 0;
+    if (d->reduce_mode == 2 && !g.cluster_reduce && splits > 1) {
+        set_error("pb2_gemm: cluster reduction requested but not possible (splits=%d, staging %zu B, ring %d B)",
+                  splits, staging, stages * stage_bytes);
+        return -1;
+    }
+    if (splits > 1 && !g.cluster_reduce) {
         const size_t need = static_cast<size_t>(tiles) * splits * bn * kBlockM * sizeof(float);
         if (need > partial_bytes || static_cast<size_t>(tiles) > counter_slots) {
             set_error("pb2_gemm: split-K scratch too small (need %zu B partials for %lld tiles x %d splits, have %zu B / %zu counters)",
@@ -449,15 +540,6 @@ static int gemm_launch(const pb2_gemm_desc* d, float* partials, unsigned int* co
         g.partials = partials;
         g.counters = counters;
     }
-
-    const int stage_bytes = (kBlockM + bn) * kBlockK * 2;
-    int stages = (200 * 1024) / stage_bytes;
-    if (stages > kMaxStages) stages = kMaxStages;
-    if (d->stages > 0 && d->stages < stages) stages = d->stages;
-    if (stages > g.k_blocks_per_split) stages = g.k_blocks_per_split;
-    if (stages < 1) stages = 1;
-    g.stages = stages;
-    g.tmem_cols = next_pow2_cols(bn);
 
     g.out = d->out; g.ld_out = d->ld_out; g.out_f32 = d->out_f32; g.transpose_out = d->transpose_out;
     g.bias = d->bias; g.bias_along_m = d->bias_along_m; g.relu = d->relu;
@@ -473,14 +555,23 @@ static int gemm_launch(const pb2_gemm_desc* d, float* partials, unsigned int* co
     if (make_tmap_bf16_2d(&tb, d->b, d->N, d->K, d->ldb, bn, kBlockK)) return -1;
 
     const size_t smem = static_cast<size_t>(stages) * stage_bytes + sizeof(SmemCtl) + 1024;
-    static int max_smem_set = 0;
-    if (!max_smem_set) {
-        // one attribute value for every launch keeps this call out of the hot path
+    if (ensure_max_smem(reinterpret_cast<const void*>(gemm_bf16_tn_kernel), 227 * 1024)) return -1;
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3(m_tiles, n_tiles, splits);
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    if (g.cluster_reduce) {
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 1;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = splits;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
     }
-    PB2_CUDA(cudaFuncSetAttribute(gemm_bf16_tn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    (void)max_smem_set;
-    dim3 grid(m_tiles, n_tiles, splits);
-    gemm_bf16_tn_kernel<<<grid, kThreads, smem, stream>>>(ta, tb, g);
+    PB2_CUDA(cudaLaunchKernelEx(&cfg, gemm_bf16_tn_kernel, ta, tb, g));
     PB2_LAUNCHED("gemm_bf16_tn_kernel");
     return 0;
 }
@@ -569,7 +660,7 @@ extern "C" int pb2_gemm_bf16_noalloc(const pb2_gemm_desc* d, cudaStream_t stream
     // the counters must be zero when the kernel starts, whatever the last call (or a failed one) left
     PB2_CUDA(cudaMemsetAsync(counters, 0, PB2_GEMM_COUNTER_BYTES, stream));
     int rc = gemm_launch(d, partials, counters, PB2_GEMM_STATIC_SCRATCH_BYTES,
-                         PB2_GEMM_COUNTER_BYTES / sizeof(unsigned int), stream);
+                         PB2_GEMM_COUNTER_BYTES / sizeof(unsigned int), stream, /*force_scratch=*/true);
     if (rc) {
         // make the limit explicit for the one failure mode that is specific to this entry point
         const char* why = pb2_last_error();

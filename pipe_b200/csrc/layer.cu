@@ -1,0 +1,93 @@
+// Host-side executor of one Transformer encoder layer: the launch sequence of the forward and
+// of the backward, issued from C++ so the Python layer pays one call per layer per pass instead of
+// one per kernel.  Pure orchestration: every kernel it launches is a public entry point of this
+// library (pb2_gemm_bf16, pb2_attention_*, pb2_add_layernorm_*, pb2_transpose_multi).
+//
+// Reference counterpart: the Python-level op sequence of nn.TransformerEncoderLayer
+// (main.py:148) as driven by the autograd engine; SURVEY.md §3.2 "GPU hot path", §7.4 item 2.
+#include <string.h>
+
+#include "common.cuh"
+#include "pipe_b200.h"
+
+namespace {
+
+struct Lin {
+    const void* w;        // A operand: [M rows, K], row stride lda
+    long long lda;
+    int M, K;
+};
+
+int linear(const pb2_encoder_layer* L, const Lin& w, const void* act, int T, void* out, const float* bias, int relu,
+           float drop_p, unsigned long long rng_stream, const void* mask_src, float mask_scale, const void* addend,
+           cudaStream_t stream) {
+    // out[T, M] = act[T, K] * w[M, K]^T  (weights on the UMMA M axis, transposed store)
+    pb2_gemm_desc d;
+    memset(&d, 0, sizeof(d));
+    d.a = w.w; d.lda = w.lda; d.M = w.M; d.K = w.K;
+    d.b = act; d.ldb = w.K; d.N = T;
+    d.out = out; d.ld_out = w.M; d.transpose_out = 1;
+    d.bias = bias; d.bias_along_m = 1; d.relu = relu;
+    d.drop_p = drop_p; d.seed = L->seed; d.rng_stream = rng_stream;
+    d.mask_src = mask_src; d.mask_scale = mask_scale; d.addend = addend;
+    d.alpha = 1.f;
+    return pb2_gemm_bf16(&d, L->workspace, L->workspace_bytes, stream);
+}
+
+}  // namespace
+
+extern "C" int pb2_encoder_layer_fwd(const pb2_encoder_layer* L, cudaStream_t stream) {
+    if (!L) { pb2::set_error("pb2_encoder_layer_fwd: null descriptor"); return -1; }
+    const int T = L->T, E = L->E, FF = L->FF;
+    const float p = L->drop_p;
+    if (T != L->S * L->NB || E % L->heads) { pb2::set_error("pb2_encoder_layer_fwd: inconsistent shape"); return -1; }
+
+    if (linear(L, Lin{L->w_qkv, E, 3 * E, E}, L->x, T, L->qkv, L->b_qkv, 0, 0.f, 0, nullptr, 0.f, nullptr, stream)) return -1;
+    if (pb2_attention_fwd(L->qkv, L->a, L->NB, L->S, L->heads, E / L->heads, L->causal, p, L->seed, 0, stream)) return -1;
+    if (linear(L, Lin{L->w_o, E, E, E}, L->a, T, L->o, L->b_o, 0, p, 1, nullptr, 0.f, nullptr, stream)) return -1;
+    if (pb2_add_layernorm_fwd(L->x, L->o, L->g1, L->be1, L->x1, L->mean1, L->rstd1, T, E, L->eps, stream)) return -1;
+    if (linear(L, Lin{L->w_1, E, FF, E}, L->x1, T, L->hmid, L->b_1, 1, p, 2, nullptr, 0.f, nullptr, stream)) return -1;
+    if (linear(L, Lin{L->w_2, FF, E, FF}, L->hmid, T, L->f, L->b_2, 0, p, 3, nullptr, 0.f, nullptr, stream)) return -1;
+    if (pb2_add_layernorm_fwd(L->x1, L->f, L->g2, L->be2, L->y, L->mean2, L->rstd2, T, E, L->eps, stream)) return -1;
+    return 0;
+}
+
+extern "C" int pb2_encoder_layer_bwd(const pb2_encoder_layer* L, cudaStream_t stream) {
+    if (!L) { pb2::set_error("pb2_encoder_layer_bwd: null descriptor"); return -1; }
+    const int T = L->T, E = L->E, FF = L->FF;
+    const float p = L->drop_p;
+    const float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
+
+    // y = LN2(x1 + drop(f))
+    if (pb2_add_layernorm_bwd(L->dy, L->x1, L->f, L->g2, L->mean2, L->rstd2, L->dr2, L->df, L->dg2, L->dbe2, T, E, p,
+                              L->seed, 3, stream)) return -1;
+    // through linear2, then ReLU + dropout (mask recovered from the saved activation)
+    if (linear(L, Lin{L->wt_2, L->ldt_2, FF, E}, L->df, T, L->dz1, nullptr, 0, 0.f, 0, L->hmid, inv_keep, nullptr, stream)) return -1;
+    // through linear1, plus the residual branch
+    if (linear(L, Lin{L->wt_1, L->ldt_1, E, FF}, L->dz1, T, L->dx1, nullptr, 0, 0.f, 0, nullptr, 0.f, L->dr2, stream)) return -1;
+    // x1 = LN1(x + drop(o))
+    if (pb2_add_layernorm_bwd(L->dx1, L->x, L->o, L->g1, L->mean1, L->rstd1, L->dr1, L->do_, L->dg1, L->dbe1, T, E, p,
+                              L->seed, 1, stream)) return -1;
+    if (linear(L, Lin{L->wt_o, L->ldt_o, E, E}, L->do_, T, L->da, nullptr, 0, 0.f, 0, nullptr, 0.f, nullptr, stream)) return -1;
+    if (pb2_attention_bwd(L->qkv, L->da, L->dqkv, L->NB, L->S, L->heads, E / L->heads, L->causal, p, L->seed, 0, stream)) return -1;
+    if (linear(L, Lin{L->wt_qkv, L->ldt_qkv, E, 3 * E}, L->dqkv, T, L->dx, nullptr, 0, 0.f, 0, nullptr, 0.f, L->dr1, stream)) return -1;
+
+    // stack every wgrad operand (and column-sum the bias gradients) in one launch
+    pb2_transpose_jobs jobs;
+    memset(&jobs, 0, sizeof(jobs));
+    auto add = [&](const void* src, int C, void* dst_base, long long ld_dst, int off, float* colsum) {
+        pb2_transpose_job& j = jobs.job[jobs.count++];
+        j.src = src; j.ld_src = C; j.R = T; j.C = C;
+        j.dst = static_cast<char*>(dst_base) + static_cast<size_t>(off) * 2; j.ld_dst = ld_dst;
+        j.colsum = colsum; j.scale = 1.f;
+    };
+    add(L->x, E, L->xt_qkv, L->ld_stash_qkv, L->stash_off_qkv, nullptr);
+    add(L->dqkv, 3 * E, L->dyt_qkv, L->ld_stash_qkv, L->stash_off_qkv, L->db_qkv);
+    add(L->a, E, L->xt_o, L->ld_stash_o, L->stash_off_o, nullptr);
+    add(L->do_, E, L->dyt_o, L->ld_stash_o, L->stash_off_o, L->db_o);
+    add(L->x1, E, L->xt_1, L->ld_stash_1, L->stash_off_1, nullptr);
+    add(L->dz1, FF, L->dyt_1, L->ld_stash_1, L->stash_off_1, L->db_1);
+    add(L->hmid, FF, L->xt_2, L->ld_stash_2, L->stash_off_2, nullptr);
+    add(L->df, E, L->dyt_2, L->ld_stash_2, L->stash_off_2, L->db_2);
+    return pb2_transpose_multi(&jobs, stream);
+}

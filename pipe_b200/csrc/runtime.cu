@@ -39,8 +39,42 @@ EncodeTiledFn get_encode_tiled() {
     return fn;
 }
 
+// A tensor map is a pure function of (address, shape, stride, box): weights hit the cache every
+// time, and activations mostly do too because the caching allocator hands the same blocks back.
+// Direct-mapped, per host thread (no locking on the launch path).
+namespace {
+struct TmapKey {
+    const void* ptr;
+    uint64_t rows, cols, ld;
+    uint32_t box_rows, box_cols;
+    bool operator==(const TmapKey& o) const {
+        return ptr == o.ptr && rows == o.rows && cols == o.cols && ld == o.ld && box_rows == o.box_rows &&
+               box_cols == o.box_cols;
+    }
+};
+struct TmapSlot {
+    TmapKey key;
+    CUtensorMap map;
+    bool valid;
+};
+constexpr size_t kTmapSlots = 8192;
+thread_local TmapSlot* t_tmap_cache = nullptr;
+inline size_t tmap_hash(const TmapKey& k) {
+    uint64_t h = reinterpret_cast<uint64_t>(k.ptr) * 0x9E3779B97F4A7C15ull;
+    h ^= (k.rows * 0xC2B2AE3D27D4EB4Full) ^ (k.cols << 17) ^ (k.ld << 29) ^ (static_cast<uint64_t>(k.box_rows) << 47);
+    return static_cast<size_t>((h >> 20) % kTmapSlots);
+}
+}  // namespace
+
 int make_tmap_bf16_2d(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld_elems,
                       uint32_t box_rows, uint32_t box_cols) {
+    if (!t_tmap_cache) t_tmap_cache = new TmapSlot[kTmapSlots]();
+    const TmapKey key{ptr, rows, cols, ld_elems, box_rows, box_cols};
+    TmapSlot& slot = t_tmap_cache[tmap_hash(key)];
+    if (slot.valid && slot.key == key) {
+        *out = slot.map;
+        return 0;
+    }
     EncodeTiledFn enc = get_encode_tiled();
     if (!enc) return -1;
     cuuint64_t dims[2] = {cols, rows};                       // innermost first
@@ -55,6 +89,25 @@ int make_tmap_bf16_2d(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t
                   (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)ld_elems, box_rows, box_cols);
         return -1;
     }
+    slot.key = key;
+    slot.map = *out;
+    slot.valid = true;
+    return 0;
+}
+
+// cudaFuncSetAttribute(max dynamic smem) once per (kernel, device) instead of once per launch.
+int ensure_max_smem(const void* func, int bytes) {
+    struct Seen { const void* f; int dev; };
+    thread_local Seen seen[32];
+    thread_local int n_seen = 0;
+    int dev = 0;
+    if (check_cuda(cudaGetDevice(&dev), "cudaGetDevice")) return -1;
+    for (int i = 0; i < n_seen; ++i)
+        if (seen[i].f == func && seen[i].dev == dev) return 0;
+    if (check_cuda(cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes),
+                   "cudaFuncSetAttribute(MaxDynamicSharedMemorySize)"))
+        return -1;
+    if (n_seen < 32) seen[n_seen++] = Seen{func, dev};
     return 0;
 }
 

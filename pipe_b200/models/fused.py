@@ -31,8 +31,11 @@ from typing import Any, Dict, List, Optional, Tuple
 import torch
 from torch import Tensor, nn
 
+import ctypes
+
+from ..ops import _lib
 from ..ops import functional as F2
-from ..ops.gemm import gemm_nt
+from ..ops.gemm import gemm_nt, workspace
 from ..ops.wgrad import LinearGrad, ensure_grad
 
 __all__ = ["FusedEncoder", "FusedEncoderLayer", "FusedDecoder", "Shadow"]
@@ -126,7 +129,9 @@ class _FusedBase(nn.Module):
 
     def _apply(self, fn, *args, **kwargs):
         out = super()._apply(fn, *args, **kwargs)
-        # masters may have been replaced / moved: re-bind shadows and wgrad stashes
+        # masters may have been replaced / moved: re-bind shadows and wgrad stashes, drop caches
+        self.__dict__.pop("_pb2_params", None)
+        self.__dict__.pop("_pb2_desc", None)
         self._rebind()
         return out
 
@@ -138,76 +143,97 @@ class _FusedBase(nn.Module):
 # encoder layer
 # ======================================================================================
 class _EncoderLayerFn(torch.autograd.Function):
+    """Forward and backward of the whole layer, each one call into the C++ layer executor
+    (``csrc/layer.cu``): 7 and 8 kernel launches respectively, no Python between them."""
+
     @staticmethod
     def forward(ctx, x: Tensor, layer: "FusedEncoderLayer", *params: Tensor) -> Tensor:  # type: ignore[override]
         S, NB, E = x.shape
         T = S * NB
+        FF = layer.linear1.weight.size(0)
         x2 = x.contiguous().view(T, E)
         if x2.dtype != torch.bfloat16:
             x2 = x2.to(torch.bfloat16)
         p = layer.dropout if layer.training else 0.0
         seed = F2.draw_seed() if p > 0 else 0
-        at, l1, l2, n1, n2 = layer.self_attn, layer.linear1, layer.linear2, layer.norm1, layer.norm2
+        dev = x2.device
 
-        w_qkv, _ = layer._sh("qkv")
-        w_o, _ = layer._sh("o")
-        w_1, _ = layer._sh("l1")
-        w_2, _ = layer._sh("l2")
+        # one allocation for every saved activation: qkv | a | o | x1 | hmid | f
+        widths = (3 * E, E, E, E, FF, E)
+        act = torch.empty(T * sum(widths), dtype=torch.bfloat16, device=dev)
+        stats = torch.empty(4 * T, dtype=torch.float32, device=dev)
+        y = torch.empty((S, NB, E), dtype=torch.bfloat16, device=dev)
 
-        qkv = gemm_nt(w_qkv, x2, transpose_out=True, bias=at.in_proj_bias, bias_along_m=True)
-        a = F2.attention_fwd(qkv, NB, S, layer.nhead, causal=layer.causal, drop_p=p, seed=seed, rng_stream=0)
-        o = gemm_nt(w_o, a, transpose_out=True, bias=at.out_proj.bias, bias_along_m=True,
-                    drop_p=p, seed=seed, rng_stream=1)
-        x1, mean1, rstd1 = F2.add_layernorm_fwd(x2, o, n1.weight, n1.bias, n1.eps)
-        hmid = gemm_nt(w_1, x1, transpose_out=True, bias=l1.bias, bias_along_m=True, relu=True,
-                       drop_p=p, seed=seed, rng_stream=2)
-        f = gemm_nt(w_2, hmid, transpose_out=True, bias=l2.bias, bias_along_m=True,
-                    drop_p=p, seed=seed, rng_stream=3)
-        y, mean2, rstd2 = F2.add_layernorm_fwd(x1, f, n2.weight, n2.bias, n2.eps)
+        d = layer._desc(dev)
+        d.T, d.NB, d.S = T, NB, S
+        d.drop_p, d.seed = p, seed
+        d.x, d.y = x2.data_ptr(), y.data_ptr()
+        base, at = act.data_ptr(), 0
+        for name, w in zip(("qkv", "a", "o", "x1", "hmid", "f"), widths):
+            setattr(d, name, base + at * 2)
+            at += T * w
+        sb = stats.data_ptr()
+        d.mean1, d.rstd1, d.mean2, d.rstd2 = sb, sb + 4 * T, sb + 8 * T, sb + 12 * T
+        stream = _lib.raw_stream(dev)
+        ws = workspace(dev, stream)
+        d.workspace, d.workspace_bytes = ws.data_ptr(), ws.numel()
+        with _lib.on_device(dev):
+            rc = _lib.load().pb2_encoder_layer_fwd(ctypes.byref(d), ctypes.c_void_p(stream))
+        _lib.check(rc, "pb2_encoder_layer_fwd")
 
         ctx.layer = layer
-        ctx.meta = (S, NB, E, p, seed)
-        ctx.save_for_backward(x2, qkv, a, o, x1, mean1, rstd1, hmid, f, mean2, rstd2)
-        return y.view(S, NB, E)
+        ctx.meta = (S, NB, E, FF, p, seed)
+        ctx.save_for_backward(x2, act, stats)
+        return y
 
     @staticmethod
     def backward(ctx, dy: Tensor):  # type: ignore[override]
         layer: FusedEncoderLayer = ctx.layer
-        S, NB, E, p, seed = ctx.meta
+        S, NB, E, FF, p, seed = ctx.meta
         T = S * NB
-        x2, qkv, a, o, x1, mean1, rstd1, hmid, f, mean2, rstd2 = ctx.saved_tensors
-        at, l1, l2, n1, n2 = layer.self_attn, layer.linear1, layer.linear2, layer.norm1, layer.norm2
-        inv_keep = 1.0 / (1.0 - p) if p > 0 else 1.0
+        x2, act, stats = ctx.saved_tensors
+        dev = x2.device
         dy2 = dy.contiguous().view(T, E)
         if dy2.dtype != torch.bfloat16:
             dy2 = dy2.to(torch.bfloat16)
+        at_, l1, l2, n1, n2 = layer.self_attn, layer.linear1, layer.linear2, layer.norm1, layer.norm2
 
-        _, wt_qkv = layer._sh("qkv")
-        _, wt_o = layer._sh("o")
-        _, wt_1 = layer._sh("l1")
-        _, wt_2 = layer._sh("l2")
-        H = l1.weight.size(0)
+        stream = _lib.raw_stream(dev)
+        # scratch: dr2 | df | dz1 | dx1 | dr1 | do | da | dqkv
+        widths = (E, E, FF, E, E, E, E, 3 * E)
+        tmp = torch.empty(T * sum(widths), dtype=torch.bfloat16, device=dev)
+        dx = torch.empty((S, NB, E), dtype=torch.bfloat16, device=dev)
 
-        # y = LN2(x1 + dropout(ffn))
-        dr2, df = F2.add_layernorm_bwd(dy2, x1, f, n2.weight, mean2, rstd2, ensure_grad(n2.weight),
-                                       ensure_grad(n2.bias), want_dh=True, drop_p=p, seed=seed, rng_stream=3)
-        # through linear2, then ReLU + dropout (mask recovered from the saved activation)
-        dz1 = gemm_nt(wt_2[:, :E], df, transpose_out=True, mask_src=hmid, mask_scale=inv_keep)
-        # through linear1, plus the residual branch
-        dx1 = gemm_nt(wt_1[:, :H], dz1, transpose_out=True, addend=dr2)
-        # x1 = LN1(x + dropout(attn_out))
-        dr1, do = F2.add_layernorm_bwd(dx1, x2, o, n1.weight, mean1, rstd1, ensure_grad(n1.weight),
-                                       ensure_grad(n1.bias), want_dh=True, drop_p=p, seed=seed, rng_stream=1)
-        da = gemm_nt(wt_o[:, :E], do, transpose_out=True)
-        dqkv = F2.attention_bwd(qkv, da, NB, S, layer.nhead, causal=layer.causal, drop_p=p, seed=seed, rng_stream=0)
-        dx = gemm_nt(wt_qkv[:, : 3 * E], dqkv, transpose_out=True, addend=dr1)
-
-        # stack every wgrad operand of this layer (and the bias gradients) in one launch
-        jobs = (layer._lg("qkv").jobs(x2, dqkv) + layer._lg("o").jobs(a, do)
-                + layer._lg("l1").jobs(x1, dz1) + layer._lg("l2").jobs(hmid, df))
-        F2.transpose_multi(jobs)
-
-        return (dx.view(S, NB, E), None) + (None,) * (len(ctx.needs_input_grad) - 2)
+        d = layer._desc(dev)
+        d.T, d.NB, d.S = T, NB, S
+        d.drop_p, d.seed = p, seed
+        d.x, d.dy, d.dx = x2.data_ptr(), dy2.data_ptr(), dx.data_ptr()
+        base, at = act.data_ptr(), 0
+        for name, w in zip(("qkv", "a", "o", "x1", "hmid", "f"), (3 * E, E, E, E, FF, E)):
+            setattr(d, name, base + at * 2)
+            at += T * w
+        sb = stats.data_ptr()
+        d.mean1, d.rstd1, d.mean2, d.rstd2 = sb, sb + 4 * T, sb + 8 * T, sb + 12 * T
+        base, at = tmp.data_ptr(), 0
+        for name, w in zip(("dr2", "df", "dz1", "dx1", "dr1", "do_", "da", "dqkv"), widths):
+            setattr(d, name, base + at * 2)
+            at += T * w
+        d.dg1, d.dbe1 = ensure_grad(n1.weight).data_ptr(), ensure_grad(n1.bias).data_ptr()
+        d.dg2, d.dbe2 = ensure_grad(n2.weight).data_ptr(), ensure_grad(n2.bias).data_ptr()
+        for key, bias in (("qkv", at_.in_proj_bias), ("o", at_.out_proj.bias), ("1", l1.bias), ("2", l2.bias)):
+            lg = layer._lg({"qkv": "qkv", "o": "o", "1": "l1", "2": "l2"}[key])
+            off = lg.reserve(T, dev, stream)
+            setattr(d, "xt_" + key, lg.xt.data_ptr())
+            setattr(d, "dyt_" + key, lg.dyt.data_ptr())
+            setattr(d, "ld_stash_" + key, lg.xt.stride(0))
+            setattr(d, "stash_off_" + key, off)
+            setattr(d, "db_" + key, bias.grad.data_ptr())
+        ws = workspace(dev, stream)
+        d.workspace, d.workspace_bytes = ws.data_ptr(), ws.numel()
+        with _lib.on_device(dev):
+            rc = _lib.load().pb2_encoder_layer_bwd(ctypes.byref(d), ctypes.c_void_p(stream))
+        _lib.check(rc, "pb2_encoder_layer_bwd")
+        return (dx, None) + (None,) * (len(ctx.needs_input_grad) - 2)
 
 
 class FusedEncoderLayer(_FusedBase):
@@ -237,8 +263,35 @@ class FusedEncoderLayer(_FusedBase):
         self._register_linear("l1", self.linear1.weight, self.linear1.bias)
         self._register_linear("l2", self.linear2.weight, self.linear2.bias)
 
+    def _desc(self, device: torch.device) -> "_lib.EncoderLayerDesc":
+        """A fresh launch descriptor with everything that does not change between calls
+        (shapes, weight shadows, biases, LayerNorm parameters) filled in."""
+        sh = {k: self._sh(k) for k in ("qkv", "o", "l1", "l2")}
+        key = tuple(t.data_ptr() for pair in sh.values() for t in pair)
+        cached = self.__dict__.get("_pb2_desc")
+        if cached is None or cached[0] != key:
+            d = _lib.EncoderLayerDesc()
+            d.E, d.heads, d.FF = self.d_model, self.nhead, self.linear1.weight.size(0)
+            d.causal, d.eps = int(self.causal), self.norm1.eps
+            for name, k in (("qkv", "qkv"), ("o", "o"), ("1", "l1"), ("2", "l2")):
+                w16, w16t = sh[k]
+                setattr(d, "w_" + name, w16.data_ptr())
+                setattr(d, "wt_" + name, w16t.data_ptr())
+                setattr(d, "ldt_" + name, w16t.stride(0))
+            at = self.self_attn
+            d.b_qkv, d.b_o = at.in_proj_bias.data_ptr(), at.out_proj.bias.data_ptr()
+            d.b_1, d.b_2 = self.linear1.bias.data_ptr(), self.linear2.bias.data_ptr()
+            d.g1, d.be1 = self.norm1.weight.data_ptr(), self.norm1.bias.data_ptr()
+            d.g2, d.be2 = self.norm2.weight.data_ptr(), self.norm2.bias.data_ptr()
+            cached = (key, bytes(d))
+            self.__dict__["_pb2_desc"] = cached
+        return _lib.EncoderLayerDesc.from_buffer_copy(cached[1])
+
     def forward(self, x: Tensor, *extra: Any):
-        y = _EncoderLayerFn.apply(x, self, *self.parameters())
+        params = self.__dict__.get("_pb2_params")
+        if params is None:
+            params = self.__dict__["_pb2_params"] = tuple(self.parameters())
+        y = _EncoderLayerFn.apply(x, self, *params)
         return (y, *extra) if extra else y
 
 

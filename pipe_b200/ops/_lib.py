@@ -34,7 +34,29 @@ class GemmDesc(ctypes.Structure):
         ("accumulate", ctypes.c_int), ("alpha", ctypes.c_float),
         ("sumsq", ctypes.c_void_p),
         ("block_n", ctypes.c_int), ("splits", ctypes.c_int), ("stages", ctypes.c_int),
+        ("reduce_mode", ctypes.c_int),
     ]
+
+
+_vp, _ll, _ci, _cf = ctypes.c_void_p, ctypes.c_longlong, ctypes.c_int, ctypes.c_float
+
+
+class EncoderLayerDesc(ctypes.Structure):
+    """Mirror of ``pb2_encoder_layer`` (include/pipe_b200.h)."""
+    _fields_ = (
+        [(n, _ci) for n in ("T", "NB", "S", "E", "heads", "FF", "causal")]
+        + [("drop_p", _cf), ("eps", _cf), ("seed", ctypes.c_ulonglong)]
+        + [(n, _vp) for n in ("w_qkv", "w_o", "w_1", "w_2", "wt_qkv", "wt_o", "wt_1", "wt_2")]
+        + [(n, _ll) for n in ("ldt_qkv", "ldt_o", "ldt_1", "ldt_2")]
+        + [(n, _vp) for n in ("b_qkv", "b_o", "b_1", "b_2", "g1", "be1", "g2", "be2")]
+        + [(n, _vp) for n in ("x", "qkv", "a", "o", "x1", "hmid", "f", "y", "mean1", "rstd1", "mean2", "rstd2")]
+        + [(n, _vp) for n in ("dy", "dx", "dr2", "df", "dz1", "dx1", "dr1", "do_", "da", "dqkv")]
+        + [(n, _vp) for n in ("dg1", "dbe1", "dg2", "dbe2", "db_qkv", "db_o", "db_1", "db_2")]
+        + [(n, _vp) for n in ("xt_qkv", "dyt_qkv", "xt_o", "dyt_o", "xt_1", "dyt_1", "xt_2", "dyt_2")]
+        + [(n, _ll) for n in ("ld_stash_qkv", "ld_stash_o", "ld_stash_1", "ld_stash_2")]
+        + [(n, _ci) for n in ("stash_off_qkv", "stash_off_o", "stash_off_1", "stash_off_2")]
+        + [("workspace", _vp), ("workspace_bytes", ctypes.c_size_t)]
+    )
 
 
 def load() -> ctypes.CDLL:
@@ -68,8 +90,39 @@ def check(rc: int, what: str) -> None:
         raise RuntimeError(f"{what} failed: {msg}")
 
 
+def raw_stream(device: torch.device) -> int:
+    """The current CUDA stream of ``device`` as an integer handle (one C call; the
+    ``torch.cuda.current_stream()`` object path costs several microseconds)."""
+    idx = device.index
+    if idx is None:
+        idx = torch.cuda.current_device()
+    return torch._C._cuda_getCurrentRawStream(idx)
+
+
 def stream_ptr(device: Optional[torch.device] = None) -> ctypes.c_void_p:
-    return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+    if device is None:
+        device = torch.device("cuda", torch.cuda.current_device())
+    return ctypes.c_void_p(raw_stream(device))
+
+
+class _Noop:
+    def __enter__(self):
+        return None
+
+    def __exit__(self, *a):
+        return False
+
+
+_NOOP = _Noop()
+
+
+def on_device(device: torch.device):
+    """Context that makes ``device`` current for a raw launch; free when it already is (the usual
+    case: pipeline workers and autograd threads run with their stage's device current)."""
+    idx = device.index
+    if idx is None or torch._C._cuda_getDevice() == idx:
+        return _NOOP
+    return torch.cuda.device(idx)
 
 
 def ptr(t: Optional[torch.Tensor]) -> Optional[int]:

@@ -45,7 +45,7 @@ def add_layernorm_fwd(x: Tensor, h: Optional[Tensor], gamma: Tensor, beta: Tenso
     y = torch.empty_like(x)
     mean = torch.empty(rows, dtype=torch.float32, device=x.device)
     rstd = torch.empty(rows, dtype=torch.float32, device=x.device)
-    with torch.cuda.device(x.device):
+    with _lib.on_device(x.device):
         rc = _lib.load().pb2_add_layernorm_fwd(c_p(x.data_ptr()), c_p(ptr(h)), c_p(gamma.data_ptr()),
                                                c_p(beta.data_ptr()), c_p(y.data_ptr()), c_p(mean.data_ptr()),
                                                c_p(rstd.data_ptr()), c_i(rows), c_i(E), c_f(eps), _s(x))
@@ -62,7 +62,7 @@ def add_layernorm_bwd(dy: Tensor, x: Tensor, h: Optional[Tensor], gamma: Tensor,
     dres = torch.empty_like(x)
     dh = torch.empty_like(x) if want_dh else None
     assert dgamma.dtype == torch.float32 and dbeta.dtype == torch.float32
-    with torch.cuda.device(x.device):
+    with _lib.on_device(x.device):
         rc = _lib.load().pb2_add_layernorm_bwd(c_p(dy.data_ptr()), c_p(x.data_ptr()), c_p(ptr(h)),
                                                c_p(gamma.data_ptr()), c_p(mean.data_ptr()), c_p(rstd.data_ptr()),
                                                c_p(dres.data_ptr()), c_p(ptr(dh)), c_p(dgamma.data_ptr()),
@@ -80,7 +80,7 @@ def embed_fwd(tokens: Tensor, weight: Tensor, pe: Tensor, scale: float, drop_p: 
     assert weight.dtype == torch.float32 and weight.is_contiguous()
     assert pe.dtype == torch.float32 and pe.is_contiguous() and pe.size(-1) == E and pe.numel() // E >= S
     out = torch.empty((S, N, E), dtype=torch.bfloat16, device=tokens.device)
-    with torch.cuda.device(tokens.device):
+    with _lib.on_device(tokens.device):
         rc = _lib.load().pb2_embed_fwd(c_p(tokens.data_ptr()), c_p(weight.data_ptr()), c_p(pe.data_ptr()),
                                        c_p(out.data_ptr()), c_i(N), c_i(S), c_i(E), c_f(scale), c_f(drop_p),
                                        c_ull(seed), c_ull(rng_stream), _s(tokens))
@@ -93,7 +93,7 @@ def embed_bwd(tokens: Tensor, dout: Tensor, dweight: Tensor, scale: float, drop_
     N, S = tokens.shape
     E = dweight.size(1)
     assert dout.dtype == torch.bfloat16 and dout.is_contiguous() and dweight.dtype == torch.float32
-    with torch.cuda.device(tokens.device):
+    with _lib.on_device(tokens.device):
         rc = _lib.load().pb2_embed_bwd(c_p(tokens.data_ptr()), c_p(dout.data_ptr()), c_p(dweight.data_ptr()),
                                        c_i(N), c_i(S), c_i(E), c_f(scale), c_f(drop_p), c_ull(seed),
                                        c_ull(rng_stream), _s(tokens))
@@ -110,7 +110,7 @@ def cross_entropy(logits: Tensor, targets: Tensor, V: int, *, write_grad: bool,
     loss = torch.empty(rows, dtype=torch.float32, device=logits.device) if want_loss else None
     if row_scale is not None:
         assert row_scale.dtype == torch.float32 and row_scale.is_contiguous() and row_scale.numel() == rows
-    with torch.cuda.device(logits.device):
+    with _lib.on_device(logits.device):
         rc = _lib.load().pb2_cross_entropy(c_p(logits.data_ptr()), c_p(targets.data_ptr()), c_p(ptr(loss)),
                                            c_p(ptr(row_scale)), c_i(rows), c_i(V), c_ll(logits.stride(0)),
                                            c_i(int(write_grad)), _s(logits))
@@ -123,7 +123,7 @@ def transpose_colsum(src: Tensor, dst: Tensor, colsum: Optional[Tensor] = None, 
     assert src.dtype == torch.bfloat16 and dst.dtype == torch.bfloat16 and src.dim() == 2 and dst.dim() == 2
     R, C = src.shape
     assert dst.size(0) == C and dst.stride(1) == 1 and src.stride(1) == 1
-    with torch.cuda.device(src.device):
+    with _lib.on_device(src.device):
         rc = _lib.load().pb2_transpose_colsum(c_p(src.data_ptr()), c_ll(src.stride(0)), c_p(dst.data_ptr()),
                                               c_ll(dst.stride(0)), c_i(R), c_i(C), c_p(ptr(colsum)), c_f(scale),
                                               _s(src))
@@ -156,14 +156,14 @@ def transpose_multi(jobs: Sequence[Tuple[Tensor, Tensor, int, Optional[Tensor], 
         j.R, j.C = R, C
         j.colsum = ptr(colsum)
         j.scale = scale
-    with torch.cuda.device(dev):
+    with _lib.on_device(dev):
         rc = _lib.load().pb2_transpose_multi(ctypes.byref(packed), _lib.stream_ptr(dev))
     _lib.check(rc, "pb2_transpose_multi")
 
 
 def sumsq(x: Tensor, out: Tensor) -> None:
     assert x.dtype == torch.float32 and x.is_contiguous() and out.dtype == torch.float32
-    with torch.cuda.device(x.device):
+    with _lib.on_device(x.device):
         rc = _lib.load().pb2_sumsq(c_p(x.data_ptr()), ctypes.c_size_t(x.numel()), c_p(out.data_ptr()), _s(x))
     _lib.check(rc, "pb2_sumsq")
 
@@ -174,7 +174,7 @@ def attention_fwd(qkv: Tensor, NB: int, S: int, H: int, *, causal: bool, drop_p:
     E = E3 // 3
     assert qkv.dtype == torch.bfloat16 and qkv.is_contiguous() and T == NB * S and E % H == 0
     out = torch.empty((T, E), dtype=torch.bfloat16, device=qkv.device)
-    with torch.cuda.device(qkv.device):
+    with _lib.on_device(qkv.device):
         rc = _lib.load().pb2_attention_fwd(c_p(qkv.data_ptr()), c_p(out.data_ptr()), c_i(NB), c_i(S), c_i(H),
                                            c_i(E // H), c_i(int(causal)), c_f(drop_p), c_ull(seed),
                                            c_ull(rng_stream), _s(qkv))
@@ -188,7 +188,7 @@ def attention_bwd(qkv: Tensor, dout: Tensor, NB: int, S: int, H: int, *, causal:
     E = E3 // 3
     assert dout.dtype == torch.bfloat16 and dout.is_contiguous() and dout.shape == (T, E)
     dqkv = torch.empty_like(qkv)
-    with torch.cuda.device(qkv.device):
+    with _lib.on_device(qkv.device):
         rc = _lib.load().pb2_attention_bwd(c_p(qkv.data_ptr()), c_p(dout.data_ptr()), c_p(dqkv.data_ptr()), c_i(NB),
                                            c_i(S), c_i(H), c_i(E // H), c_i(int(causal)), c_f(drop_p), c_ull(seed),
                                            c_ull(rng_stream), _s(qkv))

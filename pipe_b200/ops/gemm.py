@@ -23,11 +23,11 @@ _ws: Dict[tuple, Tensor] = {}
 _ws_lock = threading.Lock()
 
 
-def workspace(device: torch.device) -> Tensor:
+def workspace(device: torch.device, stream: Optional[int] = None) -> Tensor:
     """Per-(device, stream) split-K scratch: zero-initialised once, then
     self-cleaning (the kernel re-arms its counters).  Keyed by stream too, because
     two streams running split-K GEMMs at once must not share partial tiles."""
-    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    key = (device.index, _lib.raw_stream(device) if stream is None else stream)
     ws = _ws.get(key)
     if ws is None:
         with _ws_lock:
@@ -44,7 +44,7 @@ def gemm_nt(a: Tensor, b: Tensor, *, out: Optional[Tensor] = None, out_dtype: to
             relu: bool = False, drop_p: float = 0.0, seed: int = 0, rng_stream: int = 0,
             mask_src: Optional[Tensor] = None, mask_scale: float = 1.0, addend: Optional[Tensor] = None,
             accumulate: bool = False, alpha: float = 1.0, sumsq: Optional[Tensor] = None,
-            block_n: int = 0, splits: int = 0, stages: int = 0) -> Tensor:
+            block_n: int = 0, splits: int = 0, stages: int = 0, reduce_mode: int = 0, stream: Optional[int] = None) -> Tensor:
     lib = _lib.load()
     assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16, "gemm_nt takes bf16 operands"
     assert a.dim() == 2 and b.dim() == 2 and a.size(1) == b.size(1)
@@ -80,12 +80,14 @@ def gemm_nt(a: Tensor, b: Tensor, *, out: Optional[Tensor] = None, out_dtype: to
     d.accumulate = int(accumulate)
     d.alpha = float(alpha)
     d.sumsq = _lib.ptr(sumsq)
-    d.block_n, d.splits, d.stages = block_n, splits, stages
+    d.block_n, d.splits, d.stages, d.reduce_mode = block_n, splits, stages, reduce_mode
 
-    ws = workspace(a.device)
-    with torch.cuda.device(a.device):
+    if stream is None:
+        stream = _lib.raw_stream(a.device)
+    ws = workspace(a.device, stream)
+    with _lib.on_device(a.device):
         rc = lib.pb2_gemm_bf16(ctypes.byref(d), ctypes.c_void_p(ws.data_ptr()), ctypes.c_size_t(ws.numel()),
-                               _lib.stream_ptr(a.device))
+                               ctypes.c_void_p(stream))
     _lib.check(rc, "pb2_gemm_bf16")
     return out
 

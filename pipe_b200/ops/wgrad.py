@@ -26,6 +26,7 @@ from typing import Dict, Iterator, List, Optional, Set, Tuple
 import torch
 from torch import Tensor, nn
 
+from . import _lib
 from .gemm import gemm_nt
 
 __all__ = ["LinearGrad", "deferred", "flush_pending", "ensure_grad"]
@@ -52,7 +53,7 @@ class LinearGrad:
         self.xt: Optional[Tensor] = None      # [in, cap]  bf16
         self.dyt: Optional[Tensor] = None     # [out, cap] bf16
         self.used = 0
-        self.stream: Optional[torch.cuda.Stream] = None
+        self.stream: Optional[int] = None       # raw handle of the stream the operands were stacked on
 
     def _reserve(self, tokens: int) -> int:
         out_f, in_f = self.weight.shape
@@ -73,6 +74,19 @@ class LinearGrad:
         self.used = need
         return off
 
+    def reserve(self, tokens: int, device: torch.device, stream: Optional[int] = None) -> int:
+        """Reserve a column block of ``tokens`` columns for one micro-batch, register this
+        Linear for the end-of-backward flush, make sure the bias gradient exists; returns the
+        column offset.  (The caller transposes its operands into ``xt`` / ``dyt`` there.)"""
+        with _lock:
+            off = self._reserve(tokens)
+            self.stream = _lib.raw_stream(device) if stream is None else stream
+            _pending[id(self)] = self
+            _arm()
+        if self.bias is not None:
+            ensure_grad(self.bias)
+        return off
+
     def jobs(self, x: Tensor, dy: Tensor) -> List[Tuple[Tensor, Tensor, int, Optional[Tensor], float]]:
         """Reserve a column block for one micro-batch and return the two transpose
         jobs that fill it (``dy``'s job also accumulates the bias gradient)."""
@@ -80,7 +94,7 @@ class LinearGrad:
         assert dy.size(0) == tokens
         with _lock:
             off = self._reserve(tokens)
-            self.stream = torch.cuda.current_stream(x.device)
+            self.stream = _lib.raw_stream(x.device)
             _pending[id(self)] = self
             _arm()
         bias_grad = ensure_grad(self.bias) if self.bias is not None else None
@@ -93,9 +107,8 @@ class LinearGrad:
         grad = ensure_grad(w)
         fresh = getattr(w, "_pb2_fresh", False)
         normsq = getattr(w, "_pb2_normsq", None) if fresh else None
-        with torch.cuda.stream(self.stream):
-            gemm_nt(self.dyt[:, : self.used], self.xt[:, : self.used], out=grad, accumulate=not fresh,
-                    sumsq=normsq)
+        gemm_nt(self.dyt[:, : self.used], self.xt[:, : self.used], out=grad, accumulate=not fresh,
+                sumsq=normsq, stream=self.stream)
         if fresh:
             w._pb2_fresh = False
             w._pb2_sumsq_done = normsq is not None

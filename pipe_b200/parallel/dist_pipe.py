@@ -105,6 +105,10 @@ class DistPipe(nn.Module):
         if not dist.is_initialized():
             raise RuntimeError("DistPipe needs torch.distributed to be initialised")
 
+        if type(stage) is nn.Sequential:
+            # same calling convention as an in-process stage: tuples are splatted between layers
+            from ..partition import PipeSequential
+            stage = PipeSequential(*stage.children())
         self.stage = stage
         self.chunks = chunks
         self.checkpoint = checkpoint

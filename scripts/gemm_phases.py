@@ -22,14 +22,16 @@ def run(M, N, K, **kw):
     torch.cuda.synchronize()
     t = ts.view(ctas, 16).cpu()
     t0 = t[:, 0].min()
+    kw = {k: (v if not torch.is_tensor(v) else "tensor") for k, v in kw.items()}
     print(f"--- M={M} N={N} K={K} {kw} ctas={ctas}: kernel span {(t[:, 6].max() - t0).item() / 1e3:.1f} us")
     for k, nm in enumerate(names):
         col = (t[:, k] - t0).float() / 1e3
         print(f"   {nm:20s} min {col.min():7.2f}  median {col.median():7.2f}  max {col.max():7.2f} us")
 
-run(128, 80, 512, splits=1)
-run(128, 80, 512, splits=1, bias=torch.randn(128, device=dev), bias_along_m=True)
-run(4096, 80, 4096, splits=1)
-run(4096, 80, 4096, splits=4)
-run(4096, 80, 4096, splits=4, bias=torch.randn(4096, device=dev), bias_along_m=True, relu=True, drop_p=0.2, seed=5)
+run(4096, 80, 4096, splits=4, reduce_mode=1)
+run(4096, 80, 4096, splits=4, reduce_mode=2)
+run(4096, 80, 4096, splits=2, reduce_mode=2)
+run(4096, 80, 4096, splits=8, reduce_mode=2)
+run(4096, 80, 4096, splits=4, reduce_mode=2, bias=torch.randn(4096, device=dev), bias_along_m=True, relu=True, drop_p=0.2, seed=5)
 run(12288, 80, 4096, splits=1)
+run(12288, 80, 4096, splits=2, reduce_mode=2)

@@ -55,6 +55,22 @@ def test_forced_splits_and_block_n_agree():
     _close(got, want, rtol=1e-2, atol=0.5)
 
 
+@pytest.mark.parametrize("M,N,K,splits", [(4096, 75, 4096, 4), (4096, 75, 4096, 8), (1024, 250, 2048, 2),
+                                          (384, 33, 1024, 4), (4096, 75, 12288, 4)])
+def test_cluster_and_scratch_reductions_agree(M, N, K, splits):
+    """Split-K through DSMEM inside a cluster (mode 2) vs through the global workspace (mode 1)."""
+    from pipe_b200.ops.gemm import gemm_nt
+    a = torch.randn(M, K, device="cuda").bfloat16()
+    b = torch.randn(N, K, device="cuda").bfloat16()
+    bias = torch.randn(M, device="cuda")
+    want = _ref(a, b) + bias[:, None]
+    for mode in (1, 2):
+        got = gemm_nt(a, b, out_dtype=torch.float32, splits=splits, reduce_mode=mode, bias=bias, bias_along_m=True)
+        _close(got, want, rtol=1e-2, atol=1e-2 * (K ** 0.5))
+        got_t = gemm_nt(a, b, transpose_out=True, splits=splits, reduce_mode=mode, bias=bias, bias_along_m=True)
+        _close(got_t, want.t(), rtol=2e-2, atol=2e-2 * (K ** 0.5))
+
+
 def test_epilogue_bias_relu_transpose():
     from pipe_b200.ops.gemm import linear_forward
     x = torch.randn(75, 512, device="cuda").bfloat16()

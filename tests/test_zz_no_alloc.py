@@ -26,6 +26,7 @@ def _desc(_lib, a, b, out, splits, block_n):
     d.out, d.ld_out = out.data_ptr(), out.stride(0)
     d.out_f32 = 1
     d.splits, d.block_n = splits, block_n
+    d.reduce_mode = 1          # the caller-workspace split-K path, like the entry point under test
     return d
 
 
