@@ -18,7 +18,7 @@
 
 namespace pb2 {
 
-constexpr int kAttnThreads = 256;
+constexpr int kAttnThreads = 512;
 
 struct AttnShape {
     int NB, S, H, D, E;      // sequences in the micro-batch, sequence length, heads, head dim, model dim
@@ -28,29 +28,66 @@ struct AttnShape {
     unsigned long long seed, rng_stream;
 };
 
-__device__ __forceinline__ void load_head(const __nv_bfloat16* __restrict__ base, long long ld, int NB, int S, int D,
-                                          int n, __nv_bfloat16* dst, int dpad) {
-    // rows s*NB + n, D contiguous elements each; 8-element (16 B) vectors
+// Gather up to four [S, D] head slices (rows s*NB + n of different matrices) into shared memory.
+// All global loads of a batch are issued before the first shared store, so a thread has up to
+// eight 16-byte requests in flight instead of one L2 round trip per vector.
+struct HeadSrc {
+    const __nv_bfloat16* base[4];
+    long long ld[4];
+    __nv_bfloat16* dst[4];
+    int count;
+};
+
+__device__ __forceinline__ void load_heads(const HeadSrc hs, int NB, int S, int D, int n, int dpad) {
     const int vec_per_row = D / 8;
-    for (int t = threadIdx.x; t < S * vec_per_row; t += blockDim.x) {
-        const int s = t / vec_per_row, v = t % vec_per_row;
-        const uint4 raw = *reinterpret_cast<const uint4*>(base + (static_cast<size_t>(s) * NB + n) * ld + v * 8);
-        uint32_t* d = reinterpret_cast<uint32_t*>(dst + s * dpad + v * 8);     // rows are only 4-byte aligned
-        d[0] = raw.x; d[1] = raw.y; d[2] = raw.z; d[3] = raw.w;
+    const int per_mat = S * vec_per_row;
+    const int total = per_mat * hs.count;
+    constexpr int kBatch = 8;
+    for (int t0 = threadIdx.x; t0 < total; t0 += blockDim.x * kBatch) {
+        uint4 raw[kBatch];
+#pragma unroll
+        for (int u = 0; u < kBatch; ++u) {
+            const int t = t0 + u * blockDim.x;
+            if (t < total) {
+                const int m = t / per_mat, r = t - m * per_mat;
+                const int s = r / vec_per_row, v = r - s * vec_per_row;
+                const __nv_bfloat16* b = m == 0 ? hs.base[0] : m == 1 ? hs.base[1] : m == 2 ? hs.base[2] : hs.base[3];
+                const long long l = m == 3 ? hs.ld[3] : hs.ld[0];
+                raw[u] = *reinterpret_cast<const uint4*>(b + (static_cast<size_t>(s) * NB + n) * l + v * 8);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < kBatch; ++u) {
+            const int t = t0 + u * blockDim.x;
+            if (t < total) {
+                const int m = t / per_mat, r = t - m * per_mat;
+                const int s = r / vec_per_row, v = r - s * vec_per_row;
+                __nv_bfloat16* db = m == 0 ? hs.dst[0] : m == 1 ? hs.dst[1] : m == 2 ? hs.dst[2] : hs.dst[3];
+                uint32_t* d = reinterpret_cast<uint32_t*>(db + s * dpad + v * 8);   // rows are 4-byte aligned
+                d[0] = raw[u].x; d[1] = raw[u].y; d[2] = raw[u].z; d[3] = raw[u].w;
+            }
+        }
     }
 }
 
+// Dot product of two bf16 rows in shared memory.  Four independent accumulators: a CTA runs only a
+// few warps per scheduler here, so one serial FMA chain per thread would be pure exposed latency.
 __device__ __forceinline__ float dot_bf16(const __nv_bfloat16* a, const __nv_bfloat16* b, int D) {
-    float acc = 0.f;
+    float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;
     const __nv_bfloat162* a2 = reinterpret_cast<const __nv_bfloat162*>(a);
     const __nv_bfloat162* b2 = reinterpret_cast<const __nv_bfloat162*>(b);
-#pragma unroll 8
-    for (int c = 0; c < D / 2; ++c) {
-        const float2 x = __bfloat1622float2(a2[c]), y = __bfloat1622float2(b2[c]);
-        acc = fmaf(x.x, y.x, acc);
-        acc = fmaf(x.y, y.y, acc);
+#pragma unroll 4
+    for (int c = 0; c < D / 2; c += 4) {
+        const float2 x0 = __bfloat1622float2(a2[c]), y0 = __bfloat1622float2(b2[c]);
+        const float2 x1 = __bfloat1622float2(a2[c + 1]), y1 = __bfloat1622float2(b2[c + 1]);
+        const float2 x2 = __bfloat1622float2(a2[c + 2]), y2 = __bfloat1622float2(b2[c + 2]);
+        const float2 x3 = __bfloat1622float2(a2[c + 3]), y3 = __bfloat1622float2(b2[c + 3]);
+        acc0 = fmaf(x0.x, y0.x, acc0); acc0 = fmaf(x0.y, y0.y, acc0);
+        acc1 = fmaf(x1.x, y1.x, acc1); acc1 = fmaf(x1.y, y1.y, acc1);
+        acc2 = fmaf(x2.x, y2.x, acc2); acc2 = fmaf(x2.y, y2.y, acc2);
+        acc3 = fmaf(x3.x, y3.x, acc3); acc3 = fmaf(x3.y, y3.y, acc3);
     }
-    return acc;
+    return (acc0 + acc1) + (acc2 + acc3);
 }
 
 // scores -> probabilities in place; returns nothing.  One warp per row.
@@ -92,9 +129,10 @@ attn_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict
     const int n = blockIdx.x / a.H, h = blockIdx.x % a.H;
     const long long ld = 3LL * a.E;
 
-    load_head(qkv + h * D, ld, a.NB, S, D, n, q, dpad);
-    load_head(qkv + a.E + h * D, ld, a.NB, S, D, n, k, dpad);
-    load_head(qkv + 2 * a.E + h * D, ld, a.NB, S, D, n, v, dpad);
+    {
+        HeadSrc hs{{qkv + h * D, qkv + a.E + h * D, qkv + 2 * a.E + h * D, nullptr}, {ld, ld, ld, 0}, {q, k, v, nullptr}, 3};
+        load_heads(hs, a.NB, S, D, n, dpad);
+    }
     __syncthreads();
 
     for (int p = threadIdx.x; p < S * S; p += blockDim.x) {
@@ -119,15 +157,24 @@ attn_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict
     // O = P V : thread owns (i, pair of columns)
     for (int p = threadIdx.x; p < S * (D / 2); p += blockDim.x) {
         const int i = p / (D / 2), c2 = p % (D / 2);
-        float o0 = 0.f, o1 = 0.f;
+        float o0 = 0.f, o1 = 0.f, o2 = 0.f, o3 = 0.f;
         const float* pr = sc + i * spad;
-        for (int j = 0; j < S; ++j) {
-            const float2 vv = __bfloat1622float2(reinterpret_cast<const __nv_bfloat162*>(v + j * dpad)[c2]);
-            o0 = fmaf(pr[j], vv.x, o0);
-            o1 = fmaf(pr[j], vv.y, o1);
+        int j = 0;
+        for (; j + 1 < S; j += 2) {
+            const float2 va = __bfloat1622float2(reinterpret_cast<const __nv_bfloat162*>(v + j * dpad)[c2]);
+            const float2 vb = __bfloat1622float2(reinterpret_cast<const __nv_bfloat162*>(v + (j + 1) * dpad)[c2]);
+            o0 = fmaf(pr[j], va.x, o0);
+            o1 = fmaf(pr[j], va.y, o1);
+            o2 = fmaf(pr[j + 1], vb.x, o2);
+            o3 = fmaf(pr[j + 1], vb.y, o3);
+        }
+        if (j < S) {
+            const float2 va = __bfloat1622float2(reinterpret_cast<const __nv_bfloat162*>(v + j * dpad)[c2]);
+            o0 = fmaf(pr[j], va.x, o0);
+            o1 = fmaf(pr[j], va.y, o1);
         }
         reinterpret_cast<__nv_bfloat162*>(out + (static_cast<size_t>(i) * a.NB + n) * a.E + h * D)[c2] =
-            __floats2bfloat162_rn(o0, o1);
+            __floats2bfloat162_rn(o0 + o2, o1 + o3);
     }
 }
 
@@ -146,10 +193,10 @@ attn_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* __re
     const int n = blockIdx.x / a.H, h = blockIdx.x % a.H;
     const long long ld = 3LL * a.E;
 
-    load_head(qkv + h * D, ld, a.NB, S, D, n, q, dpad);
-    load_head(qkv + a.E + h * D, ld, a.NB, S, D, n, k, dpad);
-    load_head(qkv + 2 * a.E + h * D, ld, a.NB, S, D, n, v, dpad);
-    load_head(dout + h * D, a.E, a.NB, S, D, n, dO, dpad);
+    {
+        HeadSrc hs{{qkv + h * D, qkv + a.E + h * D, qkv + 2 * a.E + h * D, dout + h * D}, {ld, ld, ld, a.E}, {q, k, v, dO}, 4};
+        load_heads(hs, a.NB, S, D, n, dpad);
+    }
     __syncthreads();
 
     const CounterRng ph(a.seed);
