@@ -170,6 +170,24 @@ int pb2_adam_step(const pb2_adam_tensor* table_dev, int n_tensors, int total_til
                   float grad_scale, cudaStream_t stream);
 int pb2_refresh_shadows(const pb2_adam_tensor* table_dev, int n_tensors, int total_tiles, cudaStream_t stream);
 
+/* ---- gradient all-reduce over NVLink / NVSwitch, fused with scale + squared norm + bf16 cast-out ----
+ * In place over symmetric memory: peer_bufs[q] is rank q's fp32 buffer of n elements as mapped into
+ * THIS process (n a multiple of 4 * world), peer_pads[q] rank q's signal pad of
+ * pb2_allreduce_pad_bytes() bytes (zeroed once; `epoch` must be non-zero and increase by one per call
+ * on every rank).  Every rank of the group launches the call at the same point of its stream; the
+ * kernels synchronise among themselves with flags in the pads (a stuck peer trips a watchdog trap).
+ * use_multimem = 1 reduces inside the NVSwitch through `multicast` (the multicast alias of the
+ * buffers); otherwise a two-shot P2P pull/push.  On return (stream order) every rank's buffer holds
+ * scale * sum, *sumsq (optional) has this rank's share of the squared norm added, and cast_out_bf16
+ * (optional, local, n elements) holds a bf16 copy.
+ * Reference counterpart: none in code (DDP is only mentioned, pipe.py:290-293); baseline = NCCL
+ * all-reduce.  SURVEY.md K18. */
+int pb2_allreduce_max_ctas(void);
+size_t pb2_allreduce_pad_bytes(void);
+int pb2_allreduce_f32(float* const* peer_bufs, void* const* peer_pads, float* multicast, int world, int rank,
+                      size_t n, float scale, float* sumsq, void* cast_out_bf16, unsigned int epoch, int ctas,
+                      int use_multimem, cudaStream_t stream);
+
 /* ---- whole encoder layer: one host call launches the layer's kernel sequence -----------------
  * The framework's host-side critical path is the per-kernel launch cost:
  * a 75-token micro-batch gives each kernel 5-20 us of GPU work.  These two entry points run the

@@ -56,10 +56,17 @@ class FusedClipAdam:
 
     def __init__(self, module: nn.Module, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
                  weight_decay: float = 0.0, max_norm: float = 0.0, grad_scale: float = 1.0,
-                 distributed: bool = False, group=None) -> None:
+                 distributed: bool = False, group=None, replica_group=None, replicas: int = 1,
+                 reduce_backend: str = "fused") -> None:
+        """``replica_group`` / ``replicas`` switch on data parallelism across pipeline replicas: all
+        gradients of this rank's stage then live in ONE symmetric buffer and are averaged over the
+        replica group by the fused NVSwitch all-reduce (``reduce_backend="fused"``) or by NCCL
+        (``"nccl"``, the baseline) between backward and the update."""
         self.lr, self.betas, self.eps, self.weight_decay = lr, betas, eps, weight_decay
         self.max_norm, self.grad_scale = max_norm, grad_scale
         self.distributed, self.group = distributed, group
+        self.replica_group, self.replicas, self.reduce_backend = replica_group, int(replicas), reduce_backend
+        self.reduce_ctas = 32
         self.step_count = 0
         self.module = module
 
@@ -83,10 +90,27 @@ class FusedClipAdam:
             st = self.devs.setdefault(p.device, _DeviceState(p.device))
             st.params.append(p)
 
+        hybrid = self.replicas > 1
+        if hybrid and len(self.devs) != 1:
+            raise ValueError("replicated (hybrid) mode expects one stage = one device per rank")
         for st in self.devs.values():
             small = [p for p in st.params if id(p) not in gemm_written]
+            big = [p for p in st.params if id(p) in gemm_written]
             n_small = sum((p.numel() + 3) // 4 * 4 for p in small)
-            st.flat_small = torch.zeros(max(n_small, 4), dtype=torch.float32, device=st.device)
+            n_big = sum((p.numel() + 3) // 4 * 4 for p in big) if hybrid else 0
+            if hybrid:
+                # one symmetric buffer for every gradient of the stage: [matrices | small]
+                from ..parallel.symmetric import SymmetricBuffer
+                st.symm = SymmetricBuffer(n_big + max(n_small, 4), self.replica_group, st.device)
+                flat = st.symm.data
+                st.flat_small = flat[n_big:n_big + max(n_small, 4)]
+                at = 0
+                for p in big:
+                    p.grad = flat[at:at + p.numel()].view_as(p)
+                    at += (p.numel() + 3) // 4 * 4
+            else:
+                st.symm = None
+                st.flat_small = torch.zeros(max(n_small, 4), dtype=torch.float32, device=st.device)
             at = 0
             for p in small:
                 p.grad = st.flat_small[at:at + p.numel()].view_as(p)
@@ -95,8 +119,9 @@ class FusedClipAdam:
             tile = 0
             for k, p in enumerate(st.params):
                 if id(p) in gemm_written:
-                    p.grad = torch.zeros_like(p)
-                    p._pb2_normsq = st.normsq
+                    if not hybrid:
+                        p.grad = torch.zeros_like(p)
+                        p._pb2_normsq = st.normsq      # local norm is the global norm: fuse it into wgrad
                     p._pb2_fresh = True
                     p._pb2_sumsq_done = False
                 m = torch.zeros_like(p)
@@ -129,6 +154,24 @@ class FusedClipAdam:
                     p._pb2_fresh = True
                     p._pb2_sumsq_done = False
 
+    def _reduce_replicas(self) -> None:
+        """Average the stage's gradients over the pipeline replicas (and collect this rank's share
+        of the squared norm of the averaged gradients in the same pass)."""
+        (st,) = self.devs.values()
+        want = st.normsq if self.max_norm > 0 else None
+        if self.reduce_backend == "fused":
+            st.symm.all_reduce_(scale=1.0 / self.replicas, sumsq=want, ctas=self.reduce_ctas)
+        else:
+            dist.all_reduce(st.symm.data, group=self.replica_group)
+            st.symm.data.mul_(1.0 / self.replicas)
+            if want is not None:
+                n = st.symm.numel // st.symm.world
+                lo = n * st.symm.rank
+                F2.sumsq(st.symm.data[lo:lo + n], want)
+        if want is not None:
+            st.total_normsq.copy_(st.normsq)
+            dist.all_reduce(st.total_normsq)          # slices of every stage, over all ranks
+
     def _total_normsq(self) -> None:
         """Finish the squared norm on every device, then share the total."""
         for st in self.devs.values():
@@ -152,7 +195,9 @@ class FusedClipAdam:
     def step(self) -> None:
         wgrad.flush_pending()
         self.step_count += 1
-        if self.max_norm > 0:
+        if self.replicas > 1:
+            self._reduce_replicas()
+        elif self.max_norm > 0:
             self._total_normsq()
         lib = _lib.load()
         for st in self.devs.values():

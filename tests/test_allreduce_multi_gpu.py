@@ -1,0 +1,129 @@
+"""Fused NVSwitch all-reduce vs NCCL, and the hybrid (replicas x stages) step — needs >= 2 GPUs.
+One process per GPU (never two ranks on one GPU: the kernels wait on each other)."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+pytestmark = pytest.mark.gpu
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _need(n):
+    if torch.cuda.device_count() < n:
+        pytest.skip(f"needs {n} GPUs")
+
+
+def _spawn(fn, world, *args):
+    port = _free_port()
+    ctx = mp.get_context("spawn")
+    q = ctx.SimpleQueue()
+    procs = [ctx.Process(target=_entry, args=(fn, r, world, port, q, args)) for r in range(world)]
+    for p in procs:
+        p.start()
+    out = [q.get() for _ in range(world)]
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    bad = [o for o in out if o[1] is not None]
+    assert not bad, bad
+    return out
+
+
+def _entry(fn, rank, world, port, q, args):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    err = None
+    try:
+        fn(rank, world, *args)
+    except Exception as e:  # noqa: BLE001
+        import traceback
+        err = traceback.format_exc()
+    q.put((rank, err))
+    dist.destroy_process_group()
+
+
+def _allreduce_case(rank, world):
+    from pipe_b200.parallel import SymmetricBuffer
+    dev = torch.device("cuda", rank)
+    for numel in (1 << 10, 1000 * 1000 + 12, 64 * 1024 * 1024):
+        buf = SymmetricBuffer(numel, None, dev)
+        assert buf.mode in ("symm", "ipc"), getattr(buf, "_symm_error", "")
+        modes = [False] + ([True] if buf.multicast_ptr else [])
+        for use_mm in modes:
+            for it in range(3):                       # repeated calls: epochs, no pad resets
+                torch.manual_seed(1000 * it + rank)
+                src = torch.randn(buf.numel, device=dev)
+                buf.data.copy_(src)
+                want = src.clone()
+                dist.all_reduce(want)
+                want.mul_(1.0 / world)
+                ss = torch.zeros((), device=dev)
+                cast = torch.empty(buf.numel, dtype=torch.bfloat16, device=dev)
+                torch.cuda.synchronize()
+                dist.barrier()
+                buf.all_reduce_(scale=1.0 / world, sumsq=ss, cast_out=cast, use_multimem=use_mm)
+                torch.cuda.synchronize()
+                assert torch.allclose(buf.data, want, rtol=1e-5, atol=1e-5), (numel, use_mm, it)
+                assert torch.allclose(cast.float(), want, rtol=1e-2, atol=1e-2)
+                dist.all_reduce(ss)
+                ref = (want.double() ** 2).sum().item()
+                assert abs(ss.item() - ref) / ref < 1e-3
+        dist.barrier()
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_fused_allreduce_matches_nccl(world):
+    _need(world)
+    _spawn(_allreduce_case, world)
+
+
+def _hybrid_case(rank, world, stages, backend):
+    """k replicas x n stages must take the same optimizer step as one pipeline fed the whole batch."""
+    import copy
+
+    from pipe_b200.models import TransformerConfig, build_stage
+    from pipe_b200.parallel import HybridPipe
+    dev = torch.device("cuda", rank)
+    cfg = TransformerConfig(ntokens=512, emsize=256, nhid=512, nlayers=4, nhead=4, dropout=0.0, bptt=16, batch=8, chunks=2)
+    replicas = world // stages
+    stage_idx = rank % stages
+    body = build_stage(cfg, stage_idx, stages, dev, impl="fused", seed=1)
+    pipe = HybridPipe(body, stages=stages, chunks=cfg.chunks, checkpoint="except_last", device=dev)
+    opt = pipe.make_optimizer(reduce_backend=backend, lr=1e-2, max_norm=0.5)
+    g = torch.Generator().manual_seed(7)
+    tokens = torch.randint(0, cfg.ntokens, (cfg.batch * replicas, cfg.bptt), generator=g)
+    targets = torch.randint(0, cfg.ntokens, (cfg.batch * replicas, cfg.bptt), generator=g)
+    lo = pipe.replica * cfg.batch
+    for _ in range(2):
+        opt.zero_grad()
+        if pipe.is_first:
+            out = pipe(tokens[lo:lo + cfg.batch].to(dev), targets[lo:lo + cfg.batch].to(dev))
+        else:
+            out = pipe()
+        loss = out.local_value().sum() / (cfg.batch * cfg.bptt) if pipe.is_last else None
+        pipe.backward(loss)
+        opt.step()
+    torch.cuda.synchronize()
+    # replicas must stay bit-identical after the update (same averaged gradient everywhere)
+    flat = torch.cat([p.detach().flatten() for p in body.parameters()])
+    gathered = [torch.empty_like(flat) for _ in range(replicas)]
+    dist.all_gather(gathered, flat, group=pipe.replica_group)
+    for other in gathered[1:]:
+        assert torch.equal(gathered[0], other)
+    assert torch.isfinite(flat).all()
+
+
+@pytest.mark.parametrize("world,stages,backend", [(2, 1, "fused"), (2, 1, "nccl"), (4, 2, "fused"), (8, 4, "fused")])
+def test_hybrid_replicas_stay_in_sync(world, stages, backend):
+    _need(world)
+    _spawn(_hybrid_case, world, stages, backend)
