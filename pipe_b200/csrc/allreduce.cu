@@ -20,7 +20,7 @@
 // pads, acquire spins on the local pad, a launch epoch instead of resets.  Every CTA handshakes
 // with its counterpart CTA on the peers, so there is no intra-GPU grid barrier.  A spin that
 // exceeds its budget traps with the rank / phase / peer that failed to show up (the watchdog NCCL
-// would otherwise provide).  The kernel is sized small (default 32 CTAs) so it can share the GPU
+// would otherwise provide).  The kernel is sized small (default 64 of 148 SMs) so it can share the GPU
 // with the backward of the pipeline stages that are still running.
 //
 // Reference counterpart: none in code — the reference only remarks that DDP may wrap Pipe
@@ -35,7 +35,7 @@ namespace pb2 {
 
 constexpr int kArThreads = 512;
 constexpr int kArMaxWorld = 8;
-constexpr int kArMaxCtas = 64;
+constexpr int kArMaxCtas = 128;
 
 struct ArArgs {
     float* bufs[kArMaxWorld];           // peer-mapped data pointers (index = rank in group)
@@ -113,42 +113,53 @@ allreduce_kernel(const ArArgs a) {
     const size_t stride = static_cast<size_t>(gridDim.x) * kArThreads * 4;
     float ss = 0.f;
 
-    for (size_t off = (static_cast<size_t>(blockIdx.x) * kArThreads + threadIdx.x) * 4; off < slice; off += stride * 2) {
-        // two independent float4 per thread per trip (more loads in flight over NVLink)
-        const size_t i0 = begin + off, i1 = begin + off + stride;
-        const bool has1 = off + stride < slice;
-        float4 v0 = make_float4(0.f, 0.f, 0.f, 0.f), v1 = v0;
+    // independent float4 per thread per trip (P2P holds world x kUnroll loads in registers)
+    constexpr int kUnroll = kMultimem ? 4 : 2;
+    for (size_t off = (static_cast<size_t>(blockIdx.x) * kArThreads + threadIdx.x) * 4; off < slice; off += stride * kUnroll) {
+        float4 v[kUnroll];
+        bool has[kUnroll];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            has[u] = off + u * stride < slice;
+            v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
         if (kMultimem) {
-            v0 = multimem_ld_reduce_f4(a.mc + i0);
-            if (has1) v1 = multimem_ld_reduce_f4(a.mc + i1);
+#pragma unroll
+            for (int u = 0; u < kUnroll; ++u)
+                if (has[u]) v[u] = multimem_ld_reduce_f4(a.mc + begin + off + u * stride);
         } else {
-            float4 t0[kArMaxWorld], t1[kArMaxWorld];
+            float4 t[kUnroll][kArMaxWorld];
 #pragma unroll
             for (int q = 0; q < kArMaxWorld; ++q) {
                 if (q < a.world) {
-                    t0[q] = ld_f4(a.bufs[q] + i0);
-                    if (has1) t1[q] = ld_f4(a.bufs[q] + i1);
+#pragma unroll
+                    for (int u = 0; u < kUnroll; ++u)
+                        if (has[u]) t[u][q] = ld_f4(a.bufs[q] + begin + off + u * stride);
                 }
             }
 #pragma unroll
             for (int q = 0; q < kArMaxWorld; ++q) {
                 if (q < a.world) {
-                    v0.x += t0[q].x; v0.y += t0[q].y; v0.z += t0[q].z; v0.w += t0[q].w;
-                    if (has1) { v1.x += t1[q].x; v1.y += t1[q].y; v1.z += t1[q].z; v1.w += t1[q].w; }
+#pragma unroll
+                    for (int u = 0; u < kUnroll; ++u)
+                        if (has[u]) { v[u].x += t[u][q].x; v[u].y += t[u][q].y; v[u].z += t[u][q].z; v[u].w += t[u][q].w; }
                 }
             }
         }
-        finish(a, v0, i0, ss);
-        if (has1) finish(a, v1, i1, ss);
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u)
+            if (has[u]) finish(a, v[u], begin + off + u * stride, ss);
         if (kMultimem) {
-            multimem_st_f4(a.mc + i0, v0);
-            if (has1) multimem_st_f4(a.mc + i1, v1);
+#pragma unroll
+            for (int u = 0; u < kUnroll; ++u)
+                if (has[u]) multimem_st_f4(a.mc + begin + off + u * stride, v[u]);
         } else {
 #pragma unroll
             for (int q = 0; q < kArMaxWorld; ++q) {
                 if (q < a.world) {
-                    st_f4(a.bufs[q] + i0, v0);
-                    if (has1) st_f4(a.bufs[q] + i1, v1);
+#pragma unroll
+                    for (int u = 0; u < kUnroll; ++u)
+                        if (has[u]) st_f4(a.bufs[q] + begin + off + u * stride, v[u]);
                 }
             }
         }
@@ -203,7 +214,7 @@ extern "C" int pb2_allreduce_f32(float* const* peer_bufs, void* const* peer_pads
     if (epoch == 0) { set_error("pb2_allreduce_f32: epoch must be non-zero (pads start zeroed)"); return -1; }
     if (use_multimem && !multicast) { set_error("pb2_allreduce_f32: multimem requested without a multicast pointer"); return -1; }
     if (n == 0) return 0;
-    if (ctas <= 0) ctas = 32;
+    if (ctas <= 0) ctas = 64;
     if (ctas > kArMaxCtas) ctas = kArMaxCtas;
     ArArgs a;
     memset(&a, 0, sizeof(a));

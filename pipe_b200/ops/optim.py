@@ -66,7 +66,7 @@ class FusedClipAdam:
         self.max_norm, self.grad_scale = max_norm, grad_scale
         self.distributed, self.group = distributed, group
         self.replica_group, self.replicas, self.reduce_backend = replica_group, int(replicas), reduce_backend
-        self.reduce_ctas = 32
+        self.reduce_ctas = 64
         self.step_count = 0
         self.module = module
 

@@ -104,7 +104,7 @@ class SymmetricBuffer:
 
     # -- the collective ----------------------------------------------------------------
     def all_reduce_(self, scale: float = 1.0, sumsq: Optional[Tensor] = None, cast_out: Optional[Tensor] = None,
-                    ctas: int = 32, use_multimem: Optional[bool] = None, stream: Optional[int] = None) -> None:
+                    ctas: int = 64, use_multimem: Optional[bool] = None, stream: Optional[int] = None) -> None:
         """In-place ``data <- scale * sum over ranks(data)`` with the fused kernel; every rank
         must call it at the same point of its stream."""
         if self.mode == "torch":
@@ -125,7 +125,8 @@ class SymmetricBuffer:
         lib = _lib.load()
         self.epoch += 1
         if use_multimem is None:
-            use_multimem = bool(self.multicast_ptr)
+            # in-switch reduction pays off once several peers contribute; with two, P2P pull/push wins
+            use_multimem = bool(self.multicast_ptr) and self.world >= 4
         arr = ctypes.c_void_p * self.world
         bufs = arr(*self.peer_data)
         pads = arr(*self.peer_pads)
