@@ -59,6 +59,9 @@ typedef struct pb2_gemm_desc {
     int splits;           /* split-K factor; 0 = choose */
     int stages;           /* TMA ring depth; 0 = choose */
     int reduce_mode;      /* split-K reduction: 0 = choose, 1 = global scratch workspace, 2 = cluster / DSMEM */
+    int a_static;         /* 1: A is a weight that the kernel launched just before this one on the stream does
+                             not write, so its first tiles may be fetched while that kernel is still running
+                             (programmatic dependent launch); 0: wait for the predecessor before any load */
 } pb2_gemm_desc;
 
 size_t pb2_gemm_workspace_bytes(void);

@@ -1,0 +1,300 @@
+// Tensor-core attention core for short sequences (S <= 64): the five small matrix products of
+// attention forward + backward on warp-level MMA (bf16 in, fp32 accumulate), everything else —
+// softmax, dropout mask, the dS recurrence — on the scores held in shared memory.
+//
+// One CTA owns one (sequence, head) pair for the whole pass; Q, K, V (and dO) are gathered from the
+// packed [T, 3E] projection output into zero-padded shared tiles, the S x S score matrix never
+// leaves the SM, and results are scattered straight back into the packed layouts the neighbouring
+// GEMMs read.  The SIMT kernels in attention.cu remain the path for 64 < S <= 128.
+//
+// Why warp-level MMA and not tcgen05 here: at S = 25 the whole problem is a 32 x 32 x 256 product
+// per head; a UMMA tile is 128 rows and needs TMA-swizzled operands, TMEM allocation and an mbarrier
+// pipeline — fixed costs that exceed the work.  These products are latency-, not throughput-bound
+// (attention is <= 0.2 % of the model's FLOPs).
+//
+// Reference counterpart: nn.MultiheadAttention core (main.py:148).  SURVEY.md K3.
+#include <mma.h>
+
+#include "common.cuh"
+#include "pipe_b200.h"
+
+namespace pb2 {
+
+using namespace nvcuda;
+
+constexpr int kTcThreads = 256;
+constexpr int kTcWarps = kTcThreads / 32;
+
+struct AttnTc {
+    int NB, S, H, D, E, SP;          // SP = S rounded up to 16
+    float scale;
+    int causal;
+    float drop_p;
+    unsigned long long seed, rng_stream;
+};
+
+typedef wmma::fragment<wmma::matrix_a, 16, 16, 16, __nv_bfloat16, wmma::row_major> FragA;
+typedef wmma::fragment<wmma::matrix_a, 16, 16, 16, __nv_bfloat16, wmma::col_major> FragAT;
+typedef wmma::fragment<wmma::matrix_b, 16, 16, 16, __nv_bfloat16, wmma::row_major> FragB;
+typedef wmma::fragment<wmma::matrix_b, 16, 16, 16, __nv_bfloat16, wmma::col_major> FragBT;
+typedef wmma::fragment<wmma::accumulator, 16, 16, 16, float> FragC;
+
+// Gather `count` [S, D] head slices into zero-padded [SP, D + 8] shared tiles.
+__device__ __forceinline__ void tc_gather(const __nv_bfloat16* const* base, const long long* ld, __nv_bfloat16* const* dst,
+                                          int count, int NB, int S, int SP, int D, int n) {
+    const int dpad = D + 8, vec_per_row = D / 8;
+    const int per_mat = SP * vec_per_row;
+    for (int t = threadIdx.x; t < per_mat * count; t += blockDim.x) {
+        const int m = t / per_mat, r = t - m * per_mat;
+        const int s = r / vec_per_row, v = r - s * vec_per_row;
+        uint4 raw = make_uint4(0u, 0u, 0u, 0u);
+        if (s < S) raw = *reinterpret_cast<const uint4*>(base[m] + (static_cast<size_t>(s) * NB + n) * ld[m] + v * 8);
+        *reinterpret_cast<uint4*>(dst[m] + s * dpad + v * 8) = raw;
+    }
+}
+
+// C[SP x SP] (fp32, ld = SP + 8) = A[SP x D] * B[SP x D]^T, both row-major bf16 with ld = D + 8.
+__device__ __forceinline__ void tc_abt(const __nv_bfloat16* A, const __nv_bfloat16* B, float* C, int SP, int D) {
+    const int warp = threadIdx.x >> 5, tiles = SP / 16, dpad = D + 8, cpad = SP + 8;
+    for (int t = warp; t < tiles * tiles; t += kTcWarps) {
+        const int ti = t / tiles, tj = t % tiles;
+        FragC acc;
+        wmma::fill_fragment(acc, 0.f);
+        for (int k = 0; k < D; k += 16) {
+            FragA a;
+            FragBT b;
+            wmma::load_matrix_sync(a, A + ti * 16 * dpad + k, dpad);
+            wmma::load_matrix_sync(b, B + tj * 16 * dpad + k, dpad);
+            wmma::mma_sync(acc, a, b, acc);
+        }
+        wmma::store_matrix_sync(C + ti * 16 * cpad + tj * 16, acc, cpad, wmma::mem_row_major);
+    }
+}
+
+// Softmax over the first S columns of the first S rows of `sc` (scaled by `scale`), in place.
+__device__ __forceinline__ void tc_softmax(float* sc, int S, int SP, float scale, int causal) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, cpad = SP + 8;
+    for (int i = warp; i < SP; i += kTcWarps) {
+        float* r = sc + i * cpad;
+        if (i >= S) {
+            for (int j = lane; j < SP; j += 32) r[j] = 0.f;
+            continue;
+        }
+        const int lim = causal ? i + 1 : S;
+        float mx = -INFINITY;
+        for (int j = lane; j < lim; j += 32) mx = fmaxf(mx, r[j] * scale);
+        mx = warp_max(mx);
+        float se = 0.f;
+        for (int j = lane; j < lim; j += 32) {
+            const float e = __expf(r[j] * scale - mx);
+            r[j] = e;
+            se += e;
+        }
+        se = warp_sum(se);
+        const float inv = 1.f / se;
+        for (int j = lane; j < SP; j += 32) r[j] = j < lim ? r[j] * inv : 0.f;
+    }
+}
+
+__device__ __forceinline__ float tc_keep(const CounterRng& rng, const AttnTc& a, uint32_t thr, float inv_keep, int n, int h,
+                                         int i, int j) {
+    if (a.drop_p <= 0.f) return 1.f;
+    const uint64_t idx = ((static_cast<uint64_t>(n) * a.H + h) * a.S + i) * a.S + j;
+    return dropout_keep(rng, a.rng_stream, idx, thr) ? inv_keep : 0.f;
+}
+
+// out rows (< S) of a [16 x 16] fp32 tile held in this warp's staging area -> bf16 global
+__device__ __forceinline__ void tc_emit_tile(const float* stage, __nv_bfloat16* dst_row0, long long ld_dst, int NB,
+                                             int row0, int S) {
+    const int lane = threadIdx.x & 31;
+    // 16 rows x 8 column pairs = 128 pairs, 4 per lane
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const int p = lane + q * 32, r = p >> 3, c2 = p & 7;
+        if (row0 + r < S) {
+            const float2 v = *reinterpret_cast<const float2*>(stage + r * 24 + c2 * 2);
+            reinterpret_cast<__nv_bfloat162*>(dst_row0 + static_cast<size_t>(r) * NB * ld_dst)[c2] =
+                __floats2bfloat162_rn(v.x, v.y);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kTcThreads)
+attn_tc_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out, const AttnTc a) {
+    pdl_launch_dependents();
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int S = a.S, SP = a.SP, D = a.D, dpad = D + 8, cpad = SP + 8;
+    __nv_bfloat16* q = reinterpret_cast<__nv_bfloat16*>(smem);
+    __nv_bfloat16* k = q + SP * dpad;
+    __nv_bfloat16* v = k + SP * dpad;
+    float* sc = reinterpret_cast<float*>(v + SP * dpad);
+    __nv_bfloat16* pb = reinterpret_cast<__nv_bfloat16*>(sc + SP * cpad);
+    float* stage = reinterpret_cast<float*>(pb + SP * cpad) + (threadIdx.x >> 5) * (16 * 24);
+    const int n = blockIdx.x / a.H, h = blockIdx.x % a.H;
+    const long long ld = 3LL * a.E;
+
+    {
+        const __nv_bfloat16* base[3] = {qkv + h * D, qkv + a.E + h * D, qkv + 2 * a.E + h * D};
+        const long long lds[3] = {ld, ld, ld};
+        __nv_bfloat16* dst[3] = {q, k, v};
+        tc_gather(base, lds, dst, 3, a.NB, S, SP, D, n);
+    }
+    __syncthreads();
+    tc_abt(q, k, sc, SP, D);
+    __syncthreads();
+    tc_softmax(sc, S, SP, a.scale, a.causal);
+    __syncthreads();
+    {
+        const CounterRng rng(a.seed);
+        const uint32_t thr = static_cast<uint32_t>(fminf(a.drop_p, 0.999999f) * 4294967296.0f);
+        const float inv_keep = a.drop_p > 0.f ? 1.f / (1.f - a.drop_p) : 1.f;
+        for (int p = threadIdx.x; p < SP * SP; p += blockDim.x) {
+            const int i = p / SP, j = p % SP;
+            float w = sc[i * cpad + j];
+            if (i < S && j < S) w *= tc_keep(rng, a, thr, inv_keep, n, h, i, j);
+            pb[i * cpad + j] = __float2bfloat16(w);
+        }
+    }
+    __syncthreads();
+
+    // O = P V
+    const int warp = threadIdx.x >> 5, rt = SP / 16, ct = D / 16;
+    for (int t = warp; t < rt * ct; t += kTcWarps) {
+        const int ti = t / ct, tc = t % ct;
+        FragC acc;
+        wmma::fill_fragment(acc, 0.f);
+        for (int kk = 0; kk < SP; kk += 16) {
+            FragA pa;
+            FragB vb;
+            wmma::load_matrix_sync(pa, pb + ti * 16 * cpad + kk, cpad);
+            wmma::load_matrix_sync(vb, v + kk * dpad + tc * 16, dpad);
+            wmma::mma_sync(acc, pa, vb, acc);
+        }
+        wmma::store_matrix_sync(stage, acc, 24, wmma::mem_row_major);
+        __syncwarp();
+        tc_emit_tile(stage, out + (static_cast<size_t>(ti * 16) * a.NB + n) * a.E + h * D + tc * 16, a.E, a.NB, ti * 16, S);
+        __syncwarp();
+    }
+}
+
+__global__ void __launch_bounds__(kTcThreads)
+attn_tc_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* __restrict__ dout,
+                   __nv_bfloat16* __restrict__ dqkv, const AttnTc a) {
+    pdl_launch_dependents();
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int S = a.S, SP = a.SP, D = a.D, dpad = D + 8, cpad = SP + 8;
+    __nv_bfloat16* q = reinterpret_cast<__nv_bfloat16*>(smem);
+    __nv_bfloat16* k = q + SP * dpad;
+    __nv_bfloat16* v = k + SP * dpad;
+    __nv_bfloat16* dO = v + SP * dpad;
+    float* P = reinterpret_cast<float*>(dO + SP * dpad);
+    float* dP = P + SP * cpad;
+    __nv_bfloat16* Pd = reinterpret_cast<__nv_bfloat16*>(dP + SP * cpad);     // dropped-out probabilities (bf16)
+    __nv_bfloat16* dS = Pd + SP * cpad;                                       // score gradients (bf16)
+    float* stage = reinterpret_cast<float*>(dS + SP * cpad) + (threadIdx.x >> 5) * (16 * 24);
+    const int n = blockIdx.x / a.H, h = blockIdx.x % a.H;
+    const long long ld = 3LL * a.E;
+
+    {
+        const __nv_bfloat16* base[4] = {qkv + h * D, qkv + a.E + h * D, qkv + 2 * a.E + h * D, dout + h * D};
+        const long long lds[4] = {ld, ld, ld, a.E};
+        __nv_bfloat16* dst[4] = {q, k, v, dO};
+        tc_gather(base, lds, dst, 4, a.NB, S, SP, D, n);
+    }
+    __syncthreads();
+    tc_abt(q, k, P, SP, D);          // raw scores
+    tc_abt(dO, v, dP, SP, D);        // gradient w.r.t. the dropped-out probabilities
+    __syncthreads();
+    tc_softmax(P, S, SP, a.scale, a.causal);
+    __syncthreads();
+
+    // per row: Pd = P * keep,  dPm = dP * keep,  delta = sum_j dPm * P,  dS = P * (dPm - delta) * scale
+    {
+        const CounterRng rng(a.seed);
+        const uint32_t thr = static_cast<uint32_t>(fminf(a.drop_p, 0.999999f) * 4294967296.0f);
+        const float inv_keep = a.drop_p > 0.f ? 1.f / (1.f - a.drop_p) : 1.f;
+        const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+        for (int i = warp; i < SP; i += kTcWarps) {
+            float dlt = 0.f;
+            for (int j = lane; j < SP; j += 32) {
+                const float p = P[i * cpad + j];
+                float ks = 0.f;
+                if (i < S && j < S) ks = tc_keep(rng, a, thr, inv_keep, n, h, i, j);
+                const float dpm = dP[i * cpad + j] * ks;
+                Pd[i * cpad + j] = __float2bfloat16(p * ks);
+                dP[i * cpad + j] = dpm;
+                dlt += dpm * p;
+            }
+            dlt = warp_sum(dlt);
+            for (int j = lane; j < SP; j += 32)
+                dS[i * cpad + j] = __float2bfloat16(P[i * cpad + j] * (dP[i * cpad + j] - dlt) * a.scale);
+        }
+    }
+    __syncthreads();
+
+    // dV = Pd^T dO,  dQ = dS K,  dK = dS^T Q   — 3 x (SP/16) x (D/16) output tiles
+    const int warp = threadIdx.x >> 5, rt = SP / 16, ct = D / 16, per = rt * ct;
+    for (int t = warp; t < 3 * per; t += kTcWarps) {
+        const int which = t / per, r = t % per, ti = r / ct, tc = r % ct;
+        FragC acc;
+        wmma::fill_fragment(acc, 0.f);
+        for (int kk = 0; kk < SP; kk += 16) {
+            FragB b;
+            if (which == 1) {            // dQ: A = dS (row-major), B = K
+                FragA am;
+                wmma::load_matrix_sync(am, dS + ti * 16 * cpad + kk, cpad);
+                wmma::load_matrix_sync(b, k + kk * dpad + tc * 16, dpad);
+                wmma::mma_sync(acc, am, b, acc);
+            } else {                     // dV: A = Pd^T, B = dO;  dK: A = dS^T, B = Q
+                FragAT at;
+                const __nv_bfloat16* src = which == 0 ? Pd : dS;
+                wmma::load_matrix_sync(at, src + kk * cpad + ti * 16, cpad);
+                wmma::load_matrix_sync(b, (which == 0 ? dO : q) + kk * dpad + tc * 16, dpad);
+                wmma::mma_sync(acc, at, b, acc);
+            }
+        }
+        wmma::store_matrix_sync(stage, acc, 24, wmma::mem_row_major);
+        __syncwarp();
+        const int col0 = (which == 0 ? 2 * a.E : which == 1 ? 0 : a.E) + h * D + tc * 16;
+        tc_emit_tile(stage, dqkv + (static_cast<size_t>(ti * 16) * a.NB + n) * ld + col0, ld, a.NB, ti * 16, S);
+        __syncwarp();
+    }
+}
+
+size_t attn_tc_smem(int SP, int D, bool bwd) {
+    const size_t dpad = D + 8, cpad = SP + 8;
+    size_t b = (bwd ? 4 : 3) * SP * dpad * 2;             // Q K V (dO)
+    b += (bwd ? 2 : 1) * SP * cpad * 4;                    // fp32 score matrices
+    b += (bwd ? 2 : 1) * SP * cpad * 2;                    // bf16 probability / gradient matrices
+    b += kTcWarps * 16 * 24 * 4;                           // per-warp output staging
+    return b + 128;
+}
+
+bool attn_tc_supported(int S, int D) { return S <= 64 && D % 16 == 0 && D <= 256; }
+
+int attn_tc_fwd(const void* qkv, void* out, int NB, int S, int H, int D, int causal, float drop_p,
+                unsigned long long seed, unsigned long long rng_stream, cudaStream_t stream) {
+    const int SP = (S + 15) / 16 * 16;
+    AttnTc a{NB, S, H, D, H * D, SP, 1.f / sqrtf(static_cast<float>(D)), causal, drop_p, seed, rng_stream};
+    const size_t smem = attn_tc_smem(SP, D, false);
+    if (ensure_max_smem(reinterpret_cast<const void*>(attn_tc_fwd_kernel), 227 * 1024)) return -1;
+    attn_tc_fwd_kernel<<<NB * H, kTcThreads, smem, stream>>>(static_cast<const __nv_bfloat16*>(qkv),
+                                                             static_cast<__nv_bfloat16*>(out), a);
+    PB2_LAUNCHED("attn_tc_fwd_kernel");
+    return 0;
+}
+
+int attn_tc_bwd(const void* qkv, const void* dout, void* dqkv, int NB, int S, int H, int D, int causal, float drop_p,
+                unsigned long long seed, unsigned long long rng_stream, cudaStream_t stream) {
+    const int SP = (S + 15) / 16 * 16;
+    AttnTc a{NB, S, H, D, H * D, SP, 1.f / sqrtf(static_cast<float>(D)), causal, drop_p, seed, rng_stream};
+    const size_t smem = attn_tc_smem(SP, D, true);
+    if (ensure_max_smem(reinterpret_cast<const void*>(attn_tc_bwd_kernel), 227 * 1024)) return -1;
+    attn_tc_bwd_kernel<<<NB * H, kTcThreads, smem, stream>>>(static_cast<const __nv_bfloat16*>(qkv),
+                                                             static_cast<const __nv_bfloat16*>(dout),
+                                                             static_cast<__nv_bfloat16*>(dqkv), a);
+    PB2_LAUNCHED("attn_tc_bwd_kernel");
+    return 0;
+}
+
+}  // namespace pb2

@@ -126,6 +126,18 @@ constexpr uint64_t kEvictFirst = 0x12F0000000000000ull;
 constexpr uint64_t kEvictNormal = 0x1000000000000000ull;
 constexpr uint64_t kEvictLast = 0x14F0000000000000ull;
 
+// ---- programmatic dependent launch ---------------------------------------------------
+// launch_dependents: the next kernel in the stream (if launched with programmatic serialization)
+// may start its prologue now.  wait: block until every prerequisite grid has completed and its
+// writes are visible.  Everything a kernel does before its wait must not touch data that the
+// preceding kernel produces.
+__device__ __forceinline__ void pdl_launch_dependents() {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+__device__ __forceinline__ void pdl_wait() {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 // ---- thread-block clusters / distributed shared memory ------------------------------
 __device__ __forceinline__ uint32_t cluster_ctarank() {
     uint32_t r;

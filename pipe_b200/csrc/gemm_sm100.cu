@@ -52,6 +52,7 @@ struct GemmArgs {
     int k_blocks_per_split;
     int splits;
     int stages;
+    int ring_bytes;                  // bytes reserved for the TMA ring (>= the epilogue staging area)
     int tmem_cols;
     // epilogue
     void* out;
@@ -71,6 +72,7 @@ struct GemmArgs {
     float* sumsq;                    // optional: += sum of squares of what was written
     float* partials;
     unsigned int* counters;
+    int a_static;                    // A (weights) is not produced by the preceding kernel: prefetch before the PDL wait
     int cluster_reduce;              // splits CTAs of a tile form a cluster and reduce through DSMEM
     int local_chunks;                // 16-column chunks each cluster rank owns (ceil(n_chunks / splits))
     unsigned long long* debug_ts;    // optional: per-CTA phase timestamps (globaltimer ns), 8 per CTA
@@ -214,6 +216,69 @@ __device__ __forceinline__ void epilogue_chunk(const GemmArgs& g, const EpiCtx& 
     }
 }
 
+// Row-major store of one 16-column chunk through a per-warp shared-memory transpose.
+// In the TMEM register layout a thread owns one accumulator ROW, so a direct store makes every
+// warp-wide instruction touch 32 rows x 16 bytes (half-filled sectors, 32 different lines).  Staging
+// the 32 x 16 block in shared memory lets each instruction write 8 rows x 64 contiguous bytes instead
+// (whole sectors).  Used for the plain / accumulate / alpha / bias / sumsq epilogue of large
+// row-major outputs — the weight-gradient GEMMs, whose 64 MB fp32 results are their main cost.
+__device__ __forceinline__ void epilogue_chunk_staged(const GemmArgs& g, float* st, float (&v)[16], int m_tile0,
+                                                      int quarter, int lane, int n_first, float bias_m, float& ss) {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) v[j] = v[j] * g.alpha + bias_m;
+#pragma unroll
+    for (int j = 0; j < 16; j += 4)
+        *reinterpret_cast<float4*>(st + lane * 20 + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+    __syncwarp();
+    const int r8 = lane >> 2, c4 = (lane & 3) * 4;
+    const int n = n_first + c4;
+#pragma unroll
+    for (int rr = 0; rr < 4; ++rr) {
+        const int row = rr * 8 + r8;
+        const int m = m_tile0 + quarter * 32 + row;
+        float4 o = *reinterpret_cast<const float4*>(st + row * 20 + c4);
+        if (g.bias && !g.bias_along_m) {
+            if (n < g.N) o.x += g.bias[n];
+            if (n + 1 < g.N) o.y += g.bias[n + 1];
+            if (n + 2 < g.N) o.z += g.bias[n + 2];
+            if (n + 3 < g.N) o.w += g.bias[n + 3];
+        }
+        if (m >= g.M || n >= g.N) continue;
+        const long long idx = static_cast<long long>(m) * g.ld_out + n;
+        if (g.out_f32) {
+            float* dst = static_cast<float*>(g.out) + idx;
+            if (n + 3 < g.N && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+                if (g.accumulate) {
+                    const float4 old = *reinterpret_cast<const float4*>(dst);
+                    o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
+                }
+                *reinterpret_cast<float4*>(dst) = o;
+                ss += o.x * o.x + o.y * o.y + o.z * o.z + o.w * o.w;
+            } else {
+                float e[4] = {o.x, o.y, o.z, o.w};
+                for (int j = 0; j < 4 && n + j < g.N; ++j) {
+                    if (g.accumulate) e[j] += dst[j];
+                    dst[j] = e[j];
+                    ss += e[j] * e[j];
+                }
+            }
+        } else {
+            __nv_bfloat16* dst = static_cast<__nv_bfloat16*>(g.out) + idx;
+            if (n + 3 < g.N && ((reinterpret_cast<uintptr_t>(dst) & 7) == 0)) {
+                uint2 pk;
+                *reinterpret_cast<__nv_bfloat162*>(&pk.x) = __floats2bfloat162_rn(o.x, o.y);
+                *reinterpret_cast<__nv_bfloat162*>(&pk.y) = __floats2bfloat162_rn(o.z, o.w);
+                *reinterpret_cast<uint2*>(dst) = pk;
+            } else {
+                const float e[4] = {o.x, o.y, o.z, o.w};
+                for (int j = 0; j < 4 && n + j < g.N; ++j) dst[j] = __float2bfloat16(e[j]);
+            }
+            ss += o.x * o.x + o.y * o.y + o.z * o.z + o.w * o.w;
+        }
+    }
+    __syncwarp();
+}
+
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                     const GemmArgs g) {
@@ -223,7 +288,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     const uint32_t a_bytes = kBlockM * kBlockK * 2;
     const uint32_t b_bytes = g.block_n * kBlockK * 2;
     const uint32_t stage_bytes = a_bytes + b_bytes;
-    SmemCtl* ctl = reinterpret_cast<SmemCtl*>(smem + static_cast<size_t>(g.stages) * stage_bytes);
+    SmemCtl* ctl = reinterpret_cast<SmemCtl*>(smem + g.ring_bytes);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -235,6 +300,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     if (kb_count > g.k_blocks_per_split) kb_count = g.k_blocks_per_split;
 
     if (threadIdx.x == 0) PB2_TS(0);
+    pdl_launch_dependents();          // let the next kernel's prologue overlap this kernel
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmap_a);
         tma_prefetch_desc(&tmap_b);
@@ -258,7 +324,24 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     if (warp == 0) {
         // ===================== TMA producer =====================
         if (elect_one()) {
-            for (int it = 0; it < kb_count; ++it) {
+            // Programmatic dependent launch: this kernel may have started while its predecessor is
+            // still running.  Weights do not depend on it, so the first ring of A tiles is requested
+            // right away; the token tiles (and everything downstream of them) wait for it to finish.
+            int pre = 0;
+            if (g.a_static) {
+                pre = kb_count < g.stages ? kb_count : g.stages;
+                for (int it = 0; it < pre; ++it) {
+                    uint8_t* sa = smem + static_cast<size_t>(it) * stage_bytes;
+                    mbar_expect_tx(&ctl->full[it], stage_bytes);
+                    tma_load_2d(sa, &tmap_a, &ctl->full[it], (kb_begin + it) * kBlockK, m0, kEvictFirst);
+                }
+            }
+            pdl_wait();
+            for (int it = 0; it < pre; ++it) {
+                uint8_t* sb = smem + static_cast<size_t>(it) * stage_bytes + a_bytes;
+                tma_load_2d(sb, &tmap_b, &ctl->full[it], (kb_begin + it) * kBlockK, n0, kEvictLast);
+            }
+            for (int it = pre; it < kb_count; ++it) {
                 const int s = it % g.stages;
                 const uint32_t round = it / g.stages;
                 mbar_wait(&ctl->empty[s], (round & 1) ^ 1);
@@ -397,6 +480,10 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                      g.drop_p > 0.f ? 1.f / (1.f - g.drop_p) : 1.f, 0.f, m_glob < g.M};
             if (g.bias && g.bias_along_m && e.row_ok) e.bias_m = g.bias[m_glob];
             float ss = 0.f;
+            // plain row-major epilogues go through the shared-memory transpose (the TMA ring is idle
+            // once the accumulator is complete); everything fancier takes the per-row path
+            const bool staged = !g.transpose_out && !g.relu && g.drop_p <= 0.f && !g.mask_src && !g.addend;
+            if (!(g.bias && g.bias_along_m)) e.bias_m = 0.f;
             const float* others = g.partials + static_cast<size_t>(tile) * g.splits * tile_elems + m_local;
             for (int c = half * 16; c < g.block_n; c += 32) {
                 uint32_t r[16];
@@ -414,7 +501,13 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
 #pragma unroll
                     for (int j = 0; j < 16; ++j) v[j] += t[j];
                 }
-                if (n0 + c < g.N) epilogue_chunk(g, e, v, m_glob, n0 + c, ss);
+                if (n0 + c < g.N) {
+                    if (staged)
+                        epilogue_chunk_staged(g, reinterpret_cast<float*>(smem) + (warp - 2) * (32 * 20), v, m0, quarter, lane,
+                                              n0 + c, e.bias_m, ss);
+                    else
+                        epilogue_chunk(g, e, v, m_glob, n0 + c, ss);
+                }
             }
             if (g.sumsq) {
                 ss = warp_sum(ss);
@@ -548,13 +641,16 @@ static int gemm_launch(const pb2_gemm_desc* d, float* partials, unsigned int* co
     g.addend = static_cast<const __nv_bfloat16*>(d->addend);
     g.accumulate = d->accumulate; g.alpha = d->alpha == 0.f ? 1.f : d->alpha;
     g.sumsq = d->sumsq;
+    g.a_static = d->a_static;
     g.debug_ts = g_debug_ts;
 
     CUtensorMap ta, tb;
     if (make_tmap_bf16_2d(&ta, d->a, d->M, d->K, d->lda, kBlockM, kBlockK)) return -1;
     if (make_tmap_bf16_2d(&tb, d->b, d->N, d->K, d->ldb, bn, kBlockK)) return -1;
 
-    const size_t smem = static_cast<size_t>(stages) * stage_bytes + sizeof(SmemCtl) + 1024;
+    g.ring_bytes = stages * stage_bytes;
+    if (g.ring_bytes < kEpilogueWarps * 32 * 20 * 4) g.ring_bytes = kEpilogueWarps * 32 * 20 * 4;   // staging needs 20 KB
+    const size_t smem = static_cast<size_t>(g.ring_bytes) + sizeof(SmemCtl) + 1024;
     if (ensure_max_smem(reinterpret_cast<const void*>(gemm_bf16_tn_kernel), 227 * 1024)) return -1;
     cudaLaunchConfig_t cfg;
     memset(&cfg, 0, sizeof(cfg));
@@ -562,15 +658,22 @@ static int gemm_launch(const pb2_gemm_desc* d, float* partials, unsigned int* co
     cfg.blockDim = dim3(kThreads);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
+    int n_attr = 0;
+    // programmatic dependent launch: the kernel's prologue (and, for static weights, its first
+    // weight tiles) may overlap the tail of the preceding kernel; griddepcontrol.wait orders the rest
+    attr[n_attr].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[n_attr].val.programmaticStreamSerializationAllowed = 1;
+    ++n_attr;
     if (g.cluster_reduce) {
-        attr[0].id = cudaLaunchAttributeClusterDimension;
-        attr[0].val.clusterDim.x = 1;
-        attr[0].val.clusterDim.y = 1;
-        attr[0].val.clusterDim.z = splits;
-        cfg.attrs = attr;
-        cfg.numAttrs = 1;
+        attr[n_attr].id = cudaLaunchAttributeClusterDimension;
+        attr[n_attr].val.clusterDim.x = 1;
+        attr[n_attr].val.clusterDim.y = 1;
+        attr[n_attr].val.clusterDim.z = splits;
+        ++n_attr;
     }
+    cfg.attrs = attr;
+    cfg.numAttrs = n_attr;
     PB2_CUDA(cudaLaunchKernelEx(&cfg, gemm_bf16_tn_kernel, ta, tb, g));
     PB2_LAUNCHED("gemm_bf16_tn_kernel");
     return 0;

@@ -31,6 +31,7 @@ int linear(const pb2_encoder_layer* L, const Lin& w, const void* act, int T, voi
     d.drop_p = drop_p; d.seed = L->seed; d.rng_stream = rng_stream;
     d.mask_src = mask_src; d.mask_scale = mask_scale; d.addend = addend;
     d.alpha = 1.f;
+    d.a_static = 1;       // weight shadows are only written by the optimizer kernel, never by a layer kernel
     return pb2_gemm_bf16(&d, L->workspace, L->workspace_bytes, stream);
 }
 

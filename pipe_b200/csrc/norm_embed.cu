@@ -76,6 +76,7 @@ __global__ void __launch_bounds__(kLnThreads)
 add_ln_fwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ h,
                   const float* __restrict__ gamma, const float* __restrict__ beta, __nv_bfloat16* __restrict__ y,
                   float* __restrict__ mean_out, float* __restrict__ rstd_out, int E, float eps) {
+    pdl_launch_dependents();
     __shared__ float red[32];
     const size_t row = blockIdx.x;
     const __nv_bfloat16* xr = x + row * E;
@@ -144,6 +145,7 @@ add_ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __r
                   __nv_bfloat16* __restrict__ dres, __nv_bfloat16* __restrict__ dh, float* __restrict__ dgamma,
                   float* __restrict__ dbeta, int E, float drop_p, unsigned long long seed,
                   unsigned long long rng_stream) {
+    pdl_launch_dependents();
     __shared__ float red[32];
     const size_t row = blockIdx.x;
     const float mean = mean_in[row], rstd = rstd_in[row];
@@ -213,6 +215,7 @@ __global__ void __launch_bounds__(256)
 embed_fwd_kernel(const long long* __restrict__ tokens, const float* __restrict__ weight,
                  const float* __restrict__ pe, __nv_bfloat16* __restrict__ out, int N, int S, int E, float scale,
                  float drop_p, unsigned long long seed, unsigned long long rng_stream) {
+    pdl_launch_dependents();
     const int row = blockIdx.x;            // row = s * N + n
     const int s = row / N, n = row % N;
     const long long tok = tokens[static_cast<size_t>(n) * S + s];
@@ -242,6 +245,7 @@ __global__ void __launch_bounds__(256)
 embed_bwd_kernel(const long long* __restrict__ tokens, const __nv_bfloat16* __restrict__ dout,
                  float* __restrict__ dweight, int N, int S, int E, float scale, float drop_p,
                  unsigned long long seed, unsigned long long rng_stream) {
+    pdl_launch_dependents();
     const int row = blockIdx.x;
     const int s = row / N, n = row % N;
     const long long tok = tokens[static_cast<size_t>(n) * S + s];
@@ -273,6 +277,7 @@ __global__ void __launch_bounds__(512)
 ce_fwd_bwd_kernel(__nv_bfloat16* __restrict__ logits, const long long* __restrict__ targets,
                   float* __restrict__ loss_rows, const float* __restrict__ row_scale, int V, long long ld,
                   int write_grad) {
+    pdl_launch_dependents();
     __shared__ float red[32];
     const size_t row = blockIdx.x;
     __nv_bfloat16* l = logits + row * ld;
@@ -304,6 +309,7 @@ ce_fwd_bwd_kernel(__nv_bfloat16* __restrict__ logits, const long long* __restric
 __global__ void __launch_bounds__(256)
 transpose_colsum_kernel(const __nv_bfloat16* __restrict__ src, long long ld_src, __nv_bfloat16* __restrict__ dst,
                         long long ld_dst, int R, int C, float* __restrict__ colsum, float scale) {
+    pdl_launch_dependents();
     __shared__ __nv_bfloat16 tile[32][33];
     const int c0 = blockIdx.x * 32;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;      // 32 x 8
@@ -343,6 +349,7 @@ transpose_colsum_kernel(const __nv_bfloat16* __restrict__ src, long long ld_src,
 // a layer's backward stacks all its wgrad operands with a single kernel.
 __global__ void __launch_bounds__(256)
 transpose_multi_kernel(const pb2_transpose_jobs jobs) {
+    pdl_launch_dependents();
     const pb2_transpose_job j = jobs.job[blockIdx.y];
     if (blockIdx.x * 32 >= j.C) return;
     __shared__ __nv_bfloat16 tile[32][33];

@@ -35,6 +35,7 @@ class GemmDesc(ctypes.Structure):
         ("sumsq", ctypes.c_void_p),
         ("block_n", ctypes.c_int), ("splits", ctypes.c_int), ("stages", ctypes.c_int),
         ("reduce_mode", ctypes.c_int),
+        ("a_static", ctypes.c_int),
     ]
 
 
