@@ -23,6 +23,16 @@ namespace pb2 {
 using namespace nvcuda;
 
 constexpr int kTcThreads = 256;
+
+// debug: phase timestamps of CTA 0 of the last tensor-core attention launch (globaltimer ns)
+__device__ unsigned long long g_attn_ts[16];
+__device__ __forceinline__ void attn_ts(int slot) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        g_attn_ts[slot] = t;
+    }
+}
 constexpr int kTcWarps = kTcThreads / 32;
 
 struct AttnTc {
@@ -39,17 +49,46 @@ typedef wmma::fragment<wmma::matrix_b, 16, 16, 16, __nv_bfloat16, wmma::row_majo
 typedef wmma::fragment<wmma::matrix_b, 16, 16, 16, __nv_bfloat16, wmma::col_major> FragBT;
 typedef wmma::fragment<wmma::accumulator, 16, 16, 16, float> FragC;
 
-// Gather `count` [S, D] head slices into zero-padded [SP, D + 8] shared tiles.
-__device__ __forceinline__ void tc_gather(const __nv_bfloat16* const* base, const long long* ld, __nv_bfloat16* const* dst,
-                                          int count, int NB, int S, int SP, int D, int n) {
-    const int dpad = D + 8, vec_per_row = D / 8;
-    const int per_mat = SP * vec_per_row;
-    for (int t = threadIdx.x; t < per_mat * count; t += blockDim.x) {
-        const int m = t / per_mat, r = t - m * per_mat;
-        const int s = r / vec_per_row, v = r - s * vec_per_row;
-        uint4 raw = make_uint4(0u, 0u, 0u, 0u);
-        if (s < S) raw = *reinterpret_cast<const uint4*>(base[m] + (static_cast<size_t>(s) * NB + n) * ld[m] + v * 8);
-        *reinterpret_cast<uint4*>(dst[m] + s * dpad + v * 8) = raw;
+// Gather up to four [S, D] head slices into zero-padded [SP, D + 8] shared tiles.  A warp covers
+// whole rows (lane -> 16-byte vector of the row), four row-groups are requested before the first
+// shared store, and the loop carries no integer division: the kernel is latency-bound, so both the
+// L2 round trips and the index arithmetic are on its critical path.
+__device__ __forceinline__ void tc_gather(const __nv_bfloat16* b0, const __nv_bfloat16* b1, const __nv_bfloat16* b2,
+                                          const __nv_bfloat16* b3, long long ld012, long long ld3, __nv_bfloat16* d0,
+                                          __nv_bfloat16* d1, __nv_bfloat16* d2, __nv_bfloat16* d3, int count, int NB, int S,
+                                          int SP, int D, int n) {
+    const int dpad = D + 8, vec_per_row = D / 8;              // 8 .. 32 vectors per row
+    const int lanes_per_row = vec_per_row >= 32 ? 32 : vec_per_row;
+    const int rows_per_warp = 32 / lanes_per_row;             // rows one warp instruction covers
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int sub = lane / lanes_per_row, v = lane - sub * lanes_per_row;
+    const int total_rows = count * SP;
+    const int step = kTcWarps * rows_per_warp;
+    constexpr int kBatch = 4;
+    for (int r0 = warp * rows_per_warp + sub; r0 < total_rows; r0 += step * kBatch) {
+        uint4 raw[kBatch];
+#pragma unroll
+        for (int u = 0; u < kBatch; ++u) {
+            const int R = r0 + u * step;
+            raw[u] = make_uint4(0u, 0u, 0u, 0u);
+            if (R < total_rows && v < vec_per_row) {
+                const int m = (R >= SP) + (R >= 2 * SP) + (R >= 3 * SP);
+                const int s = R - m * SP;
+                const __nv_bfloat16* base = m == 0 ? b0 : m == 1 ? b1 : m == 2 ? b2 : b3;
+                const long long ld = m == 3 ? ld3 : ld012;
+                if (s < S) raw[u] = *reinterpret_cast<const uint4*>(base + (static_cast<size_t>(s) * NB + n) * ld + v * 8);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < kBatch; ++u) {
+            const int R = r0 + u * step;
+            if (R < total_rows && v < vec_per_row) {
+                const int m = (R >= SP) + (R >= 2 * SP) + (R >= 3 * SP);
+                const int s = R - m * SP;
+                __nv_bfloat16* dst = m == 0 ? d0 : m == 1 ? d1 : m == 2 ? d2 : d3;
+                *reinterpret_cast<uint4*>(dst + s * dpad + v * 8) = raw[u];
+            }
+        }
     }
 }
 
@@ -72,27 +111,39 @@ __device__ __forceinline__ void tc_abt(const __nv_bfloat16* A, const __nv_bfloat
 }
 
 // Softmax over the first S columns of the first S rows of `sc` (scaled by `scale`), in place.
+// Eight lanes share a row, so 32 rows are in flight at once (a warp-per-row loop would walk the rows
+// one latency chain after another).  SP <= 64: at most 8 columns per lane.
 __device__ __forceinline__ void tc_softmax(float* sc, int S, int SP, float scale, int causal) {
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, cpad = SP + 8;
-    for (int i = warp; i < SP; i += kTcWarps) {
+    const int sub = threadIdx.x & 7, cpad = SP + 8;
+    for (int i = threadIdx.x >> 3; i < SP; i += kTcThreads / 8) {
         float* r = sc + i * cpad;
-        if (i >= S) {
-            for (int j = lane; j < SP; j += 32) r[j] = 0.f;
-            continue;
-        }
-        const int lim = causal ? i + 1 : S;
+        const int lim = i < S ? (causal ? i + 1 : S) : 0;
+        float x[8];
         float mx = -INFINITY;
-        for (int j = lane; j < lim; j += 32) mx = fmaxf(mx, r[j] * scale);
-        mx = warp_max(mx);
-        float se = 0.f;
-        for (int j = lane; j < lim; j += 32) {
-            const float e = __expf(r[j] * scale - mx);
-            r[j] = e;
-            se += e;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int j = sub + u * 8;
+            x[u] = (j < lim) ? r[j] * scale : -INFINITY;
+            mx = fmaxf(mx, x[u]);
         }
-        se = warp_sum(se);
-        const float inv = 1.f / se;
-        for (int j = lane; j < SP; j += 32) r[j] = j < lim ? r[j] * inv : 0.f;
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 4));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+        float se = 0.f;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            x[u] = (sub + u * 8 < lim) ? __expf(x[u] - mx) : 0.f;
+            se += x[u];
+        }
+        se += __shfl_xor_sync(0xffffffffu, se, 4);
+        se += __shfl_xor_sync(0xffffffffu, se, 2);
+        se += __shfl_xor_sync(0xffffffffu, se, 1);
+        const float inv = lim > 0 ? 1.f / se : 0.f;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int j = sub + u * 8;
+            if (j < SP) r[j] = x[u] * inv;
+        }
     }
 }
 
@@ -122,6 +173,7 @@ __device__ __forceinline__ void tc_emit_tile(const float* stage, __nv_bfloat16* 
 __global__ void __launch_bounds__(kTcThreads)
 attn_tc_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out, const AttnTc a) {
     pdl_launch_dependents();
+    attn_ts(0);
     extern __shared__ __align__(128) uint8_t smem[];
     const int S = a.S, SP = a.SP, D = a.D, dpad = D + 8, cpad = SP + 8;
     __nv_bfloat16* q = reinterpret_cast<__nv_bfloat16*>(smem);
@@ -133,17 +185,15 @@ attn_tc_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restr
     const int n = blockIdx.x / a.H, h = blockIdx.x % a.H;
     const long long ld = 3LL * a.E;
 
-    {
-        const __nv_bfloat16* base[3] = {qkv + h * D, qkv + a.E + h * D, qkv + 2 * a.E + h * D};
-        const long long lds[3] = {ld, ld, ld};
-        __nv_bfloat16* dst[3] = {q, k, v};
-        tc_gather(base, lds, dst, 3, a.NB, S, SP, D, n);
-    }
+    tc_gather(qkv + h * D, qkv + a.E + h * D, qkv + 2 * a.E + h * D, nullptr, ld, 0, q, k, v, nullptr, 3, a.NB, S, SP, D, n);
     __syncthreads();
+    attn_ts(1);
     tc_abt(q, k, sc, SP, D);
     __syncthreads();
+    attn_ts(2);
     tc_softmax(sc, S, SP, a.scale, a.causal);
     __syncthreads();
+    attn_ts(3);
     {
         const CounterRng rng(a.seed);
         const uint32_t thr = static_cast<uint32_t>(fminf(a.drop_p, 0.999999f) * 4294967296.0f);
@@ -156,25 +206,41 @@ attn_tc_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restr
         }
     }
     __syncthreads();
+    attn_ts(4);
 
-    // O = P V
-    const int warp = threadIdx.x >> 5, rt = SP / 16, ct = D / 16;
-    for (int t = warp; t < rt * ct; t += kTcWarps) {
-        const int ti = t / ct, tc = t % ct;
-        FragC acc;
-        wmma::fill_fragment(acc, 0.f);
+    // O = P V: each warp keeps up to four output tiles in flight (independent accumulators)
+    const int warp = threadIdx.x >> 5, rt = SP / 16, ct = D / 16, total = rt * ct;
+    for (int t0 = warp; t0 < total; t0 += kTcWarps * 4) {
+        FragC acc[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) wmma::fill_fragment(acc[u], 0.f);
         for (int kk = 0; kk < SP; kk += 16) {
-            FragA pa;
-            FragB vb;
-            wmma::load_matrix_sync(pa, pb + ti * 16 * cpad + kk, cpad);
-            wmma::load_matrix_sync(vb, v + kk * dpad + tc * 16, dpad);
-            wmma::mma_sync(acc, pa, vb, acc);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int t = t0 + u * kTcWarps;
+                if (t < total) {
+                    FragA pa;
+                    FragB vb;
+                    wmma::load_matrix_sync(pa, pb + (t / ct) * 16 * cpad + kk, cpad);
+                    wmma::load_matrix_sync(vb, v + kk * dpad + (t % ct) * 16, dpad);
+                    wmma::mma_sync(acc[u], pa, vb, acc[u]);
+                }
+            }
         }
-        wmma::store_matrix_sync(stage, acc, 24, wmma::mem_row_major);
-        __syncwarp();
-        tc_emit_tile(stage, out + (static_cast<size_t>(ti * 16) * a.NB + n) * a.E + h * D + tc * 16, a.E, a.NB, ti * 16, S);
-        __syncwarp();
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int t = t0 + u * kTcWarps;
+            if (t < total) {
+                const int ti = t / ct, tc = t % ct;
+                wmma::store_matrix_sync(stage, acc[u], 24, wmma::mem_row_major);
+                __syncwarp();
+                tc_emit_tile(stage, out + (static_cast<size_t>(ti * 16) * a.NB + n) * a.E + h * D + tc * 16, a.E, a.NB,
+                             ti * 16, S);
+                __syncwarp();
+            }
+        }
     }
+    attn_ts(5);
 }
 
 __global__ void __launch_bounds__(kTcThreads)
@@ -195,12 +261,8 @@ attn_tc_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* _
     const int n = blockIdx.x / a.H, h = blockIdx.x % a.H;
     const long long ld = 3LL * a.E;
 
-    {
-        const __nv_bfloat16* base[4] = {qkv + h * D, qkv + a.E + h * D, qkv + 2 * a.E + h * D, dout + h * D};
-        const long long lds[4] = {ld, ld, ld, a.E};
-        __nv_bfloat16* dst[4] = {q, k, v, dO};
-        tc_gather(base, lds, dst, 4, a.NB, S, SP, D, n);
-    }
+    tc_gather(qkv + h * D, qkv + a.E + h * D, qkv + 2 * a.E + h * D, dout + h * D, ld, a.E, q, k, v, dO, 4, a.NB, S, SP,
+              D, n);
     __syncthreads();
     tc_abt(q, k, P, SP, D);          // raw scores
     tc_abt(dO, v, dP, SP, D);        // gradient w.r.t. the dropped-out probabilities
@@ -208,56 +270,80 @@ attn_tc_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* _
     tc_softmax(P, S, SP, a.scale, a.causal);
     __syncthreads();
 
-    // per row: Pd = P * keep,  dPm = dP * keep,  delta = sum_j dPm * P,  dS = P * (dPm - delta) * scale
+    // per row (8 lanes each): Pd = P * keep,  dPm = dP * keep,  delta = sum_j dPm * P,  dS = P * (dPm - delta) * scale
     {
         const CounterRng rng(a.seed);
         const uint32_t thr = static_cast<uint32_t>(fminf(a.drop_p, 0.999999f) * 4294967296.0f);
         const float inv_keep = a.drop_p > 0.f ? 1.f / (1.f - a.drop_p) : 1.f;
-        const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-        for (int i = warp; i < SP; i += kTcWarps) {
+        const int sub = threadIdx.x & 7;
+        for (int i = threadIdx.x >> 3; i < SP; i += kTcThreads / 8) {
+            float p[8], dpm[8];
             float dlt = 0.f;
-            for (int j = lane; j < SP; j += 32) {
-                const float p = P[i * cpad + j];
-                float ks = 0.f;
-                if (i < S && j < S) ks = tc_keep(rng, a, thr, inv_keep, n, h, i, j);
-                const float dpm = dP[i * cpad + j] * ks;
-                Pd[i * cpad + j] = __float2bfloat16(p * ks);
-                dP[i * cpad + j] = dpm;
-                dlt += dpm * p;
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const int j = sub + u * 8;
+                p[u] = 0.f;
+                dpm[u] = 0.f;
+                if (j < SP) {
+                    p[u] = P[i * cpad + j];
+                    float ks = 0.f;
+                    if (i < S && j < S) ks = tc_keep(rng, a, thr, inv_keep, n, h, i, j);
+                    dpm[u] = dP[i * cpad + j] * ks;
+                    Pd[i * cpad + j] = __float2bfloat16(p[u] * ks);
+                    dlt += dpm[u] * p[u];
+                }
             }
-            dlt = warp_sum(dlt);
-            for (int j = lane; j < SP; j += 32)
-                dS[i * cpad + j] = __float2bfloat16(P[i * cpad + j] * (dP[i * cpad + j] - dlt) * a.scale);
+            dlt += __shfl_xor_sync(0xffffffffu, dlt, 4);
+            dlt += __shfl_xor_sync(0xffffffffu, dlt, 2);
+            dlt += __shfl_xor_sync(0xffffffffu, dlt, 1);
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const int j = sub + u * 8;
+                if (j < SP) dS[i * cpad + j] = __float2bfloat16(p[u] * (dpm[u] - dlt) * a.scale);
+            }
         }
     }
     __syncthreads();
 
-    // dV = Pd^T dO,  dQ = dS K,  dK = dS^T Q   — 3 x (SP/16) x (D/16) output tiles
-    const int warp = threadIdx.x >> 5, rt = SP / 16, ct = D / 16, per = rt * ct;
-    for (int t = warp; t < 3 * per; t += kTcWarps) {
-        const int which = t / per, r = t % per, ti = r / ct, tc = r % ct;
-        FragC acc;
-        wmma::fill_fragment(acc, 0.f);
+    // dV = Pd^T dO,  dQ = dS K,  dK = dS^T Q  — 3 x (SP/16) x (D/16) output tiles, four in flight per warp
+    const int warp = threadIdx.x >> 5, rt = SP / 16, ct = D / 16, per = rt * ct, total = 3 * per;
+    for (int t0 = warp; t0 < total; t0 += kTcWarps * 4) {
+        FragC acc[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) wmma::fill_fragment(acc[u], 0.f);
         for (int kk = 0; kk < SP; kk += 16) {
-            FragB b;
-            if (which == 1) {            // dQ: A = dS (row-major), B = K
-                FragA am;
-                wmma::load_matrix_sync(am, dS + ti * 16 * cpad + kk, cpad);
-                wmma::load_matrix_sync(b, k + kk * dpad + tc * 16, dpad);
-                wmma::mma_sync(acc, am, b, acc);
-            } else {                     // dV: A = Pd^T, B = dO;  dK: A = dS^T, B = Q
-                FragAT at;
-                const __nv_bfloat16* src = which == 0 ? Pd : dS;
-                wmma::load_matrix_sync(at, src + kk * cpad + ti * 16, cpad);
-                wmma::load_matrix_sync(b, (which == 0 ? dO : q) + kk * dpad + tc * 16, dpad);
-                wmma::mma_sync(acc, at, b, acc);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int t = t0 + u * kTcWarps;
+                if (t < total) {
+                    const int which = t / per, r = t % per, ti = r / ct, tc = r % ct;
+                    FragB bm;
+                    if (which == 1) {            // dQ: A = dS (row-major), B = K
+                        FragA am;
+                        wmma::load_matrix_sync(am, dS + ti * 16 * cpad + kk, cpad);
+                        wmma::load_matrix_sync(bm, k + kk * dpad + tc * 16, dpad);
+                        wmma::mma_sync(acc[u], am, bm, acc[u]);
+                    } else {                     // dV: A = Pd^T, B = dO;  dK: A = dS^T, B = Q
+                        FragAT at;
+                        wmma::load_matrix_sync(at, (which == 0 ? Pd : dS) + kk * cpad + ti * 16, cpad);
+                        wmma::load_matrix_sync(bm, (which == 0 ? dO : q) + kk * dpad + tc * 16, dpad);
+                        wmma::mma_sync(acc[u], at, bm, acc[u]);
+                    }
+                }
             }
         }
-        wmma::store_matrix_sync(stage, acc, 24, wmma::mem_row_major);
-        __syncwarp();
-        const int col0 = (which == 0 ? 2 * a.E : which == 1 ? 0 : a.E) + h * D + tc * 16;
-        tc_emit_tile(stage, dqkv + (static_cast<size_t>(ti * 16) * a.NB + n) * ld + col0, ld, a.NB, ti * 16, S);
-        __syncwarp();
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int t = t0 + u * kTcWarps;
+            if (t < total) {
+                const int which = t / per, r = t % per, ti = r / ct, tc = r % ct;
+                wmma::store_matrix_sync(stage, acc[u], 24, wmma::mem_row_major);
+                __syncwarp();
+                const int col0 = (which == 0 ? 2 * a.E : which == 1 ? 0 : a.E) + h * D + tc * 16;
+                tc_emit_tile(stage, dqkv + (static_cast<size_t>(ti * 16) * a.NB + n) * ld + col0, ld, a.NB, ti * 16, S);
+                __syncwarp();
+            }
+        }
     }
 }
 
@@ -298,3 +384,7 @@ int attn_tc_bwd(const void* qkv, const void* dout, void* dqkv, int NB, int S, in
 }
 
 }  // namespace pb2
+
+extern "C" int pb2_debug_attn_timestamps(unsigned long long* out16) {
+    return cudaMemcpyFromSymbol(out16, pb2::g_attn_ts, sizeof(unsigned long long) * 16) == cudaSuccess ? 0 : -1;
+}
