@@ -31,6 +31,7 @@
 // No counterpart in the reference: its GEMMs are cuBLAS calls behind nn.Linear /
 // nn.MultiheadAttention (main.py:45,148); SURVEY.md K2/K4/K6/K7, W5.
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -598,10 +599,18 @@ static int gemm_launch(const pb2_gemm_desc* d, float* partials, unsigned int* co
 
     const int stage_bytes = (kBlockM + bn) * kBlockK * 2;
     int stages = (200 * 1024) / stage_bytes;
-    if (tiles * splits > 148) {
-        // more CTAs than SMs: size the ring so two CTAs fit per SM and both waves stream at once
-        const int two = (110 * 1024) / stage_bytes;
-        if (two >= 2) stages = two;
+    {
+        // With more CTAs than SMs the ring is sized so that two CTAs fit on an SM and both waves
+        // stream at once.  (Capping single-wave launches too, so that the next GEMM could co-reside
+        // during this one's epilogue, measured slightly slower: PB2_GEMM_RING_KB=108 -> +4 % step time.)
+        static int cap_kb = -1;
+        if (cap_kb < 0) {
+            const char* e = getenv("PB2_GEMM_RING_KB");
+            cap_kb = e ? atoi(e) : 200;
+        }
+        const int kb = (tiles * splits > 148 && cap_kb > 110) ? 110 : cap_kb;   // > 1 wave: always two per SM
+        const int two = (kb * 1024) / stage_bytes;
+        if (two >= 2 && two < stages) stages = two;
     }
     if (stages > kMaxStages) stages = kMaxStages;
     if (d->stages > 0 && d->stages < stages) stages = d->stages;
