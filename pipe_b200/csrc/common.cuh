@@ -276,6 +276,11 @@ __device__ __forceinline__ bool dropout_keep(const CounterRng& ph, uint64_t stre
     return v >= threshold;
 }
 
+// 16-byte vector reduction to global memory (one L2 atomic operation for four floats).
+__device__ __forceinline__ void red_add_f32x4(float* addr, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

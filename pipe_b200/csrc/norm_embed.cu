@@ -166,15 +166,20 @@ add_ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __r
             load8(dy + row * E + c, d);
             const float4 g0 = *reinterpret_cast<const float4*>(gamma + c), g1 = *reinterpret_cast<const float4*>(gamma + c + 4);
             const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+            float dgv[8];
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
                 xh[i][j] = (a[j] - mean) * rstd;
                 g[i][j] = d[j] * gg[j];
                 s1 += g[i][j];
                 s2 += g[i][j] * xh[i][j];
-                atomicAdd(dgamma + c + j, d[j] * xh[i][j]);
-                atomicAdd(dbeta + c + j, d[j]);
+                dgv[j] = d[j] * xh[i][j];
             }
+            // 16-byte vector reductions (red.global.add.v4.f32): a quarter of the atomic operations
+            red_add_f32x4(dgamma + c, dgv[0], dgv[1], dgv[2], dgv[3]);
+            red_add_f32x4(dgamma + c + 4, dgv[4], dgv[5], dgv[6], dgv[7]);
+            red_add_f32x4(dbeta + c, d[0], d[1], d[2], d[3]);
+            red_add_f32x4(dbeta + c + 4, d[4], d[5], d[6], d[7]);
         }
     }
     const float m1 = block_sum(s1, red) / E;

@@ -27,6 +27,7 @@ Parity: reference ``pipeline.py:43-60`` (helpers), ``82-117`` (``run``),
 """
 from __future__ import annotations
 
+import sys
 from contextlib import nullcontext
 from queue import Queue
 from typing import TYPE_CHECKING, Callable, List, Optional, Sequence, Tuple
@@ -92,6 +93,8 @@ class Pipeline:
         #: called as ``hook(i, j, batch)`` right after cell (i, j)'s forward was
         #: collected on the main thread (the DDP hybrid hangs its reducers here)
         self.cell_hooks: List[Callable[[int, int, Batch], None]] = []
+        #: run the last cell of every tick on the calling thread instead of its worker
+        self.inline_last_cell = True
 
     def close(self) -> None:
         self.pool.close()
@@ -132,6 +135,7 @@ class Pipeline:
         first_exc: Optional[ExcInfo] = None
 
         # -- dispatch ------------------------------------------------------
+        inline = None
         for i, j in tick:
             batch = batches[i]
             if j != 0:
@@ -139,11 +143,29 @@ class Pipeline:
 
             task = self._make_task(i, j, batch, partitions[j], trackers[i],
                                    compute_streams[j], checkpointed=i < checkpoint_stop)
-            self.in_queues[j].put(task)
+            if self.inline_last_cell and (i, j) == tick[-1]:
+                inline = (j, task)          # run below, on this thread, while the workers run the rest
+            else:
+                self.in_queues[j].put(task)
+
+        # The last cell of the tick runs on the calling thread: one queue hop and one thread wake-up
+        # less on the critical path (for a single-stage pipe that is every cell).  Workers still run
+        # the other cells of the tick concurrently, so cross-device overlap is unchanged.
+        inline_result = None
+        if inline is not None:
+            j_in, task_in = inline
+            try:
+                with use_device(devices[j_in]):
+                    inline_result = (True, (task_in, task_in.compute()))
+            except Exception:
+                inline_result = (False, sys.exc_info())
 
         # -- collect -------------------------------------------------------
         for i, j in tick:
-            ok, payload = self.out_queues[j].get()
+            if inline is not None and (i, j) == tick[-1]:
+                ok, payload = inline_result
+            else:
+                ok, payload = self.out_queues[j].get()
 
             if first_exc is not None:
                 continue  # keep draining so the queues stay in lock-step
