@@ -153,7 +153,11 @@ class Checkpoint(torch.autograd.Function):
         pairs = [(y, g) for y, g in zip(outputs, grad_output)
                  if torch.is_tensor(y) and y.requires_grad]
         if pairs:
-            torch.autograd.backward([y for y, _ in pairs], [g for _, g in pairs])
+            # The nested pass must not end the mini-batch-wide deferral of weight gradients
+            # (pipe_b200.ops.wgrad): queue its flush on the outer pass instead.
+            from ..ops import wgrad
+            with wgrad.outer_backward():
+                torch.autograd.backward([y for y, _ in pairs], [g for _, g in pairs])
 
         grads: List[Optional[Tensor]] = [None] * 5
         grads.extend(x.grad if torch.is_tensor(x) else None for x in leaves)

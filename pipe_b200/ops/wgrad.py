@@ -29,11 +29,12 @@ from torch import Tensor, nn
 from . import _lib
 from .gemm import gemm_nt
 
-__all__ = ["LinearGrad", "deferred", "flush_pending", "ensure_grad"]
+__all__ = ["LinearGrad", "deferred", "outer_backward", "flush_pending", "ensure_grad"]
 
 _lock = threading.RLock()
 _pending: "Dict[int, LinearGrad]" = {}
 _defer_depth = 0
+_nested_depth = 0
 _callback_queued = False
 
 
@@ -119,7 +120,7 @@ def _arm() -> None:
     """Make sure something will flush: queue an engine callback unless an outer
     ``deferred()`` block owns the flush."""
     global _callback_queued
-    if _defer_depth > 0 or _callback_queued:
+    if _defer_depth > 0 or _nested_depth > 0 or _callback_queued:
         return
     try:
         torch.autograd.Variable._execution_engine.queue_callback(_engine_done)
@@ -143,6 +144,25 @@ def flush_pending() -> None:
         _pending.clear()
     for lg in todo:
         lg.flush()
+
+
+@contextmanager
+def outer_backward() -> Iterator[None]:
+    """Wrap a *re-entrant* ``torch.autograd.backward`` call (checkpoint recompute).
+
+    An engine callback queued from inside the nested pass would fire when the nested pass ends,
+    i.e. once per checkpointed cell, and the "one wgrad GEMM per mini-batch" deferral would
+    degenerate into one per micro-batch.  So the callback is queued here, in the context of the
+    *outer* pass, and arming is suppressed while the nested pass runs."""
+    global _nested_depth
+    with _lock:
+        _arm()
+        _nested_depth += 1
+    try:
+        yield
+    finally:
+        with _lock:
+            _nested_depth -= 1
 
 
 @contextmanager
