@@ -31,19 +31,31 @@ lines = []
 
 
 def time_ms(fn, n_iter=12, n_warm=3):
-    """Median kernel duration from CUPTI (torch.profiler): host launch gaps do not count."""
-    from torch.profiler import ProfilerActivity, profile
+    """Per-call device time with no host in the loop: the calls are captured once into a CUDA
+    graph (on a side stream) and the graph is replayed between two events."""
     for i in range(n_warm):
         fn(i)
     torch.cuda.synchronize()
-    with profile(activities=[ProfilerActivity.CUDA]) as prof:
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        for i in range(n_warm):
+            fn(i)                      # per-stream workspaces get allocated outside capture
+    torch.cuda.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph, stream=side):
         for i in range(n_iter):
             fn(i)
+    torch.cuda.synchronize()
+    best = float("inf")
+    for _ in range(4):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        graph.replay()
+        e1.record()
         torch.cuda.synchronize()
-    per_call = {}
-    ev = [e for e in prof.events() if e.device_time > 0]
-    total = sum(e.device_time for e in ev)
-    return total / n_iter / 1e3
+        best = min(best, e0.elapsed_time(e1) / n_iter)
+    return best
 
 
 def case(name, M, N, K, out_f32=False, transpose=True, **kw):
@@ -65,7 +77,11 @@ def case(name, M, N, K, out_f32=False, transpose=True, **kw):
 
 
 T, E, V = 75, 4096, 28782
-if args.sweep:
+if args.sweep and os.environ.get("SWEEP") == "wgrad":
+    for bn in (256, 128, 64):
+        for stages in (0, 2, 4):
+            case("sweep wgrad ExE", E, E, 512, out_f32=True, transpose=False, block_n=bn, stages=stages)
+elif args.sweep:
     for splits in (1, 2, 4, 8, 16):
         for stages in (0, 3):
             case("sweep out-proj fwd", E, T, E, splits=splits, stages=stages)
