@@ -144,3 +144,38 @@ def test_state_dict_moves_between_eager_and_fused():
     assert list(eager.state_dict().keys()) == list(fused.state_dict().keys())
     fused.load_state_dict(eager.state_dict())
     eager.load_state_dict(fused.state_dict())
+
+
+def test_skip_connection_across_fused_stages_and_inline_toggle():
+    """@skippable stash/pop around fused layers in a 2-stage-on-one-GPU pipe, both dispatch modes."""
+    from pipe_b200 import Pipe
+    from pipe_b200.models import build_layer
+    from pipe_b200.skip import pop, skippable, stash
+
+    @skippable(stash=["emb"])
+    class StashEmb(nn.Module):
+        def forward(self, x):
+            yield stash("emb", x)
+            return x
+
+    @skippable(pop=["emb"])
+    class PopAdd(nn.Module):
+        def forward(self, x):
+            emb = yield pop("emb")
+            return x + emb
+
+    cfg = _tiny_cfg(0.0)
+    outs = []
+    for inline in (True, False):
+        layers = [build_layer(cfg, k, "fused", 0, seed=5) for k in range(cfg.nlayers + 2)]
+        seq = nn.Sequential(layers[0], StashEmb().cuda(), layers[1], layers[2], PopAdd().cuda(), layers[3])
+        pipe = Pipe(seq, chunks=4, checkpoint="always", balance=[3, 3], devices=["cuda:0", "cuda:0"])
+        assert len(pipe.partitions) == 2 and pipe._skip_layout.requires_copy(None, "emb")
+        pipe.pipeline.inline_last_cell = inline
+        tokens = torch.randint(0, cfg.ntokens, (cfg.batch, cfg.bptt), device=dev, generator=torch.Generator(dev).manual_seed(1))
+        out = pipe(tokens).local_value()
+        out.float().sum().backward()
+        outs.append((out.detach().clone(), pipe[0].encoder.weight.grad.clone()))
+        pipe.close()
+    assert rel(outs[0][0], outs[1][0]) < 1e-3
+    assert rel(outs[0][1], outs[1][1]) < 1e-2
