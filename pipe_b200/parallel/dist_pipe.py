@@ -135,6 +135,8 @@ class DistPipe(nn.Module):
         self._cells: List[_Cell] = []
         self._out_leaves: List[Tuple[Any, ...]] = []
         self._sends: List[Any] = []
+        self._early: Dict[int, Any] = {}                  # receives posted ahead of their micro-batch
+        self._early_grads: Dict[int, Any] = {}
         self.last_bubble = 0.0
 
     # -- topology --------------------------------------------------------------
@@ -195,16 +197,32 @@ class DistPipe(nn.Module):
         for t in tensors:
             self._sends.append(dist.isend(t.detach().contiguous(), self._next(), group=group))
 
+    def _post_recv_forward(self, i: int) -> None:
+        """Queue the receives of micro-batch ``i`` now (its shapes must be known), so the transfer
+        is already in flight — or done — when the stage gets to it."""
+        if i in self._early or i not in self._recv_specs:
+            return
+        group = self._fwd_groups[self.index - 1]
+        out, works = [], []
+        for s in self._recv_specs[i]:
+            t = torch.empty(s.shape, dtype=s.dtype, device=self.device)
+            works.append(dist.irecv(t, self._prev(), group=group))
+            out.append(t)
+        self._early[i] = (out, works)
+
     def _recv_forward(self, i: int) -> Tuple[Tensor, ...]:
         group = self._fwd_groups[self.index - 1]
         specs = self._recv_specs.get(i)
         if specs is None:
             specs = self._recv_specs[i] = self._recv_meta(self._prev(), group)
-        out, works = [], []
-        for s in specs:
-            t = torch.empty(s.shape, dtype=s.dtype, device=self.device)
-            works.append(dist.irecv(t, self._prev(), group=group))
-            out.append(t)
+        if i in self._early:
+            out, works = self._early.pop(i)
+        else:
+            out, works = [], []
+            for s in specs:
+                t = torch.empty(s.shape, dtype=s.dtype, device=self.device)
+                works.append(dist.irecv(t, self._prev(), group=group))
+                out.append(t)
         for w in works:
             w.wait()
         return tuple(t.requires_grad_(s.requires_grad) for t, s in zip(out, specs))
@@ -271,6 +289,8 @@ class DistPipe(nn.Module):
                 values = (b.tensor,) if b.atomic else tuple(b.values)
             else:
                 values = self._recv_forward(i)
+                if i + 1 < m:
+                    self._post_recv_forward(i + 1)      # next micro-batch's transfer overlaps this cell
             cell.inputs = values
 
             if i < stop:
@@ -339,7 +359,9 @@ class DistPipe(nn.Module):
                 grads = [l.grad if torch.is_tensor(l) else None for l in cell.leaves]
                 works = []
             else:
-                grads, works = self._post_recv_grads(i)
+                grads, works = self._early_grads.pop(i, None) or self._post_recv_grads(i)
+                if i > 0:
+                    self._early_grads[i - 1] = self._post_recv_grads(i - 1)   # overlaps this cell's backward
 
             if cell.checkpointed:
                 outs = self._recompute(cell)        # overlaps the gradient transfer
