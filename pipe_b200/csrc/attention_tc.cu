@@ -1,11 +1,12 @@
-// Tensor-core attention core for short sequences (S <= 64): the five small matrix products of
+// Tensor-core attention core for short sequences (S <= 128 while the tiles fit shared memory): the five small matrix products of
 // attention forward + backward on warp-level MMA (bf16 in, fp32 accumulate), everything else —
 // softmax, dropout mask, the dS recurrence — on the scores held in shared memory.
 //
 // One CTA owns one (sequence, head) pair for the whole pass; Q, K, V (and dO) are gathered from the
 // packed [T, 3E] projection output into zero-padded shared tiles, the S x S score matrix never
 // leaves the SM, and results are scattered straight back into the packed layouts the neighbouring
-// GEMMs read.  The SIMT kernels in attention.cu remain the path for 64 < S <= 128.
+// GEMMs read.  The SIMT kernels in attention.cu remain the fallback when the tiles do not fit
+// (S = 128 with head_dim > 64).
 //
 // Why warp-level MMA and not tcgen05 here: at S = 25 the whole problem is a 32 x 32 x 256 product
 // per head; a UMMA tile is 128 rows and needs TMA-swizzled operands, TMEM allocation and an mbarrier
@@ -112,16 +113,16 @@ __device__ __forceinline__ void tc_abt(const __nv_bfloat16* A, const __nv_bfloat
 
 // Softmax over the first S columns of the first S rows of `sc` (scaled by `scale`), in place.
 // Eight lanes share a row, so 32 rows are in flight at once (a warp-per-row loop would walk the rows
-// one latency chain after another).  SP <= 64: at most 8 columns per lane.
+// one latency chain after another).  SP <= 128: at most 16 columns per lane.
 __device__ __forceinline__ void tc_softmax(float* sc, int S, int SP, float scale, int causal) {
     const int sub = threadIdx.x & 7, cpad = SP + 8;
     for (int i = threadIdx.x >> 3; i < SP; i += kTcThreads / 8) {
         float* r = sc + i * cpad;
         const int lim = i < S ? (causal ? i + 1 : S) : 0;
-        float x[8];
+        float x[16];
         float mx = -INFINITY;
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
+        for (int u = 0; u < 16; ++u) {
             const int j = sub + u * 8;
             x[u] = (j < lim) ? r[j] * scale : -INFINITY;
             mx = fmaxf(mx, x[u]);
@@ -131,7 +132,7 @@ __device__ __forceinline__ void tc_softmax(float* sc, int S, int SP, float scale
         mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
         float se = 0.f;
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
+        for (int u = 0; u < 16; ++u) {
             x[u] = (sub + u * 8 < lim) ? __expf(x[u] - mx) : 0.f;
             se += x[u];
         }
@@ -140,7 +141,7 @@ __device__ __forceinline__ void tc_softmax(float* sc, int S, int SP, float scale
         se += __shfl_xor_sync(0xffffffffu, se, 1);
         const float inv = lim > 0 ? 1.f / se : 0.f;
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
+        for (int u = 0; u < 16; ++u) {
             const int j = sub + u * 8;
             if (j < SP) r[j] = x[u] * inv;
         }
@@ -255,9 +256,13 @@ attn_tc_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* _
     __nv_bfloat16* dO = v + SP * dpad;
     float* P = reinterpret_cast<float*>(dO + SP * dpad);
     float* dP = P + SP * cpad;
-    __nv_bfloat16* Pd = reinterpret_cast<__nv_bfloat16*>(dP + SP * cpad);     // dropped-out probabilities (bf16)
-    __nv_bfloat16* dS = Pd + SP * cpad;                                       // score gradients (bf16)
-    float* stage = reinterpret_cast<float*>(dS + SP * cpad) + (threadIdx.x >> 5) * (16 * 24);
+    // The bf16 matrices the last three products read are written over the fp32 rows they are derived
+    // from (same row pitch in bytes, so bpad = 2 * cpad bf16 elements): S = 128 with D = 64 then
+    // fits the 227 KB of shared memory.
+    __nv_bfloat16* Pd = reinterpret_cast<__nv_bfloat16*>(P);                  // dropped-out probabilities
+    __nv_bfloat16* dS = reinterpret_cast<__nv_bfloat16*>(dP);                 // score gradients
+    const int bpad = 2 * cpad;
+    float* stage = dP + SP * cpad + (threadIdx.x >> 5) * (16 * 24);
     const int n = blockIdx.x / a.H, h = blockIdx.x % a.H;
     const long long ld = 3LL * a.E;
 
@@ -277,29 +282,34 @@ attn_tc_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* _
         const float inv_keep = a.drop_p > 0.f ? 1.f / (1.f - a.drop_p) : 1.f;
         const int sub = threadIdx.x & 7;
         for (int i = threadIdx.x >> 3; i < SP; i += kTcThreads / 8) {
-            float p[8], dpm[8];
+            float p[16], dpm[16], keepv[16];
             float dlt = 0.f;
 #pragma unroll
-            for (int u = 0; u < 8; ++u) {
+            for (int u = 0; u < 16; ++u) {
                 const int j = sub + u * 8;
                 p[u] = 0.f;
                 dpm[u] = 0.f;
+                keepv[u] = 0.f;
                 if (j < SP) {
                     p[u] = P[i * cpad + j];
                     float ks = 0.f;
                     if (i < S && j < S) ks = tc_keep(rng, a, thr, inv_keep, n, h, i, j);
                     dpm[u] = dP[i * cpad + j] * ks;
-                    Pd[i * cpad + j] = __float2bfloat16(p[u] * ks);
                     dlt += dpm[u] * p[u];
+                    keepv[u] = ks;
                 }
             }
             dlt += __shfl_xor_sync(0xffffffffu, dlt, 4);
             dlt += __shfl_xor_sync(0xffffffffu, dlt, 2);
             dlt += __shfl_xor_sync(0xffffffffu, dlt, 1);
+            __syncwarp();          // every lane of the row has read its fp32 values: rows may now be overwritten
 #pragma unroll
-            for (int u = 0; u < 8; ++u) {
+            for (int u = 0; u < 16; ++u) {
                 const int j = sub + u * 8;
-                if (j < SP) dS[i * cpad + j] = __float2bfloat16(p[u] * (dpm[u] - dlt) * a.scale);
+                if (j < SP) {
+                    Pd[i * bpad + j] = __float2bfloat16(p[u] * keepv[u]);
+                    dS[i * bpad + j] = __float2bfloat16(p[u] * (dpm[u] - dlt) * a.scale);
+                }
             }
         }
     }
@@ -320,12 +330,12 @@ attn_tc_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* _
                     FragB bm;
                     if (which == 1) {            // dQ: A = dS (row-major), B = K
                         FragA am;
-                        wmma::load_matrix_sync(am, dS + ti * 16 * cpad + kk, cpad);
+                        wmma::load_matrix_sync(am, dS + ti * 16 * bpad + kk, bpad);
                         wmma::load_matrix_sync(bm, k + kk * dpad + tc * 16, dpad);
                         wmma::mma_sync(acc[u], am, bm, acc[u]);
                     } else {                     // dV: A = Pd^T, B = dO;  dK: A = dS^T, B = Q
                         FragAT at;
-                        wmma::load_matrix_sync(at, (which == 0 ? Pd : dS) + kk * cpad + ti * 16, cpad);
+                        wmma::load_matrix_sync(at, (which == 0 ? Pd : dS) + kk * bpad + ti * 16, bpad);
                         wmma::load_matrix_sync(bm, (which == 0 ? dO : q) + kk * dpad + tc * 16, dpad);
                         wmma::mma_sync(acc[u], at, bm, acc[u]);
                     }
@@ -350,13 +360,17 @@ attn_tc_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* _
 size_t attn_tc_smem(int SP, int D, bool bwd) {
     const size_t dpad = D + 8, cpad = SP + 8;
     size_t b = (bwd ? 4 : 3) * SP * dpad * 2;             // Q K V (dO)
-    b += (bwd ? 2 : 1) * SP * cpad * 4;                    // fp32 score matrices
-    b += (bwd ? 2 : 1) * SP * cpad * 2;                    // bf16 probability / gradient matrices
+    b += (bwd ? 2 : 1) * SP * cpad * 4;                    // fp32 score matrices (backward: bf16 copies alias them)
+    if (!bwd) b += SP * cpad * 2;                          // forward: bf16 probabilities
     b += kTcWarps * 16 * 24 * 4;                           // per-warp output staging
     return b + 128;
 }
 
-bool attn_tc_supported(int S, int D) { return S <= 64 && D % 16 == 0 && D <= 256; }
+bool attn_tc_supported(int S, int D) {
+    if (S > 128 || D % 16 != 0 || D > 256) return false;
+    const int SP = (S + 15) / 16 * 16;
+    return attn_tc_smem(SP, D, true) <= 227 * 1024;        // e.g. S = 128 needs D <= 64; S <= 64 any D <= 256
+}
 
 int attn_tc_fwd(const void* qkv, void* out, int NB, int S, int H, int D, int causal, float drop_p,
                 unsigned long long seed, unsigned long long rng_stream, cudaStream_t stream) {
