@@ -139,6 +139,11 @@ typedef struct pb2_transpose_jobs {
 } pb2_transpose_jobs;
 int pb2_transpose_multi(const pb2_transpose_jobs* jobs, cudaStream_t stream);
 
+/* ---- asynchronous L2 prefetch of [ptr, ptr + bytes) (16-byte aligned) -----------------------
+ * Returns at once; the lines arrive in L2 in the background.  Used to pull the next GEMM's weights
+ * while kernels that do not touch HBM are running. */
+int pb2_l2_prefetch(const void* ptr, size_t bytes, cudaStream_t stream);
+
 /* ---- *out += sum(x^2)  (gradient-norm partial; x fp32, 16-byte aligned) ---------------------- */
 int pb2_sumsq(const float* x, size_t n, float* out, cudaStream_t stream);
 
@@ -230,6 +235,11 @@ typedef struct pb2_encoder_layer {
     /* split-K workspace of pb2_gemm_workspace_bytes() bytes (see pb2_gemm_bf16) */
     void* workspace;
     size_t workspace_bytes;
+    /* optional: the first weight the NEXT layer call on this stream will stream (forward: the next
+     * layer's w_qkv, backward: the previous layer's wt_2); prefetched into L2 during this call's tail */
+    const void* next_weight;
+    size_t next_weight_bytes;
+    int prefetch;                    /* 1: prefetch each GEMM's weights one GEMM ahead */
 } pb2_encoder_layer;
 
 int pb2_encoder_layer_fwd(const pb2_encoder_layer* L, cudaStream_t stream);

@@ -43,11 +43,20 @@ extern "C" int pb2_encoder_layer_fwd(const pb2_encoder_layer* L, cudaStream_t st
     const float p = L->drop_p;
     if (T != L->S * L->NB || E % L->heads) { pb2::set_error("pb2_encoder_layer_fwd: inconsistent shape"); return -1; }
 
+    // Weight prefetch runs one GEMM ahead: while a GEMM (or the attention / LayerNorm kernel after it)
+    // executes, the next GEMM's weights are already on their way into L2, so DRAM does not idle during
+    // prologues, epilogues and the kernels that never touch HBM.
+    const bool pf = L->prefetch != 0;
+    const size_t w_ee = static_cast<size_t>(E) * E * 2, w_ef = static_cast<size_t>(E) * FF * 2;
+    if (pf && pb2_l2_prefetch(L->w_o, w_ee, stream)) return -1;
     if (linear(L, Lin{L->w_qkv, E, 3 * E, E}, L->x, T, L->qkv, L->b_qkv, 0, 0.f, 0, nullptr, 0.f, nullptr, stream)) return -1;
+    if (pf && pb2_l2_prefetch(L->w_1, w_ef, stream)) return -1;
     if (pb2_attention_fwd(L->qkv, L->a, L->NB, L->S, L->heads, E / L->heads, L->causal, p, L->seed, 0, stream)) return -1;
     if (linear(L, Lin{L->w_o, E, E, E}, L->a, T, L->o, L->b_o, 0, p, 1, nullptr, 0.f, nullptr, stream)) return -1;
     if (pb2_add_layernorm_fwd(L->x, L->o, L->g1, L->be1, L->x1, L->mean1, L->rstd1, T, E, L->eps, stream)) return -1;
+    if (pf && pb2_l2_prefetch(L->w_2, w_ef, stream)) return -1;
     if (linear(L, Lin{L->w_1, E, FF, E}, L->x1, T, L->hmid, L->b_1, 1, p, 2, nullptr, 0.f, nullptr, stream)) return -1;
+    if (pf && L->next_weight && pb2_l2_prefetch(L->next_weight, L->next_weight_bytes, stream)) return -1;
     if (linear(L, Lin{L->w_2, FF, E, FF}, L->hmid, T, L->f, L->b_2, 0, p, 3, nullptr, 0.f, nullptr, stream)) return -1;
     if (pb2_add_layernorm_fwd(L->x1, L->f, L->g2, L->be2, L->y, L->mean2, L->rstd2, T, E, L->eps, stream)) return -1;
     return 0;
@@ -59,18 +68,25 @@ extern "C" int pb2_encoder_layer_bwd(const pb2_encoder_layer* L, cudaStream_t st
     const float p = L->drop_p;
     const float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
 
+    const bool pf = L->prefetch != 0;
+    const size_t w_ee = static_cast<size_t>(E) * L->ldt_o * 2, w_1t = static_cast<size_t>(E) * L->ldt_1 * 2,
+                 w_qt = static_cast<size_t>(E) * L->ldt_qkv * 2;
+    if (pf && pb2_l2_prefetch(L->wt_1, w_1t, stream)) return -1;
     // y = LN2(x1 + drop(f))
     if (pb2_add_layernorm_bwd(L->dy, L->x1, L->f, L->g2, L->mean2, L->rstd2, L->dr2, L->df, L->dg2, L->dbe2, T, E, p,
                               L->seed, 3, stream)) return -1;
     // through linear2, then ReLU + dropout (mask recovered from the saved activation)
     if (linear(L, Lin{L->wt_2, L->ldt_2, FF, E}, L->df, T, L->dz1, nullptr, 0, 0.f, 0, L->hmid, inv_keep, nullptr, stream)) return -1;
+    if (pf && pb2_l2_prefetch(L->wt_o, w_ee, stream)) return -1;
     // through linear1, plus the residual branch
     if (linear(L, Lin{L->wt_1, L->ldt_1, E, FF}, L->dz1, T, L->dx1, nullptr, 0, 0.f, 0, nullptr, 0.f, L->dr2, stream)) return -1;
     // x1 = LN1(x + drop(o))
     if (pb2_add_layernorm_bwd(L->dx1, L->x, L->o, L->g1, L->mean1, L->rstd1, L->dr1, L->do_, L->dg1, L->dbe1, T, E, p,
                               L->seed, 1, stream)) return -1;
+    if (pf && pb2_l2_prefetch(L->wt_qkv, w_qt, stream)) return -1;
     if (linear(L, Lin{L->wt_o, L->ldt_o, E, E}, L->do_, T, L->da, nullptr, 0, 0.f, 0, nullptr, 0.f, nullptr, stream)) return -1;
     if (pb2_attention_bwd(L->qkv, L->da, L->dqkv, L->NB, L->S, L->heads, E / L->heads, L->causal, p, L->seed, 0, stream)) return -1;
+    if (pf && L->next_weight && pb2_l2_prefetch(L->next_weight, L->next_weight_bytes, stream)) return -1;
     if (linear(L, Lin{L->wt_qkv, L->ldt_qkv, E, 3 * E}, L->dqkv, T, L->dx, nullptr, 0, 0.f, 0, nullptr, 0.f, L->dr1, stream)) return -1;
 
     // stack every wgrad operand (and column-sum the bias gradients) in one launch

@@ -26,6 +26,8 @@ Parity: reference ``main.py:24-73,115-120,139-157``; SURVEY.md K1-K9.
 from __future__ import annotations
 
 import math
+import os
+import threading
 from typing import Any, Dict, List, Optional, Tuple
 
 import torch
@@ -142,6 +144,21 @@ class _FusedBase(nn.Module):
 # ======================================================================================
 # encoder layer
 # ======================================================================================
+class _Chain(threading.local):
+    """Which fused layer ran forward last on this thread: lets every layer learn its successor and
+    predecessor at run time, so its executor can prefetch the neighbour's first weight into L2."""
+
+    def __init__(self) -> None:
+        self.last: Optional["FusedEncoderLayer"] = None
+
+
+_chain = _Chain()
+# Measured on B200 (config 3, 1 GPU): prefetching one GEMM ahead made the step 25 % SLOWER (40.0 -> 49.8 ms):
+# the extra launches serialise the PDL chain and the prefetched lines compete with the streaming GEMM for
+# HBM and L2.  Kept as an opt-in experiment (PB2_PREFETCH=1), off by default.
+_PREFETCH = os.environ.get("PB2_PREFETCH", "0") == "1"
+
+
 class _EncoderLayerFn(torch.autograd.Function):
     """Forward and backward of the whole layer, each one call into the C++ layer executor
     (``csrc/layer.cu``): 7 and 8 kernel launches respectively, no Python between them."""
@@ -168,6 +185,19 @@ class _EncoderLayerFn(torch.autograd.Function):
         d.T, d.NB, d.S = T, NB, S
         d.drop_p, d.seed = p, seed
         d.x, d.y = x2.data_ptr(), y.data_ptr()
+        # learn the layer order on this thread (wraps around from the stage's last layer to its first,
+        # which is what the next micro-batch runs), then prefetch one GEMM / one layer ahead
+        prev = _chain.last
+        if prev is not None and prev is not layer:
+            prev.__dict__["_pb2_next"] = layer
+            layer.__dict__["_pb2_prev"] = prev
+        _chain.last = layer
+        d.prefetch = int(_PREFETCH)
+        nxt = layer.__dict__.get("_pb2_next")
+        if _PREFETCH and nxt is not None and nxt is not layer:
+            w_next, _ = nxt._sh("qkv")
+            if w_next.device == dev:
+                d.next_weight, d.next_weight_bytes = w_next.data_ptr(), w_next.numel() * 2
         base, at = act.data_ptr(), 0
         for name, w in zip(("qkv", "a", "o", "x1", "hmid", "f"), widths):
             setattr(d, name, base + at * 2)
@@ -208,6 +238,12 @@ class _EncoderLayerFn(torch.autograd.Function):
         d.T, d.NB, d.S = T, NB, S
         d.drop_p, d.seed = p, seed
         d.x, d.dy, d.dx = x2.data_ptr(), dy2.data_ptr(), dx.data_ptr()
+        d.prefetch = int(_PREFETCH)
+        before = layer.__dict__.get("_pb2_prev")          # runs its backward right after this one
+        if _PREFETCH and before is not None and before is not layer:
+            _, wt_prev = before._sh("l2")
+            if wt_prev.device == dev:
+                d.next_weight, d.next_weight_bytes = wt_prev.data_ptr(), wt_prev.numel() * 2
         base, at = act.data_ptr(), 0
         for name, w in zip(("qkv", "a", "o", "x1", "hmid", "f"), (3 * E, E, E, E, FF, E)):
             setattr(d, name, base + at * 2)
