@@ -12,7 +12,7 @@ Parity: reference ``pipe.py:446-464,476-477,484,490``, ``pipeline.py:44-54,229``
 """
 from __future__ import annotations
 
-from typing import Any, Callable, Iterator, List, Sequence, Tuple, Union
+from typing import Any, Callable, Iterator, List, Optional, Sequence, Tuple, Union
 
 import torch
 from torch import Tensor
@@ -163,6 +163,52 @@ def scatter(*inputs: Any, chunks: int) -> List[Batch]:
     return [Batch(tuple(col[i] for col in columns)) for i in range(n_pieces)]
 
 
+def _adjacent_base(tensors: Sequence[Tensor]) -> Optional[Tensor]:
+    """If ``tensors`` are consecutive dim-0 slices of one contiguous buffer (a last stage that wrote
+    its micro-batch outputs straight into a :class:`GatherBuffer`), return the zero-copy view that
+    spans them; else ``None``."""
+    first = tensors[0]
+    if not first.is_contiguous() or first.dim() == 0:
+        return None
+    storage = first.untyped_storage()
+    item = first.element_size()
+    at = first.storage_offset()
+    rows = 0
+    for t in tensors:
+        if (t.dtype != first.dtype or t.device != first.device or t.shape[1:] != first.shape[1:]
+                or not t.is_contiguous() or t.untyped_storage().data_ptr() != storage.data_ptr()
+                or t.storage_offset() != at):
+            return None
+        at += t.numel()
+        rows += t.size(0)
+    if (first.storage_offset() + (at - first.storage_offset())) * item > storage.nbytes():
+        return None
+    return torch.empty(0, dtype=first.dtype, device=first.device).set_(
+        storage, first.storage_offset(), (rows, *first.shape[1:]))
+
+
+class _AdjacentCat(torch.autograd.Function):
+    """``torch.cat`` of tensors that already sit next to each other in memory: forward is a view,
+    backward splits the gradient (the gather copy of the mini-batch output goes away)."""
+
+    @staticmethod
+    def forward(ctx, base: Tensor, *tensors: Tensor) -> Tensor:  # type: ignore[override]
+        ctx.sizes = [t.size(0) for t in tensors]
+        return base.detach()
+
+    @staticmethod
+    def backward(ctx, grad: Tensor):  # type: ignore[override]
+        return (None,) + tuple(grad.split(ctx.sizes))
+
+
+def _cat(tensors: Sequence[Tensor]) -> Tensor:
+    if len(tensors) > 1:
+        base = _adjacent_base(tensors)
+        if base is not None:
+            return _AdjacentCat.apply(base, *tensors)
+    return torch.cat(tuple(tensors))
+
+
 def gather(outputs: List[Batch]):
     """Concatenate micro-batch outputs back into a mini-batch.
 
@@ -171,7 +217,7 @@ def gather(outputs: List[Batch]):
     one entry per micro-batch.
     """
     if outputs[0].atomic:
-        return torch.cat(tuple(b.tensor for b in outputs))
+        return _cat([b.tensor for b in outputs])
 
     width = len(outputs[0])
     gathered: List[Any] = []
@@ -182,7 +228,7 @@ def gather(outputs: List[Batch]):
             if type(b[k]) is not kind:
                 raise TypeError(f"Types for microbatch outputs do not match, found: {kind} and {type(b[k])}")
             column.append(b[k])
-        gathered.append(torch.cat(column) if torch.is_tensor(outputs[0][k]) else column)
+        gathered.append(_cat(column) if torch.is_tensor(outputs[0][k]) else column)
     return tuple(gathered)
 
 
@@ -208,5 +254,10 @@ class GatherBuffer:
             start += s
 
     def slot(self, i: int) -> Tensor:
+        """Micro-batch ``i``'s rows as an *alias* of the buffer (same memory, but not an autograd
+        view of it: in-place writes into neighbouring slots must not trip view/version tracking)."""
         lo, hi = self.offsets[i]
-        return self.buffer[lo:hi]
+        b = self.buffer
+        row = b[0].numel() if b.size(0) else 0
+        return torch.empty(0, dtype=b.dtype, device=b.device).set_(
+            b.untyped_storage(), b.storage_offset() + lo * row, (hi - lo, *b.shape[1:]))

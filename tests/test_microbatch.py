@@ -109,3 +109,29 @@ def test_gather_buffer():
     gb.slot(0).fill_(1)
     gb.slot(1).fill_(2)
     assert gb.buffer[:, 0].tolist() == [1, 1, 1, 2, 2]
+
+
+def test_gather_is_zero_copy_for_adjacent_slices_and_keeps_gradients():
+    gb = GatherBuffer(5, (2,), dtype=torch.float32, device=torch.device("cpu"))
+    gb.plan([3, 2])
+    w = torch.ones(2, requires_grad=True)
+
+    class WriteInto(torch.autograd.Function):
+        @staticmethod
+        def forward(ctx, x, slot):
+            slot.copy_(x)          # what a last-stage kernel does with the raw pointer
+            return torch.empty(0).set_(slot.untyped_storage(), slot.storage_offset(), slot.shape)
+
+        @staticmethod
+        def backward(ctx, g):
+            return g, None
+
+    a = WriteInto.apply(torch.arange(6.0).view(3, 2) * w, gb.slot(0))
+    b = WriteInto.apply(torch.arange(4.0).view(2, 2) * w, gb.slot(1))
+    out = gather([Batch(a), Batch(b)])
+    assert out.data_ptr() == gb.buffer.data_ptr() and out.shape == (5, 2)      # no copy
+    out.sum().backward()
+    assert w.grad.tolist() == [0 + 2 + 4 + 0 + 2, 1 + 3 + 5 + 1 + 3]
+    # non-adjacent tensors still go through torch.cat
+    c = gather([Batch(torch.zeros(2, 2)), Batch(torch.ones(1, 2))])
+    assert c.shape == (3, 2)
