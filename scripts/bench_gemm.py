@@ -77,7 +77,21 @@ def case(name, M, N, K, out_f32=False, transpose=True, **kw):
 
 
 T, E, V = 75, 4096, 28782
-if args.sweep and os.environ.get("SWEEP") == "wgrad":
+if args.sweep and os.environ.get("SWEEP") == "epi":
+    mask = torch.randn(T, E, device=dev).bfloat16()
+    bias = torch.randn(E, device=dev)
+    case("E x E plain", E, T, E)
+    case("E x E bias", E, T, E, bias=bias, bias_along_m=True)
+    case("E x E bias+relu+drop", E, T, E, bias=bias, bias_along_m=True, relu=True, drop_p=0.2, seed=3)
+    case("E x E mask", E, T, E, mask_src=mask, mask_scale=1.25)
+    case("E x E addend", E, T, E, addend=mask)
+    case("E x E plain splits=2", E, T, E, splits=2)
+    case("E x E plain splits=8", E, T, E, splits=8)
+    case("3E x E plain (QKV)", 3 * E, T, E)
+    case("3E x E splits=2", 3 * E, T, E, splits=2)
+    case("E x 3E (QKV dgrad)", E, T, 3 * E)
+    case("E x 3E splits=8", E, T, 3 * E, splits=8)
+elif args.sweep and os.environ.get("SWEEP") == "wgrad":
     for bn in (256, 128, 64):
         for stages in (0, 2, 4):
             case("sweep wgrad ExE", E, E, 512, out_f32=True, transpose=False, block_n=bn, stages=stages)

@@ -23,3 +23,15 @@ for e in ev[start:start + 70]:
     print(f"{s:10.1f} us  dur {d:7.1f}  gap {gap:7.1f}  {e.name[:60]}")
     prev_end = e.time_range.end
 print("total span", ev[-1].time_range.end - t0, "us; kernels", len(ev))
+# ---- idle-gap summary over the whole step ----
+gaps = []
+busy_end = ev[0].time_range.end
+for a, b in zip(ev, ev[1:]):
+    busy_end = max(busy_end, a.time_range.end)
+    g = b.time_range.start - busy_end
+    if g > 5:
+        gaps.append((g, a.name[:38], b.name[:38], b.time_range.start - t0))
+tot = sum(g for g, *_ in gaps)
+print(f"idle gaps > 5 us: {len(gaps)} totalling {tot:.0f} us of {ev[-1].time_range.end - t0:.0f} us")
+for g, a, b, at in sorted(gaps, reverse=True)[:25]:
+    print(f"  gap {g:7.1f} us at {at:9.1f}: after {a}  before {b}")
