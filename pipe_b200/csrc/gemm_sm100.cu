@@ -43,6 +43,7 @@ constexpr int kBlockM = 128;
 constexpr int kBlockK = 64;          // 64 bf16 = one 128-byte swizzle row
 constexpr int kUmmaK = 16;
 constexpr int kMaxStages = 8;
+constexpr int kStagePitch = 20;         // floats per row of a staged 16-column chunk (80 B: 16-byte aligned, conflict-free)
 constexpr int kEpilogueWarps = 8;       // two per TMEM lane quarter, alternating 16-column chunks
 constexpr int kThreads = 64 + 32 * kEpilogueWarps;
 
@@ -115,8 +116,51 @@ struct EpiCtx {
     bool row_ok;
 };
 
+// Everything in a chunk's epilogue that does not depend on the accumulator — the dropout
+// keep-bits and the mask / residual operands from global memory — gathered ahead of time, so that in
+// the cluster path it is computed / in flight while the split-K partials cross the cluster instead of
+// after them.
+struct ChunkPre {
+    uint32_t keep;       // bit j: element j survives dropout
+    float mk[16];        // mask_src values
+    float ad[16];        // addend values
+    bool have;
+};
+
+__device__ __forceinline__ void epilogue_prefetch(const GemmArgs& g, const EpiCtx& e, int m_glob, int n_first,
+                                                  ChunkPre& pre) {
+    const bool tr = g.transpose_out != 0;
+    const long long stride = tr ? g.ld_out : 1;
+    const long long idx0 = tr ? static_cast<long long>(n_first) * g.ld_out + m_glob
+                              : static_cast<long long>(m_glob) * g.ld_out + n_first;
+    const int n_valid = g.N - n_first;
+    pre.have = true;
+    pre.keep = 0xFFFFu;
+    if (e.row_ok) {
+        if (g.mask_src) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) pre.mk[j] = (j < n_valid) ? __bfloat162float(g.mask_src[idx0 + j * stride]) : 0.f;
+        }
+        if (g.addend) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) pre.ad[j] = (j < n_valid) ? __bfloat162float(g.addend[idx0 + j * stride]) : 0.f;
+        }
+    }
+    if (g.drop_p > 0.f) {
+        uint32_t bits = 0;
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            const uint64_t idx = static_cast<uint64_t>(idx0 + j * stride);
+            const uint4 r = e.rng(idx >> 2, g.stream);
+            const uint32_t sel = (idx & 3) == 0 ? r.x : (idx & 3) == 1 ? r.y : (idx & 3) == 2 ? r.z : r.w;
+            bits |= (sel >= e.thr ? 1u : 0u) << j;
+        }
+        pre.keep = bits;
+    }
+}
+
 __device__ __forceinline__ void epilogue_chunk(const GemmArgs& g, const EpiCtx& e, float (&v)[16], int m_glob,
-                                               int n_first, float& ss) {
+                                               int n_first, float& ss, const ChunkPre* pre = nullptr) {
     const bool tr = g.transpose_out != 0;
     const long long stride = tr ? g.ld_out : 1;
     const long long idx0 = tr ? static_cast<long long>(n_first) * g.ld_out + m_glob
@@ -138,7 +182,10 @@ __device__ __forceinline__ void epilogue_chunk(const GemmArgs& g, const EpiCtx& 
 #pragma unroll
         for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j], 0.f);
     }
-    if (g.drop_p > 0.f) {
+    if (g.drop_p > 0.f && pre) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) v[j] = ((pre->keep >> j) & 1u) ? v[j] * e.inv_keep : 0.f;
+    } else if (g.drop_p > 0.f) {
         if (tr) {
             // element index n * ld + m: lanes m..m+3 share a counter, each column needs its own call
 #pragma unroll
@@ -163,14 +210,16 @@ __device__ __forceinline__ void epilogue_chunk(const GemmArgs& g, const EpiCtx& 
     if (g.mask_src) {
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
-            const float mk = (j < n_valid) ? __bfloat162float(g.mask_src[idx0 + j * stride]) : 0.f;
+            const float mk = pre ? pre->mk[j] : ((j < n_valid) ? __bfloat162float(g.mask_src[idx0 + j * stride]) : 0.f);
             v[j] = mk > 0.f ? v[j] * g.mask_scale : 0.f;
         }
     }
     if (g.addend) {
 #pragma unroll
-        for (int j = 0; j < 16; ++j)
-            if (j < n_valid) v[j] += __bfloat162float(g.addend[idx0 + j * stride]);
+        for (int j = 0; j < 16; ++j) {
+            if (pre) v[j] += pre->ad[j];
+            else if (j < n_valid) v[j] += __bfloat162float(g.addend[idx0 + j * stride]);
+        }
     }
 
     if (g.out_f32) {
@@ -401,7 +450,9 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         // ---- split-K reduction inside the cluster, through distributed shared memory ----
         // Chunk k (16 accumulator columns) is owned by cluster rank k % splits.  Every CTA sends its
         // partial of each foreign chunk into the owner's staging area (the now idle TMA ring):
-        //   staging[src rank][owner-local chunk][column 0..15][row 0..127]  fp32
+        //   staging[src rank][owner-local chunk][row 0..127][16 columns, row pitch 20 floats]  fp32
+        // (a thread owns an accumulator row, so it ships 64 contiguous bytes as four 16-byte DSMEM
+        // stores; the 80-byte pitch keeps the owner's 16-byte reads free of bank conflicts)
         // and each owner then finishes only its own chunks, so the fix-up and the epilogue are
         // spread over all CTAs of the tile and no partial tile ever goes to global memory.
         const uint32_t rank = cluster_ctarank();
@@ -415,17 +466,29 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                 tmem_ld_32x16(t_lane + k * 16, r);
                 tmem_ld_wait();
                 const uint32_t local = stage_base +
-                    (((rank * g.local_chunks + (k / g.splits)) * 16) * kBlockM + m_local) * 4u;
+                    ((rank * g.local_chunks + (k / g.splits)) * kBlockM + m_local) * (kStagePitch * 4u);
                 const uint32_t remote = dsmem_addr(local, owner);
 #pragma unroll
-                for (int j = 0; j < 16; ++j) dsmem_st_f32(remote + j * kBlockM * 4, __uint_as_float(r[j]));
+                for (int j = 0; j < 16; j += 4)
+                    dsmem_st_f32x4(remote + j * 4, __uint_as_float(r[j]), __uint_as_float(r[j + 1]),
+                                   __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
             }
+        }
+        // While the partials are in flight: everything of this thread's first owned chunk that does not
+        // depend on them (dropout bits, mask / residual operands, bias).
+        EpiCtx e{CounterRng(g.seed), static_cast<uint32_t>(fminf(g.drop_p, 0.999999f) * 4294967296.0f),
+                 g.drop_p > 0.f ? 1.f / (1.f - g.drop_p) : 1.f, 0.f, m_glob < g.M};
+        ChunkPre pre;
+        pre.have = false;
+        if (is_epi) {
+            if (g.bias && g.bias_along_m && e.row_ok) e.bias_m = g.bias[m_glob];
+            const int k_first = half * g.splits + static_cast<int>(rank);
+            if (half < g.local_chunks && k_first < n_chunks && n0 + k_first * 16 < g.N &&
+                (g.drop_p > 0.f || g.mask_src || g.addend))
+                epilogue_prefetch(g, e, m_glob, n0 + k_first * 16, pre);
         }
         cluster_sync_all();                                   // (2) all partials delivered
         if (is_epi) {
-            EpiCtx e{CounterRng(g.seed), static_cast<uint32_t>(fminf(g.drop_p, 0.999999f) * 4294967296.0f),
-                     g.drop_p > 0.f ? 1.f / (1.f - g.drop_p) : 1.f, 0.f, m_glob < g.M};
-            if (g.bias && g.bias_along_m && e.row_ok) e.bias_m = g.bias[m_glob];
             float ss = 0.f;
             const float* staging = reinterpret_cast<const float*>(smem);
             for (int kl = half; kl < g.local_chunks; kl += 2) {
@@ -439,11 +502,16 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                 for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
                 for (int src = 0; src < g.splits; ++src) {
                     if (src == static_cast<int>(rank)) continue;
-                    const float* p = staging + ((static_cast<size_t>(src) * g.local_chunks + kl) * 16) * kBlockM + m_local;
+                    const float4* p = reinterpret_cast<const float4*>(
+                        staging + ((static_cast<size_t>(src) * g.local_chunks + kl) * kBlockM + m_local) * kStagePitch);
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) v[j] += p[j * kBlockM];
+                    for (int q = 0; q < 4; ++q) {
+                        const float4 t = p[q];
+                        v[4 * q] += t.x; v[4 * q + 1] += t.y; v[4 * q + 2] += t.z; v[4 * q + 3] += t.w;
+                    }
                 }
-                if (n0 + k * 16 < g.N) epilogue_chunk(g, e, v, m_glob, n0 + k * 16, ss);
+                if (n0 + k * 16 < g.N)
+                    epilogue_chunk(g, e, v, m_glob, n0 + k * 16, ss, (kl == half && pre.have) ? &pre : nullptr);
             }
             if (g.sumsq) {
                 ss = warp_sum(ss);
@@ -623,7 +691,7 @@ static int gemm_launch(const pb2_gemm_desc* d, float* partials, unsigned int* co
     // staging area fits the idle TMA ring; otherwise through the global scratch workspace
     const int n_chunks = bn / 16;
     g.local_chunks = (n_chunks + splits - 1) / splits;
-    const size_t staging = static_cast<size_t>(splits) * g.local_chunks * 16 * kBlockM * sizeof(float);
+    const size_t staging = static_cast<size_t>(splits) * g.local_chunks * kStagePitch * kBlockM * sizeof(float);
     const bool pow2 = (splits & (splits - 1)) == 0;
     g.cluster_reduce = (splits > 1 && splits <= 8 && pow2 && !force_scratch && d->reduce_mode != 1 &&
                         staging <= static_cast<size_t>(stages) * stage_bytes) ? 1 : 0;

@@ -290,3 +290,36 @@ def test_trace_cells_labels(monkeypatch):
     pipe.trace_cells(True)
     pipe(torch.rand(2, 1))
     assert sorted(seen) == ["chunk0-part0", "chunk0-part1", "chunk1-part0", "chunk1-part1"]
+
+
+@pytest.mark.parametrize("inline", [True, False])
+def test_inline_last_cell_toggle_is_transparent(inline):
+    """Running the last cell of a tick on the calling thread or on its worker gives the same result,
+    the same exception behaviour and the same thread for the *other* cells."""
+    import threading
+    torch.manual_seed(0)
+    seen = []
+
+    class Probe(nn.Module):
+        def forward(self, x):
+            seen.append(threading.current_thread().name)
+            return x * 1.0
+
+    seq = nn.Sequential(nn.Linear(4, 4), Probe(), nn.Linear(4, 2))
+    ref = nn.Sequential(nn.Linear(4, 4), nn.Identity(), nn.Linear(4, 2))
+    ref[0].load_state_dict(seq[0].state_dict())
+    ref[2].load_state_dict(seq[2].state_dict())
+    pipe = Pipe(seq, chunks=3, checkpoint="except_last")
+    pipe.pipeline.inline_last_cell = inline
+    x = torch.rand(6, 4)
+    out = pipe(x).local_value()
+    assert torch.allclose(out, ref(x), atol=1e-6)
+    out.sum().backward()
+    ref(x).sum().backward()
+    assert torch.allclose(pipe[0].weight.grad, ref[0].weight.grad, atol=1e-6)
+    main = threading.current_thread().name
+    if inline:
+        assert main in seen                      # some cells ran on the calling thread
+    else:
+        assert main not in seen[:3]              # forward cells all went through the worker
+    pipe.close()
