@@ -62,6 +62,9 @@ typedef struct pb2_gemm_desc {
     int a_static;         /* 1: A is a weight that the kernel launched just before this one on the stream does
                              not write, so its first tiles may be fetched while that kernel is still running
                              (programmatic dependent launch); 0: wait for the predecessor before any load */
+    int persistent;       /* tile scheduling when there is no split-K: 0 = choose (persistent CTAs with a
+                             double-buffered TMEM accumulator when there are more tiles than SMs),
+                             1 = always persistent, 2 = one CTA per tile */
 } pb2_gemm_desc;
 
 size_t pb2_gemm_workspace_bytes(void);

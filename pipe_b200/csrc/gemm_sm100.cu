@@ -595,6 +595,184 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     if (threadIdx.x == 32) PB2_TS(6);
 }
 
+// ---------------------------------------------------------------------------------------
+// Persistent variant for problems with more output tiles than SMs (no split-K): the weight-gradient
+// GEMMs (4096 x 4096 fp32 outputs, 512 tiles) and the large-token GEMMs of big micro-batches.
+//
+// One CTA per SM walks tiles blockIdx.x, blockIdx.x + gridDim.x, ...  The TMA ring runs straight
+// across tile boundaries and the accumulator is double-buffered in TMEM (2 x block_n columns), so
+// the tensor core works on tile i+1 while the eight epilogue warps drain tile i: for a K=512 wgrad
+// tile the 128 KB fp32 store takes longer than the MMAs, and without the overlap the two add up.
+// Tiles are walked M-fastest, so CTAs that run side by side share the same B tile in L2.
+//   acc_full[b]  : MMA warp -> epilogue   (tcgen05.commit)
+//   acc_empty[b] : epilogue -> MMA warp   (one arrival per epilogue warp)
+struct __align__(8) SmemCtlP {
+    uint64_t full[kMaxStages];
+    uint64_t empty[kMaxStages];
+    uint64_t acc_full[2];
+    uint64_t acc_empty[2];
+    uint32_t tmem_base;
+    uint32_t pad;
+};
+
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_bf16_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                            const GemmArgs g, const int m_tiles, const int n_tiles) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    // carve: [stages][A 16 KB][B block_n*128 B], then 20 KB of epilogue staging, then the control block
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    const uint32_t a_bytes = kBlockM * kBlockK * 2;
+    const uint32_t b_bytes = g.block_n * kBlockK * 2;
+    const uint32_t stage_bytes = a_bytes + b_bytes;
+    float* staging = reinterpret_cast<float*>(smem + g.ring_bytes);
+    SmemCtlP* ctl = reinterpret_cast<SmemCtlP*>(smem + g.ring_bytes + kEpilogueWarps * 32 * kStagePitch * 4);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int total_tiles = m_tiles * n_tiles;
+    const int my_tiles = (total_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+    const int kbt = g.k_blocks_total;
+    const int total_it = my_tiles * kbt;
+    const uint32_t acc_stride = static_cast<uint32_t>(g.tmem_cols) >> 1;
+
+    pdl_launch_dependents();
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmap_a);
+        tma_prefetch_desc(&tmap_b);
+        for (int s = 0; s < g.stages; ++s) {
+            mbar_init(&ctl->full[s], 1);
+            mbar_init(&ctl->empty[s], 1);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(&ctl->acc_full[b], 1);
+            mbar_init(&ctl->acc_empty[b], kEpilogueWarps);
+        }
+        fence_mbar_init();
+    }
+    if (warp == 1) {
+        tmem_alloc(&ctl->tmem_base, g.tmem_cols);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = ctl->tmem_base;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (elect_one()) {
+            int pre = 0;
+            if (g.a_static) {
+                // weights do not depend on the preceding kernel: request the first ring of A right away
+                pre = total_it < g.stages ? total_it : g.stages;
+                for (int it = 0; it < pre; ++it) {
+                    const int tile = blockIdx.x + (it / kbt) * gridDim.x;
+                    mbar_expect_tx(&ctl->full[it], stage_bytes);
+                    tma_load_2d(smem + static_cast<size_t>(it) * stage_bytes, &tmap_a, &ctl->full[it],
+                                (it % kbt) * kBlockK, (tile % m_tiles) * kBlockM, kEvictLast);
+                }
+            }
+            pdl_wait();
+            for (int it = 0; it < pre; ++it) {
+                const int tile = blockIdx.x + (it / kbt) * gridDim.x;
+                tma_load_2d(smem + static_cast<size_t>(it) * stage_bytes + a_bytes, &tmap_b, &ctl->full[it],
+                            (it % kbt) * kBlockK, (tile / m_tiles) * g.block_n, kEvictLast);
+            }
+            int s = pre % g.stages;
+            uint32_t round = pre / g.stages;
+            int kb = pre % kbt;
+            int tile = blockIdx.x + (pre / kbt) * gridDim.x;
+            for (int it = pre; it < total_it; ++it) {
+                mbar_wait(&ctl->empty[s], (round & 1) ^ 1);
+                uint8_t* sa = smem + static_cast<size_t>(s) * stage_bytes;
+                mbar_expect_tx(&ctl->full[s], stage_bytes);
+                // every operand tile is read by a whole row / column of output tiles: keep both in L2
+                tma_load_2d(sa, &tmap_a, &ctl->full[s], kb * kBlockK, (tile % m_tiles) * kBlockM, kEvictLast);
+                tma_load_2d(sa + a_bytes, &tmap_b, &ctl->full[s], kb * kBlockK, (tile / m_tiles) * g.block_n, kEvictLast);
+                if (++s == g.stages) { s = 0; ++round; }
+                if (++kb == kbt) { kb = 0; tile += gridDim.x; }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        const uint32_t idesc = umma_idesc_bf16(kBlockM, g.block_n);
+        int s = 0;
+        uint32_t round = 0;
+        for (int t = 0; t < my_tiles; ++t) {
+            const uint32_t acc = t & 1;
+            mbar_wait(&ctl->acc_empty[acc], ((t >> 1) & 1) ^ 1);      // epilogue has drained this accumulator
+            tc_fence_after();
+            const uint32_t d_tmem = tmem_base + acc * acc_stride;
+            for (int kb = 0; kb < kbt; ++kb) {
+                mbar_wait(&ctl->full[s], round & 1);
+                tc_fence_after();
+                if (elect_one()) {
+                    const uint32_t sa = smem_u32(smem + static_cast<size_t>(s) * stage_bytes);
+                    const uint64_t da = umma_desc_k_sw128(sa);
+                    const uint64_t db = umma_desc_k_sw128(sa + a_bytes);
+#pragma unroll
+                    for (int k = 0; k < kBlockK / kUmmaK; ++k)
+                        umma_bf16(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+                    umma_commit(&ctl->empty[s]);
+                    if (kb == kbt - 1) umma_commit(&ctl->acc_full[acc]);
+                }
+                __syncwarp();
+                if (++s == g.stages) { s = 0; ++round; }
+            }
+        }
+    } else {
+        // ===================== epilogue (warps 2..9) =====================
+        const int quarter = warp & 3;
+        const int half = (warp - 2) >> 2;
+        const int m_local = quarter * 32 + lane;
+        const bool staged = !g.transpose_out && !g.relu && g.drop_p <= 0.f && !g.mask_src && !g.addend;
+        float* st = staging + (warp - 2) * (32 * kStagePitch);
+        float ss = 0.f;
+        for (int t = 0; t < my_tiles; ++t) {
+            const int tile = blockIdx.x + t * gridDim.x;
+            const int m0 = (tile % m_tiles) * kBlockM;
+            const int n0 = (tile / m_tiles) * g.block_n;
+            const int m_glob = m0 + m_local;
+            const uint32_t acc = t & 1;
+            EpiCtx e{CounterRng(g.seed), static_cast<uint32_t>(fminf(g.drop_p, 0.999999f) * 4294967296.0f),
+                     g.drop_p > 0.f ? 1.f / (1.f - g.drop_p) : 1.f, 0.f, m_glob < g.M};
+            if (g.bias && g.bias_along_m && e.row_ok) e.bias_m = g.bias[m_glob];
+            mbar_wait(&ctl->acc_full[acc], (t >> 1) & 1);
+            tc_fence_after();
+            const uint32_t t_lane = tmem_base + acc * acc_stride + (static_cast<uint32_t>(quarter * 32) << 16);
+            for (int c = half * 16; c < g.block_n; c += 32) {
+                uint32_t r[16];
+                tmem_ld_32x16(t_lane + c, r);
+                tmem_ld_wait();
+                float v[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
+                if (n0 + c < g.N) {
+                    if (staged)
+                        epilogue_chunk_staged(g, st, v, m0, quarter, lane, n0 + c, e.bias_m, ss);
+                    else
+                        epilogue_chunk(g, e, v, m_glob, n0 + c, ss);
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&ctl->acc_empty[acc]);      // the MMA warp may overwrite this accumulator
+        }
+        if (g.sumsq) {
+            ss = warp_sum(ss);
+            if (lane == 0) atomicAdd(g.sumsq, ss);
+        }
+        tc_fence_before();
+    }
+
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, g.tmem_cols);
+    }
+}
+
 static int next_pow2_cols(int n) {
     int c = 32;
     while (c < n) c <<= 1;
@@ -615,6 +793,19 @@ static unsigned long long* g_debug_ts = nullptr;
 // Debug hook (not part of the supported ABI): phase timestamps of subsequent launches go to `buf`
 // (8 x u64 per CTA, CTA-linear order); pass NULL to switch off.
 extern "C" void pb2_debug_gemm_timestamps(unsigned long long* buf) { g_debug_ts = buf; }
+
+// SM count of the current device (cached per device ordinal).
+static int sm_count() {
+    static int cache[64] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (cache[dev] == 0) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        cache[dev] = n;
+    }
+    return cache[dev];
+}
 
 static int gemm_launch(const pb2_gemm_desc* d, float* partials, unsigned int* counters, size_t partial_bytes,
                        size_t counter_slots, cudaStream_t stream, bool force_scratch = false) {
@@ -681,7 +872,7 @@ static int gemm_launch(const pb2_gemm_desc* d, float* partials, unsigned int* co
         if (two >= 2 && two < stages) stages = two;
     }
     if (stages > kMaxStages) stages = kMaxStages;
-    if (d->stages > 0 && d->stages < stages) stages = d->stages;
+    if (d->stages > 0) stages = d->stages < (200 * 1024) / stage_bytes ? d->stages : (200 * 1024) / stage_bytes;   // explicit request wins
     if (stages > g.k_blocks_per_split) stages = g.k_blocks_per_split;
     if (stages < 1) stages = 1;
     g.stages = stages;
@@ -724,6 +915,35 @@ static int gemm_launch(const pb2_gemm_desc* d, float* partials, unsigned int* co
     CUtensorMap ta, tb;
     if (make_tmap_bf16_2d(&ta, d->a, d->M, d->K, d->lda, kBlockM, kBlockK)) return -1;
     if (make_tmap_bf16_2d(&tb, d->b, d->N, d->K, d->ldb, bn, kBlockK)) return -1;
+
+    // more tiles than SMs and no split-K: one persistent CTA per SM, epilogue overlapped with the next tile
+    if (splits == 1 && d->persistent != 2 && (d->persistent == 1 || tiles > sm_count())) {
+        int pst = (204 * 1024) / stage_bytes;
+        if (pst > kMaxStages) pst = kMaxStages;
+        if (d->stages > 0 && d->stages < pst) pst = d->stages;
+        if (pst >= 2 && 2 * bn <= 512) {
+            g.stages = pst;
+            g.ring_bytes = pst * stage_bytes;
+            g.tmem_cols = next_pow2_cols(2 * bn);
+            g.debug_ts = nullptr;
+            const size_t smem_p = static_cast<size_t>(g.ring_bytes) + kEpilogueWarps * 32 * kStagePitch * 4 + sizeof(SmemCtlP) + 1024;
+            if (ensure_max_smem(reinterpret_cast<const void*>(gemm_bf16_persistent_kernel), 227 * 1024)) return -1;
+            cudaLaunchConfig_t pc;
+            memset(&pc, 0, sizeof(pc));
+            pc.gridDim = dim3(static_cast<unsigned>(tiles < sm_count() ? tiles : sm_count()));
+            pc.blockDim = dim3(kThreads);
+            pc.dynamicSmemBytes = smem_p;
+            pc.stream = stream;
+            cudaLaunchAttribute pa[1];
+            pa[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            pa[0].val.programmaticStreamSerializationAllowed = 1;
+            pc.attrs = pa;
+            pc.numAttrs = 1;
+            PB2_CUDA(cudaLaunchKernelEx(&pc, gemm_bf16_persistent_kernel, ta, tb, g, m_tiles, n_tiles));
+            PB2_LAUNCHED("gemm_bf16_persistent_kernel");
+            return 0;
+        }
+    }
 
     g.ring_bytes = stages * stage_bytes;
     if (g.ring_bytes < kEpilogueWarps * 32 * 20 * 4) g.ring_bytes = kEpilogueWarps * 32 * 20 * 4;   // staging needs 20 KB

@@ -36,6 +36,7 @@ class GemmDesc(ctypes.Structure):
         ("block_n", ctypes.c_int), ("splits", ctypes.c_int), ("stages", ctypes.c_int),
         ("reduce_mode", ctypes.c_int),
         ("a_static", ctypes.c_int),
+        ("persistent", ctypes.c_int),
     ]
 
 

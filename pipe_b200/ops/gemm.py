@@ -44,7 +44,7 @@ def gemm_nt(a: Tensor, b: Tensor, *, out: Optional[Tensor] = None, out_dtype: to
             relu: bool = False, drop_p: float = 0.0, seed: int = 0, rng_stream: int = 0,
             mask_src: Optional[Tensor] = None, mask_scale: float = 1.0, addend: Optional[Tensor] = None,
             accumulate: bool = False, alpha: float = 1.0, sumsq: Optional[Tensor] = None,
-            block_n: int = 0, splits: int = 0, stages: int = 0, reduce_mode: int = 0, a_static: bool = False,
+            block_n: int = 0, splits: int = 0, stages: int = 0, reduce_mode: int = 0, a_static: bool = False, persistent: int = 0,
             stream: Optional[int] = None) -> Tensor:
     lib = _lib.load()
     assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16, "gemm_nt takes bf16 operands"
@@ -83,6 +83,7 @@ def gemm_nt(a: Tensor, b: Tensor, *, out: Optional[Tensor] = None, out_dtype: to
     d.sumsq = _lib.ptr(sumsq)
     d.block_n, d.splits, d.stages, d.reduce_mode = block_n, splits, stages, reduce_mode
     d.a_static = int(a_static)
+    d.persistent = persistent
 
     if stream is None:
         stream = _lib.raw_stream(a.device)

@@ -91,6 +91,24 @@ if args.sweep and os.environ.get("SWEEP") == "epi":
     case("3E x E splits=2", 3 * E, T, E, splits=2)
     case("E x 3E (QKV dgrad)", E, T, 3 * E)
     case("E x 3E splits=8", E, T, 3 * E, splits=8)
+elif args.sweep and os.environ.get("SWEEP") == "persist":
+    # persistent (double-buffered accumulator) against one-CTA-per-tile, with a numerics check
+    for (nm, M, N, K, f32, tr) in (("wgrad ExE", E, E, 512, True, False), ("wgrad 3ExE", 3 * E, E, 512, True, False),
+                                   ("wgrad vocab", V, E, 512, True, False), ("shipped 1024 tok", 3 * 2048, 1024, 2048, False, True),
+                                   ("fwd vocab", V, T, E, False, True), ("dgrad vocab", E, T, V, False, True)):
+        a = torch.randn(M, (K + 7) // 8 * 8, device=dev).bfloat16()[:, :K]
+        b = torch.randn(N, (K + 7) // 8 * 8, device=dev).bfloat16()[:, :K]
+        want = a.float() @ b.float().t()
+        got = gemm_nt(a, b, transpose_out=tr, out_dtype=torch.float32 if f32 else torch.bfloat16, persistent=1).float()
+        if tr:
+            got = got.t()
+        err = ((got - want).abs().max() / want.abs().max()).item()
+        print(f"{nm}: persistent max rel err {err:.2e}", flush=True)
+        assert err < 2e-2
+        del a, b, want, got
+        for pers in (2, 1):
+            for stages in ((0, 3) if pers == 1 else (0, 4)):
+                case(nm, M, N, K, out_f32=f32, transpose=tr, persistent=pers, stages=stages)
 elif args.sweep and os.environ.get("SWEEP") == "wgrad":
     for bn in (256, 128, 64):
         for stages in (0, 2, 4):

@@ -9,15 +9,22 @@ dev = "cuda"
 flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
 names = ["start", "setup done", "first stage landed", "last MMA issued", "accum ready", "epilogue done", "end", "c0 pre-ld", "c0 post-ld", "c16 pre-ld", "c16 post-ld", "c32 pre", "c32 post", "c48 pre", "c48 post"]
 
-def run(M, N, K, **kw):
+def run(M, N, K, wgrad=False, **kw):
     a = torch.randn(M, K, device=dev).bfloat16(); b = torch.randn(N, K, device=dev).bfloat16()
-    out = torch.empty(N, M, dtype=torch.bfloat16, device=dev)
-    ctas = ((M + 127) // 128) * kw.get("splits", 1)
+    if wgrad:
+        out = torch.empty(M, N, dtype=torch.float32, device=dev)
+        bn = kw.get("block_n", 256)
+        ctas = ((M + 127) // 128) * ((N + bn - 1) // bn)
+        kw = dict(kw, transpose_out=False)
+    else:
+        out = torch.empty(N, M, dtype=torch.bfloat16, device=dev)
+        ctas = ((M + 127) // 128) * kw.get("splits", 1)
+        kw = dict(kw, transpose_out=True)
     ts = torch.zeros(ctas * 16, dtype=torch.int64, device=dev)
-    gemm_nt(a, b, out=out, transpose_out=True, **kw)
+    gemm_nt(a, b, out=out, **kw)
     flush.zero_()
     lib.pb2_debug_gemm_timestamps(ctypes.c_void_p(ts.data_ptr()))
-    gemm_nt(a, b, out=out, transpose_out=True, **kw)
+    gemm_nt(a, b, out=out, **kw)
     lib.pb2_debug_gemm_timestamps(ctypes.c_void_p(0))
     torch.cuda.synchronize()
     t = ts.view(ctas, 16).cpu()
@@ -28,6 +35,12 @@ def run(M, N, K, **kw):
         col = (t[:, k] - t0).float() / 1e3
         print(f"   {nm:20s} min {col.min():7.2f}  median {col.median():7.2f}  max {col.max():7.2f} us")
 
+if len(sys.argv) > 1 and sys.argv[1] == "big":
+    run(4096, 4096, 512, wgrad=True)
+    run(4096, 4096, 512, wgrad=True, stages=4)
+    run(6144, 1024, 2048)
+    run(6144, 1024, 2048, stages=4)
+    sys.exit(0)
 run(4096, 80, 4096, splits=4, reduce_mode=1)
 run(4096, 80, 4096, splits=4, reduce_mode=2)
 run(4096, 80, 4096, splits=2, reduce_mode=2)

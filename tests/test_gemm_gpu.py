@@ -112,3 +112,35 @@ def test_epilogue_mask_addend_accumulate_sumsq_alpha():
     gemm_nt(a, b, out=acc, accumulate=True, alpha=0.5, sumsq=ss)
     _close(acc, base * 0.5 + 1.0, atol=0.3)
     assert abs(ss.item() - (acc.double() ** 2).sum().item()) / (acc.double() ** 2).sum().item() < 1e-3
+
+
+@pytest.mark.parametrize("M,N,K,bn", [(2560, 2048, 320, 0), (2500, 1000, 200, 128), (20000, 75, 512, 0)])
+def test_persistent_schedule_is_bit_identical(M, N, K, bn):
+    """More tiles than SMs: persistent CTAs with the double-buffered TMEM accumulator must give exactly
+    what one CTA per tile gives, for every epilogue (same MMA order, same counter-RNG indices)."""
+    from pipe_b200.ops.gemm import gemm_nt
+    torch.manual_seed(1)
+    a = torch.randn(M, K, device="cuda").bfloat16()
+    b = torch.randn(N, K, device="cuda").bfloat16()
+    bias_m = torch.randn(M, device="cuda")
+    bias_n = torch.randn(N, device="cuda")
+    mask = torch.randn(N, M, device="cuda").bfloat16()
+    variants = [
+        dict(out_dtype=torch.float32),
+        dict(out_dtype=torch.float32, bias=bias_n, alpha=0.5),
+        dict(transpose_out=True, bias=bias_m, bias_along_m=True, relu=True, drop_p=0.3, seed=5, rng_stream=2),
+        dict(transpose_out=True, mask_src=mask, mask_scale=1.5, addend=mask),
+    ]
+    for kw in variants:
+        one = gemm_nt(a, b, block_n=bn, persistent=2, splits=1, **kw)
+        per = gemm_nt(a, b, block_n=bn, persistent=1, splits=1, **kw)
+        assert torch.equal(one, per), kw.keys()
+    want = _ref(a, b)
+    _close(gemm_nt(a, b, block_n=bn, persistent=1, splits=1, out_dtype=torch.float32), want, rtol=1e-2, atol=1e-2 * K ** 0.5)
+    # accumulate + sumsq across several tiles per CTA
+    acc1 = torch.ones(M, N, device="cuda"); acc2 = torch.ones(M, N, device="cuda")
+    s1 = torch.zeros((), device="cuda"); s2 = torch.zeros((), device="cuda")
+    gemm_nt(a, b, out=acc1, accumulate=True, sumsq=s1, block_n=bn, persistent=2, splits=1)
+    gemm_nt(a, b, out=acc2, accumulate=True, sumsq=s2, block_n=bn, persistent=1, splits=1)
+    assert torch.equal(acc1, acc2)
+    assert abs(s1.item() - s2.item()) <= 1e-4 * abs(s1.item())
