@@ -2,19 +2,31 @@
 // attention forward + backward on warp-level MMA (bf16 in, fp32 accumulate), everything else —
 // softmax, dropout mask, the dS recurrence — on the scores held in shared memory.
 //
-// One CTA owns one (sequence, head) pair for the whole pass; Q, K, V (and dO) are gathered from the
-// packed [T, 3E] projection output into zero-padded shared tiles, the S x S score matrix never
-// leaves the SM, and results are scattered straight back into the packed layouts the neighbouring
-// GEMMs read.  The SIMT kernels in attention.cu remain the fallback when the tiles do not fit
-// (S = 128 with head_dim > 64).
+// One (sequence, head) pair is owned by a thread-block cluster of 1, 2 or 4 CTAs for the whole pass.
+// With more than one CTA the head dimension is split: every CTA gathers its D / cs columns of Q, K, V
+// (and dO) from the packed [T, 3E] projection output into zero-padded shared tiles, computes the
+// partial S x S score products over those columns, and pushes them into its peers' shared memory
+// (DSMEM); after one cluster barrier every CTA holds all partials, sums them in the same order (so
+// the softmax is bit-identical across the cluster), and finishes the products whose outputs are its
+// own D / cs columns.  The S x S score matrix never leaves the SMs, and results are scattered
+// straight back into the packed layouts the neighbouring GEMMs read.
+//
+// Why split a head at all: a micro-batch of the tutorial configuration is 3 sequences x 16 heads =
+// 48 independent problems on 148 SMs, and each problem is bound by instruction issue of its one CTA
+// (ncu: issue slot busy ~100 %, 7.8 k instructions per warp), not by math or memory.  Four CTAs per
+// head put 192 CTAs on the machine and cut every D-proportional phase by four.
 //
 // Why warp-level MMA and not tcgen05 here: at S = 25 the whole problem is a 32 x 32 x 256 product
 // per head; a UMMA tile is 128 rows and needs TMA-swizzled operands, TMEM allocation and an mbarrier
 // pipeline — fixed costs that exceed the work.  These products are latency-, not throughput-bound
 // (attention is <= 0.2 % of the model's FLOPs).
+// The SIMT kernels in attention.cu remain the fallback when the tiles do not fit (S = 128 with
+// head_dim > 64).
 //
 // Reference counterpart: nn.MultiheadAttention core (main.py:148).  SURVEY.md K3.
 #include <mma.h>
+#include <stdlib.h>
+#include <string.h>
 
 #include "common.cuh"
 #include "pipe_b200.h"
@@ -42,6 +54,8 @@ struct AttnTc {
     int causal;
     float drop_p;
     unsigned long long seed, rng_stream;
+    int cs;                          // CTAs per (sequence, head): the cluster size
+    int Dc;                          // head-dim columns per CTA (D / cs)
 };
 
 typedef wmma::fragment<wmma::matrix_a, 16, 16, 16, __nv_bfloat16, wmma::row_major> FragA;
@@ -58,7 +72,7 @@ __device__ __forceinline__ void tc_gather(const __nv_bfloat16* b0, const __nv_bf
                                           const __nv_bfloat16* b3, long long ld012, long long ld3, __nv_bfloat16* d0,
                                           __nv_bfloat16* d1, __nv_bfloat16* d2, __nv_bfloat16* d3, int count, int NB, int S,
                                           int SP, int D, int n) {
-    const int dpad = D + 8, vec_per_row = D / 8;              // 8 .. 32 vectors per row
+    const int dpad = D + 8, vec_per_row = D / 8;              // 2 .. 32 vectors per row
     const int lanes_per_row = vec_per_row >= 32 ? 32 : vec_per_row;
     const int rows_per_warp = 32 / lanes_per_row;             // rows one warp instruction covers
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -93,28 +107,59 @@ __device__ __forceinline__ void tc_gather(const __nv_bfloat16* b0, const __nv_bf
     }
 }
 
-// C[SP x SP] (fp32, ld = SP + 8) = A[SP x D] * B[SP x D]^T, both row-major bf16 with ld = D + 8.
-__device__ __forceinline__ void tc_abt(const __nv_bfloat16* A, const __nv_bfloat16* B, float* C, int SP, int D) {
+// One or two score-shaped products at once, the tiles of both spread over all warps:
+//   C0[SP x SP] = A0[SP x D] * B0[SP x D]^T   and (if A1)   C1 = A1 * B1^T
+// fp32 results with ld = SP + 8; operands row-major bf16 with ld = D + 8.
+__device__ __forceinline__ void tc_abt(const __nv_bfloat16* A0, const __nv_bfloat16* B0, float* C0,
+                                       const __nv_bfloat16* A1, const __nv_bfloat16* B1, float* C1, int SP, int D) {
     const int warp = threadIdx.x >> 5, tiles = SP / 16, dpad = D + 8, cpad = SP + 8;
-    for (int t = warp; t < tiles * tiles; t += kTcWarps) {
-        const int ti = t / tiles, tj = t % tiles;
-        FragC acc;
-        wmma::fill_fragment(acc, 0.f);
-        for (int k = 0; k < D; k += 16) {
-            FragA a;
-            FragBT b;
-            wmma::load_matrix_sync(a, A + ti * 16 * dpad + k, dpad);
-            wmma::load_matrix_sync(b, B + tj * 16 * dpad + k, dpad);
-            wmma::mma_sync(acc, a, b, acc);
+    const int per = tiles * tiles, total = A1 ? 2 * per : per;
+    for (int t = warp; t < total; t += kTcWarps) {
+        const int second = t >= per;
+        const int r = t - second * per, ti = r / tiles, tj = r - ti * tiles;
+        const __nv_bfloat16* A = (second ? A1 : A0) + ti * 16 * dpad;
+        const __nv_bfloat16* B = (second ? B1 : B0) + tj * 16 * dpad;
+        // two accumulators break the MMA dependency chain along K
+        FragC acc0, acc1;
+        wmma::fill_fragment(acc0, 0.f);
+        wmma::fill_fragment(acc1, 0.f);
+        for (int k = 0; k < D; k += 32) {
+            FragA a0, a1;
+            FragBT b0, b1;
+            wmma::load_matrix_sync(a0, A + k, dpad);
+            wmma::load_matrix_sync(b0, B + k, dpad);
+            if (k + 16 < D) {
+                wmma::load_matrix_sync(a1, A + k + 16, dpad);
+                wmma::load_matrix_sync(b1, B + k + 16, dpad);
+            }
+            wmma::mma_sync(acc0, a0, b0, acc0);
+            if (k + 16 < D) wmma::mma_sync(acc1, a1, b1, acc1);
         }
-        wmma::store_matrix_sync(C + ti * 16 * cpad + tj * 16, acc, cpad, wmma::mem_row_major);
+#pragma unroll
+        for (int e = 0; e < acc0.num_elements; ++e) acc0.x[e] += acc1.x[e];
+        wmma::store_matrix_sync((second ? C1 : C0) + ti * 16 * cpad + tj * 16, acc0, cpad, wmma::mem_row_major);
     }
 }
 
-// Softmax over the first S columns of the first S rows of `sc` (scaled by `scale`), in place.
-// Eight lanes share a row, so 32 rows are in flight at once (a warp-per-row loop would walk the rows
-// one latency chain after another).  SP <= 128: at most 16 columns per lane.
-__device__ __forceinline__ void tc_softmax(float* sc, int S, int SP, float scale, int causal) {
+// Push `count` floats (a multiple of 4, 16-byte aligned) of this CTA's shared memory to the same
+// location in every other CTA of the cluster.
+__device__ __forceinline__ void tc_push(const float* local, int count, int cs, uint32_t rank) {
+    const uint32_t base = smem_u32(local);
+    for (int v = threadIdx.x * 4; v < count; v += kTcThreads * 4) {
+        const float4 x = *reinterpret_cast<const float4*>(local + v);
+#pragma unroll 4
+        for (int peer = 0; peer < cs; ++peer)
+            if (peer != static_cast<int>(rank)) dsmem_st_f32x4(dsmem_addr(base + v * 4u, peer), x.x, x.y, x.z, x.w);
+    }
+}
+
+// Softmax over the first S columns of the first S rows of the scores (scaled by `scale`).  The scores
+// arrive as `nslot` partial matrices `slot` floats apart (one per cluster rank) that are summed on
+// the way in; the probabilities are written to the first one.  Eight lanes share a row, so 32 rows
+// are in flight at once (a warp-per-row loop would walk the rows one latency chain after another).
+// SP <= 128: at most 16 columns per lane.
+template <int NSLOT>
+__device__ __forceinline__ void tc_softmax(float* sc, int slot, int S, int SP, float scale, int causal) {
     const int sub = threadIdx.x & 7, cpad = SP + 8;
     for (int i = threadIdx.x >> 3; i < SP; i += kTcThreads / 8) {
         float* r = sc + i * cpad;
@@ -124,7 +169,13 @@ __device__ __forceinline__ void tc_softmax(float* sc, int S, int SP, float scale
 #pragma unroll
         for (int u = 0; u < 16; ++u) {
             const int j = sub + u * 8;
-            x[u] = (j < lim) ? r[j] * scale : -INFINITY;
+            x[u] = -INFINITY;
+            if (j < lim) {
+                float t = r[j];
+#pragma unroll
+                for (int s = 1; s < NSLOT; ++s) t += r[s * slot + j];
+                x[u] = t * scale;
+            }
             mx = fmaxf(mx, x[u]);
         }
         mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 4));
@@ -155,88 +206,108 @@ __device__ __forceinline__ float tc_keep(const CounterRng& rng, const AttnTc& a,
     return dropout_keep(rng, a.rng_stream, idx, thr) ? inv_keep : 0.f;
 }
 
-// out rows (< S) of a [16 x 16] fp32 tile held in this warp's staging area -> bf16 global
-__device__ __forceinline__ void tc_emit_tile(const float* stage, __nv_bfloat16* dst_row0, long long ld_dst, int NB,
-                                             int row0, int S) {
+// out rows (< S) of a [16 x 16] fp32 tile held in this warp's staging area -> bf16 global;
+// `row_stride` is the distance between consecutive sequence positions in elements
+__device__ __forceinline__ void tc_emit_tile(const float* stage, __nv_bfloat16* dst_row0, size_t row_stride, int row0, int S) {
     const int lane = threadIdx.x & 31;
     // 16 rows x 8 column pairs = 128 pairs, 4 per lane
+    const int c2 = lane & 7, r_lo = lane >> 3;
+    __nv_bfloat16* dst = dst_row0 + r_lo * row_stride + c2 * 2;
+    const float* src = stage + r_lo * 24 + c2 * 2;
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
-        const int p = lane + q * 32, r = p >> 3, c2 = p & 7;
-        if (row0 + r < S) {
-            const float2 v = *reinterpret_cast<const float2*>(stage + r * 24 + c2 * 2);
-            reinterpret_cast<__nv_bfloat162*>(dst_row0 + static_cast<size_t>(r) * NB * ld_dst)[c2] =
-                __floats2bfloat162_rn(v.x, v.y);
+        if (row0 + r_lo + q * 4 < S) {
+            const float2 v = *reinterpret_cast<const float2*>(src + q * 4 * 24);
+            *reinterpret_cast<__nv_bfloat162*>(dst + q * 4 * row_stride) = __floats2bfloat162_rn(v.x, v.y);
         }
     }
 }
 
+template <int CS>
 __global__ void __launch_bounds__(kTcThreads)
 attn_tc_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out, const AttnTc a) {
     pdl_launch_dependents();
     attn_ts(0);
+    constexpr int cs = CS;
+    const uint32_t rank = cs > 1 ? cluster_ctarank() : 0u;
+    if (cs > 1) cluster_arrive();            // waited for right before the first DSMEM store: every peer is running by then
     extern __shared__ __align__(128) uint8_t smem[];
-    const int S = a.S, SP = a.SP, D = a.D, dpad = D + 8, cpad = SP + 8;
+    const int S = a.S, SP = a.SP, Dc = a.Dc, dpad = Dc + 8, cpad = SP + 8, slot = SP * cpad;
     __nv_bfloat16* q = reinterpret_cast<__nv_bfloat16*>(smem);
     __nv_bfloat16* k = q + SP * dpad;
     __nv_bfloat16* v = k + SP * dpad;
-    float* sc = reinterpret_cast<float*>(v + SP * dpad);
-    __nv_bfloat16* pb = reinterpret_cast<__nv_bfloat16*>(sc + SP * cpad);
-    float* stage = reinterpret_cast<float*>(pb + SP * cpad) + (threadIdx.x >> 5) * (16 * 24);
-    const int n = blockIdx.x / a.H, h = blockIdx.x % a.H;
+    float* sc = reinterpret_cast<float*>(v + SP * dpad);                     // cs partial score matrices
+    __nv_bfloat16* pb = reinterpret_cast<__nv_bfloat16*>(sc + cs * slot);
+    float* stage = reinterpret_cast<float*>(pb + slot) + (threadIdx.x >> 5) * (16 * 24);
+    const int pair = blockIdx.x / cs;
+    const int n = pair / a.H, h = pair - n * a.H;
     const long long ld = 3LL * a.E;
+    const int col0 = h * a.D + static_cast<int>(rank) * Dc;
 
-    tc_gather(qkv + h * D, qkv + a.E + h * D, qkv + 2 * a.E + h * D, nullptr, ld, 0, q, k, v, nullptr, 3, a.NB, S, SP, D, n);
+    tc_gather(qkv + col0, qkv + a.E + col0, qkv + 2 * a.E + col0, nullptr, ld, 0, q, k, v, nullptr, 3, a.NB, S, SP, Dc, n);
     __syncthreads();
     attn_ts(1);
-    tc_abt(q, k, sc, SP, D);
+    tc_abt(q, k, sc + rank * slot, nullptr, nullptr, nullptr, SP, Dc);
     __syncthreads();
+    if (cs > 1) {
+        cluster_wait();
+        tc_push(sc + rank * slot, slot, cs, rank);
+        cluster_sync_all();
+    }
     attn_ts(2);
-    tc_softmax(sc, S, SP, a.scale, a.causal);
+    tc_softmax<CS>(sc, slot, S, SP, a.scale, a.causal);
     __syncthreads();
     attn_ts(3);
     {
         const CounterRng rng(a.seed);
         const uint32_t thr = static_cast<uint32_t>(fminf(a.drop_p, 0.999999f) * 4294967296.0f);
         const float inv_keep = a.drop_p > 0.f ? 1.f / (1.f - a.drop_p) : 1.f;
-        for (int p = threadIdx.x; p < SP * SP; p += blockDim.x) {
-            const int i = p / SP, j = p % SP;
-            float w = sc[i * cpad + j];
-            if (i < S && j < S) w *= tc_keep(rng, a, thr, inv_keep, n, h, i, j);
-            pb[i * cpad + j] = __float2bfloat16(w);
+        // a thread keeps its column and walks rows: no division in the loop
+        const int rows_per_pass = kTcThreads / SP > 0 ? kTcThreads / SP : 1;
+        if (SP <= kTcThreads) {
+            const int j = threadIdx.x % SP;
+            for (int i = threadIdx.x / SP; i < SP; i += rows_per_pass) {
+                float w = sc[i * cpad + j];
+                if (i < S && j < S) w *= tc_keep(rng, a, thr, inv_keep, n, h, i, j);
+                pb[i * cpad + j] = __float2bfloat16(w);
+            }
         }
     }
     __syncthreads();
     attn_ts(4);
 
-    // O = P V: each warp keeps up to four output tiles in flight (independent accumulators)
-    const int warp = threadIdx.x >> 5, rt = SP / 16, ct = D / 16, total = rt * ct;
+    // O[:, own columns] = P V: each warp keeps up to four output tiles in flight (independent accumulators)
+    const int warp = threadIdx.x >> 5, rt = SP / 16, ct = Dc / 16, total = rt * ct;
+    const size_t row_stride = static_cast<size_t>(a.NB) * a.E;
     for (int t0 = warp; t0 < total; t0 += kTcWarps * 4) {
         FragC acc[4];
+        int ti[4], tc[4];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) wmma::fill_fragment(acc[u], 0.f);
+        for (int u = 0; u < 4; ++u) {
+            wmma::fill_fragment(acc[u], 0.f);
+            const int t = t0 + u * kTcWarps;
+            ti[u] = t / ct;
+            tc[u] = t - ti[u] * ct;
+        }
         for (int kk = 0; kk < SP; kk += 16) {
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
-                const int t = t0 + u * kTcWarps;
-                if (t < total) {
+                if (t0 + u * kTcWarps < total) {
                     FragA pa;
                     FragB vb;
-                    wmma::load_matrix_sync(pa, pb + (t / ct) * 16 * cpad + kk, cpad);
-                    wmma::load_matrix_sync(vb, v + kk * dpad + (t % ct) * 16, dpad);
+                    wmma::load_matrix_sync(pa, pb + ti[u] * 16 * cpad + kk, cpad);
+                    wmma::load_matrix_sync(vb, v + kk * dpad + tc[u] * 16, dpad);
                     wmma::mma_sync(acc[u], pa, vb, acc[u]);
                 }
             }
         }
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
-            const int t = t0 + u * kTcWarps;
-            if (t < total) {
-                const int ti = t / ct, tc = t % ct;
+            if (t0 + u * kTcWarps < total) {
                 wmma::store_matrix_sync(stage, acc[u], 24, wmma::mem_row_major);
                 __syncwarp();
-                tc_emit_tile(stage, out + (static_cast<size_t>(ti * 16) * a.NB + n) * a.E + h * D + tc * 16, a.E, a.NB,
-                             ti * 16, S);
+                tc_emit_tile(stage, out + (static_cast<size_t>(ti[u] * 16) * a.NB + n) * a.E + col0 + tc[u] * 16, row_stride,
+                             ti[u] * 16, S);
                 __syncwarp();
             }
         }
@@ -244,36 +315,51 @@ attn_tc_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restr
     attn_ts(5);
 }
 
+template <int CS>
 __global__ void __launch_bounds__(kTcThreads)
 attn_tc_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* __restrict__ dout,
                    __nv_bfloat16* __restrict__ dqkv, const AttnTc a) {
     pdl_launch_dependents();
+    attn_ts(8);
+    constexpr int cs = CS;
+    const uint32_t rank = cs > 1 ? cluster_ctarank() : 0u;
+    if (cs > 1) cluster_arrive();
     extern __shared__ __align__(128) uint8_t smem[];
-    const int S = a.S, SP = a.SP, D = a.D, dpad = D + 8, cpad = SP + 8;
+    const int S = a.S, SP = a.SP, Dc = a.Dc, dpad = Dc + 8, cpad = SP + 8, slot = SP * cpad;
     __nv_bfloat16* q = reinterpret_cast<__nv_bfloat16*>(smem);
     __nv_bfloat16* k = q + SP * dpad;
     __nv_bfloat16* v = k + SP * dpad;
     __nv_bfloat16* dO = v + SP * dpad;
-    float* P = reinterpret_cast<float*>(dO + SP * dpad);
-    float* dP = P + SP * cpad;
+    float* P = reinterpret_cast<float*>(dO + SP * dpad);       // cs partial score matrices, then the probabilities in the first
+    float* dP = P + cs * slot;                                 // cs partial dO V^T matrices
     // The bf16 matrices the last three products read are written over the fp32 rows they are derived
     // from (same row pitch in bytes, so bpad = 2 * cpad bf16 elements): S = 128 with D = 64 then
     // fits the 227 KB of shared memory.
     __nv_bfloat16* Pd = reinterpret_cast<__nv_bfloat16*>(P);                  // dropped-out probabilities
     __nv_bfloat16* dS = reinterpret_cast<__nv_bfloat16*>(dP);                 // score gradients
     const int bpad = 2 * cpad;
-    float* stage = dP + SP * cpad + (threadIdx.x >> 5) * (16 * 24);
-    const int n = blockIdx.x / a.H, h = blockIdx.x % a.H;
+    float* stage = dP + cs * slot + (threadIdx.x >> 5) * (16 * 24);
+    const int pair = blockIdx.x / cs;
+    const int n = pair / a.H, h = pair - n * a.H;
     const long long ld = 3LL * a.E;
+    const int col0 = h * a.D + static_cast<int>(rank) * Dc;
 
-    tc_gather(qkv + h * D, qkv + a.E + h * D, qkv + 2 * a.E + h * D, dout + h * D, ld, a.E, q, k, v, dO, 4, a.NB, S, SP,
-              D, n);
+    tc_gather(qkv + col0, qkv + a.E + col0, qkv + 2 * a.E + col0, dout + col0, ld, a.E, q, k, v, dO, 4, a.NB, S, SP, Dc, n);
     __syncthreads();
-    tc_abt(q, k, P, SP, D);          // raw scores
-    tc_abt(dO, v, dP, SP, D);        // gradient w.r.t. the dropped-out probabilities
+    attn_ts(9);
+    // raw scores and the gradient w.r.t. the dropped-out probabilities (partial over this CTA's columns)
+    tc_abt(q, k, P + rank * slot, dO, v, dP + rank * slot, SP, Dc);
     __syncthreads();
-    tc_softmax(P, S, SP, a.scale, a.causal);
+    if (cs > 1) {
+        cluster_wait();
+        tc_push(P + rank * slot, slot, cs, rank);
+        tc_push(dP + rank * slot, slot, cs, rank);
+        cluster_sync_all();
+    }
+    attn_ts(10);
+    tc_softmax<CS>(P, slot, S, SP, a.scale, a.causal);
     __syncthreads();
+    attn_ts(11);
 
     // per row (8 lanes each): Pd = P * keep,  dPm = dP * keep,  delta = sum_j dPm * P,  dS = P * (dPm - delta) * scale
     {
@@ -294,7 +380,10 @@ attn_tc_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* _
                     p[u] = P[i * cpad + j];
                     float ks = 0.f;
                     if (i < S && j < S) ks = tc_keep(rng, a, thr, inv_keep, n, h, i, j);
-                    dpm[u] = dP[i * cpad + j] * ks;
+                    float g = dP[i * cpad + j];
+#pragma unroll
+                    for (int s = 1; s < CS; ++s) g += dP[s * slot + i * cpad + j];
+                    dpm[u] = g * ks;
                     dlt += dpm[u] * p[u];
                     keepv[u] = ks;
                 }
@@ -314,29 +403,37 @@ attn_tc_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* _
         }
     }
     __syncthreads();
+    attn_ts(12);
 
-    // dV = Pd^T dO,  dQ = dS K,  dK = dS^T Q  — 3 x (SP/16) x (D/16) output tiles, four in flight per warp
-    const int warp = threadIdx.x >> 5, rt = SP / 16, ct = D / 16, per = rt * ct, total = 3 * per;
+    // dV = Pd^T dO,  dQ = dS K,  dK = dS^T Q  (own columns) — 3 x (SP/16) x (Dc/16) output tiles, four in flight per warp
+    const int warp = threadIdx.x >> 5, rt = SP / 16, ct = Dc / 16, per = rt * ct, total = 3 * per;
+    const size_t row_stride = static_cast<size_t>(a.NB) * ld;
     for (int t0 = warp; t0 < total; t0 += kTcWarps * 4) {
         FragC acc[4];
+        int which[4], ti[4], tc[4];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) wmma::fill_fragment(acc[u], 0.f);
+        for (int u = 0; u < 4; ++u) {
+            wmma::fill_fragment(acc[u], 0.f);
+            const int t = t0 + u * kTcWarps;
+            which[u] = (t >= per) + (t >= 2 * per);
+            const int r = t - which[u] * per;
+            ti[u] = r / ct;
+            tc[u] = r - ti[u] * ct;
+        }
         for (int kk = 0; kk < SP; kk += 16) {
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
-                const int t = t0 + u * kTcWarps;
-                if (t < total) {
-                    const int which = t / per, r = t % per, ti = r / ct, tc = r % ct;
+                if (t0 + u * kTcWarps < total) {
                     FragB bm;
-                    if (which == 1) {            // dQ: A = dS (row-major), B = K
+                    if (which[u] == 1) {         // dQ: A = dS (row-major), B = K
                         FragA am;
-                        wmma::load_matrix_sync(am, dS + ti * 16 * bpad + kk, bpad);
-                        wmma::load_matrix_sync(bm, k + kk * dpad + tc * 16, dpad);
+                        wmma::load_matrix_sync(am, dS + ti[u] * 16 * bpad + kk, bpad);
+                        wmma::load_matrix_sync(bm, k + kk * dpad + tc[u] * 16, dpad);
                         wmma::mma_sync(acc[u], am, bm, acc[u]);
                     } else {                     // dV: A = Pd^T, B = dO;  dK: A = dS^T, B = Q
                         FragAT at;
-                        wmma::load_matrix_sync(at, (which == 0 ? Pd : dS) + kk * bpad + ti * 16, bpad);
-                        wmma::load_matrix_sync(bm, (which == 0 ? dO : q) + kk * dpad + tc * 16, dpad);
+                        wmma::load_matrix_sync(at, (which[u] == 0 ? Pd : dS) + kk * bpad + ti[u] * 16, bpad);
+                        wmma::load_matrix_sync(bm, (which[u] == 0 ? dO : q) + kk * dpad + tc[u] * 16, dpad);
                         wmma::mma_sync(acc[u], at, bm, acc[u]);
                     }
                 }
@@ -344,23 +441,23 @@ attn_tc_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* _
         }
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
-            const int t = t0 + u * kTcWarps;
-            if (t < total) {
-                const int which = t / per, r = t % per, ti = r / ct, tc = r % ct;
+            if (t0 + u * kTcWarps < total) {
                 wmma::store_matrix_sync(stage, acc[u], 24, wmma::mem_row_major);
                 __syncwarp();
-                const int col0 = (which == 0 ? 2 * a.E : which == 1 ? 0 : a.E) + h * D + tc * 16;
-                tc_emit_tile(stage, dqkv + (static_cast<size_t>(ti * 16) * a.NB + n) * ld + col0, ld, a.NB, ti * 16, S);
+                const int c = (which[u] == 0 ? 2 * a.E : which[u] == 1 ? 0 : a.E) + col0 + tc[u] * 16;
+                tc_emit_tile(stage, dqkv + (static_cast<size_t>(ti[u] * 16) * a.NB + n) * ld + c, row_stride, ti[u] * 16, S);
                 __syncwarp();
             }
         }
     }
+    attn_ts(13);
 }
 
-size_t attn_tc_smem(int SP, int D, bool bwd) {
-    const size_t dpad = D + 8, cpad = SP + 8;
-    size_t b = (bwd ? 4 : 3) * SP * dpad * 2;             // Q K V (dO)
-    b += (bwd ? 2 : 1) * SP * cpad * 4;                    // fp32 score matrices (backward: bf16 copies alias them)
+size_t attn_tc_smem(int SP, int Dc, int cs, bool bwd) {
+    const size_t dpad = Dc + 8, cpad = SP + 8;
+    size_t b = (bwd ? 4 : 3) * SP * dpad * 2;             // Q K V (dO), this CTA's columns
+    b += (bwd ? 2 : 1) * cs * SP * cpad * 4;               // fp32 partial score matrices, one per cluster rank
+                                                           // (backward: the bf16 copies alias the first)
     if (!bwd) b += SP * cpad * 2;                          // forward: bf16 probabilities
     b += kTcWarps * 16 * 24 * 4;                           // per-warp output staging
     return b + 128;
@@ -369,17 +466,66 @@ size_t attn_tc_smem(int SP, int D, bool bwd) {
 bool attn_tc_supported(int S, int D) {
     if (S > 128 || D % 16 != 0 || D > 256) return false;
     const int SP = (S + 15) / 16 * 16;
-    return attn_tc_smem(SP, D, true) <= 227 * 1024;        // e.g. S = 128 needs D <= 64; S <= 64 any D <= 256
+    return attn_tc_smem(SP, D, 1, true) <= 227 * 1024;     // e.g. S = 128 needs D <= 64; S <= 64 any D <= 256
+}
+
+// CTAs per (sequence, head).  Splitting pays while the launch is smaller than the machine: the
+// per-head work is issue-bound, and the extra cost is one DSMEM exchange of the S x S partials.
+// PB2_ATTN_CLUSTER=1|2|4 overrides (for tests and measurements).
+static int g_attn_cluster_forced = -1;
+static int attn_tc_cluster(int NB, int H, int SP, int D, bool bwd) {
+    int& forced = g_attn_cluster_forced;
+    if (forced < 0) {
+        const char* e = getenv("PB2_ATTN_CLUSTER");
+        forced = e ? atoi(e) : 0;
+    }
+    if (forced == 1) return 1;
+    const int cands[2] = {4, 2};
+    for (int c : cands) {
+        if (forced && c != forced) continue;
+        if (D % (16 * c) != 0 || D / c < 32) continue;
+        if (attn_tc_smem(SP, D / c, c, bwd) > 96 * 1024) continue;
+        if (!forced && static_cast<long long>(NB) * H * c > 2 * 148) continue;
+        return c;
+    }
+    return 1;
+}
+
+static int attn_tc_launch(const void* kernel, size_t smem, int ctas, int cs, void** args, cudaStream_t stream) {
+    if (ensure_max_smem(kernel, 227 * 1024)) return -1;
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3(ctas);
+    cfg.blockDim = dim3(kTcThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    if (cs > 1) {
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = cs;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+    }
+    PB2_CUDA(cudaLaunchKernelExC(&cfg, kernel, args));
+    return 0;
 }
 
 int attn_tc_fwd(const void* qkv, void* out, int NB, int S, int H, int D, int causal, float drop_p,
                 unsigned long long seed, unsigned long long rng_stream, cudaStream_t stream) {
     const int SP = (S + 15) / 16 * 16;
-    AttnTc a{NB, S, H, D, H * D, SP, 1.f / sqrtf(static_cast<float>(D)), causal, drop_p, seed, rng_stream};
-    const size_t smem = attn_tc_smem(SP, D, false);
-    if (ensure_max_smem(reinterpret_cast<const void*>(attn_tc_fwd_kernel), 227 * 1024)) return -1;
-    attn_tc_fwd_kernel<<<NB * H, kTcThreads, smem, stream>>>(static_cast<const __nv_bfloat16*>(qkv),
-                                                             static_cast<__nv_bfloat16*>(out), a);
+    const int cs = attn_tc_cluster(NB, H, SP, D, false);
+    AttnTc a{NB, S, H, D, H * D, SP, 1.f / sqrtf(static_cast<float>(D)), causal, drop_p, seed, rng_stream, cs, D / cs};
+    const __nv_bfloat16* qp = static_cast<const __nv_bfloat16*>(qkv);
+    __nv_bfloat16* op = static_cast<__nv_bfloat16*>(out);
+    void* args[] = {&qp, &op, &a};
+    const void* kern = cs == 4 ? reinterpret_cast<const void*>(attn_tc_fwd_kernel<4>)
+                     : cs == 2 ? reinterpret_cast<const void*>(attn_tc_fwd_kernel<2>)
+                               : reinterpret_cast<const void*>(attn_tc_fwd_kernel<1>);
+    if (attn_tc_launch(kern, attn_tc_smem(SP, D / cs, cs, false), NB * H * cs, cs,
+                       args, stream))
+        return -1;
     PB2_LAUNCHED("attn_tc_fwd_kernel");
     return 0;
 }
@@ -387,17 +533,26 @@ int attn_tc_fwd(const void* qkv, void* out, int NB, int S, int H, int D, int cau
 int attn_tc_bwd(const void* qkv, const void* dout, void* dqkv, int NB, int S, int H, int D, int causal, float drop_p,
                 unsigned long long seed, unsigned long long rng_stream, cudaStream_t stream) {
     const int SP = (S + 15) / 16 * 16;
-    AttnTc a{NB, S, H, D, H * D, SP, 1.f / sqrtf(static_cast<float>(D)), causal, drop_p, seed, rng_stream};
-    const size_t smem = attn_tc_smem(SP, D, true);
-    if (ensure_max_smem(reinterpret_cast<const void*>(attn_tc_bwd_kernel), 227 * 1024)) return -1;
-    attn_tc_bwd_kernel<<<NB * H, kTcThreads, smem, stream>>>(static_cast<const __nv_bfloat16*>(qkv),
-                                                             static_cast<const __nv_bfloat16*>(dout),
-                                                             static_cast<__nv_bfloat16*>(dqkv), a);
+    const int cs = attn_tc_cluster(NB, H, SP, D, true);
+    AttnTc a{NB, S, H, D, H * D, SP, 1.f / sqrtf(static_cast<float>(D)), causal, drop_p, seed, rng_stream, cs, D / cs};
+    const __nv_bfloat16* qp = static_cast<const __nv_bfloat16*>(qkv);
+    const __nv_bfloat16* dp = static_cast<const __nv_bfloat16*>(dout);
+    __nv_bfloat16* gp = static_cast<__nv_bfloat16*>(dqkv);
+    void* args[] = {&qp, &dp, &gp, &a};
+    const void* kern = cs == 4 ? reinterpret_cast<const void*>(attn_tc_bwd_kernel<4>)
+                     : cs == 2 ? reinterpret_cast<const void*>(attn_tc_bwd_kernel<2>)
+                               : reinterpret_cast<const void*>(attn_tc_bwd_kernel<1>);
+    if (attn_tc_launch(kern, attn_tc_smem(SP, D / cs, cs, true), NB * H * cs, cs,
+                       args, stream))
+        return -1;
     PB2_LAUNCHED("attn_tc_bwd_kernel");
     return 0;
 }
 
 }  // namespace pb2
+
+// Debug hook (not part of the supported ABI): force the CTAs per head (1, 2, 4; 0 = choose).
+extern "C" void pb2_debug_attn_cluster(int cs) { pb2::g_attn_cluster_forced = cs; }
 
 extern "C" int pb2_debug_attn_timestamps(unsigned long long* out16) {
     return cudaMemcpyFromSymbol(out16, pb2::g_attn_ts, sizeof(unsigned long long) * 16) == cudaSuccess ? 0 : -1;

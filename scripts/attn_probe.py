@@ -23,6 +23,10 @@ def t(NB, S, H, D, p):
     ts = (ctypes.c_ulonglong * 16)()
     _lib.load().pb2_debug_attn_timestamps(ts)
     print("   fwd phases (us): gather %.2f  QK^T %.2f  softmax %.2f  dropout %.2f  PV+emit %.2f" % tuple((ts[i + 1] - ts[i]) / 1e3 for i in range(5)))
+    F2.attention_bwd(qkv, dout, NB, S, H, causal=False, drop_p=p, seed=1, rng_stream=0)
+    torch.cuda.synchronize()
+    _lib.load().pb2_debug_attn_timestamps(ts)
+    print("   bwd phases (us): gather %.2f  QK^T+dOV^T %.2f  softmax %.2f  dS %.2f  3 products+emit %.2f" % tuple((ts[i + 1] - ts[i]) / 1e3 for i in range(8, 13)))
     print(f"NB={NB} S={S} H={H} D={D} p={p}: fwd {f[len(f)//2]:.1f} us  bwd {b[len(b)//2]:.1f} us  ctas={NB*H}", flush=True)
 t(3, 25, 16, 256, 0.2)
 t(3, 25, 16, 256, 0.0)

@@ -153,6 +153,38 @@ def test_attention_fwd_bwd(NB, S, H, D, causal):
     dqkv = F2.attention_bwd(qkv, dout, NB, S, H, causal=causal, drop_p=0.0, seed=0, rng_stream=0)
     close(dqkv, ref.grad, 3e-2)
 
+@pytest.mark.parametrize("cs", [1, 2, 4])
+@pytest.mark.parametrize("NB,S,H,D,causal", [(3, 25, 16, 256, False), (2, 40, 4, 128, True), (5, 16, 2, 64, False)])
+def test_attention_head_split_across_cluster(cs, NB, S, H, D, causal):
+    """1, 2 or 4 CTAs per (sequence, head) — partial scores exchanged through DSMEM — agree with the
+    fp32 reference, and produce the same dropout mask as the unsplit kernel."""
+    from pipe_b200.ops import _lib, functional as F2
+    lib = _lib.load()
+    E = H * D
+    torch.manual_seed(cs)
+    qkv = (torch.randn(S * NB, 3 * E, device=dev) * 0.5).bfloat16()
+    dout = torch.randn(S * NB, E, device=dev).bfloat16()
+    try:
+        lib.pb2_debug_attn_cluster(cs)
+        out = F2.attention_fwd(qkv, NB, S, H, causal=causal, drop_p=0.0, seed=0, rng_stream=0)
+        dqkv = F2.attention_bwd(qkv, dout, NB, S, H, causal=causal, drop_p=0.0, seed=0, rng_stream=0)
+        out_d = F2.attention_fwd(qkv, NB, S, H, causal=causal, drop_p=0.3, seed=7, rng_stream=1)
+        dqkv_d = F2.attention_bwd(qkv, dout, NB, S, H, causal=causal, drop_p=0.3, seed=7, rng_stream=1)
+        lib.pb2_debug_attn_cluster(1)
+        out_1 = F2.attention_fwd(qkv, NB, S, H, causal=causal, drop_p=0.3, seed=7, rng_stream=1)
+        dqkv_1 = F2.attention_bwd(qkv, dout, NB, S, H, causal=causal, drop_p=0.3, seed=7, rng_stream=1)
+    finally:
+        lib.pb2_debug_attn_cluster(0)
+    ref = qkv.float().requires_grad_()
+    t = ref.view(S, NB, 3, H, D)
+    q, k, v = (t[:, :, i].permute(1, 2, 0, 3) for i in range(3))
+    want = F.scaled_dot_product_attention(q, k, v, is_causal=causal).permute(2, 0, 1, 3).reshape(S * NB, E)
+    close(out, want)
+    want.backward(dout.float())
+    close(dqkv, ref.grad, 3e-2)
+    close(out_d, out_1.float(), 2e-2)
+    close(dqkv_d, dqkv_1.float(), 3e-2)
+
 
 def test_attention_dropout_consistent_between_fwd_and_bwd():
     """Finite-difference-free check: with dropout on, d(sum(out * g))/dV computed by the backward
