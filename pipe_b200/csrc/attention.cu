@@ -123,6 +123,7 @@ __device__ __forceinline__ float keep_scale(const CounterRng& ph, const AttnShap
 __global__ void __launch_bounds__(kAttnThreads)
 attn_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out, const AttnShape a) {
     pdl_launch_dependents();
+    pdl_wait();          // launched programmatically: nothing below may run before the predecessor is complete
     extern __shared__ __align__(16) uint8_t smem[];
     const int S = a.S, D = a.D, dpad = D + 2, spad = S + 1;   // odd word stride: lanes on different rows hit different banks
     __nv_bfloat16* q = reinterpret_cast<__nv_bfloat16*>(smem);
@@ -185,6 +186,7 @@ __global__ void __launch_bounds__(kAttnThreads)
 attn_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* __restrict__ dout,
                 __nv_bfloat16* __restrict__ dqkv, const AttnShape a) {
     pdl_launch_dependents();
+    pdl_wait();          // launched programmatically: nothing below may run before the predecessor is complete
     extern __shared__ __align__(16) uint8_t smem[];
     const int S = a.S, D = a.D, dpad = D + 2, spad = S + 1;   // odd word stride: lanes on different rows hit different banks
     __nv_bfloat16* q = reinterpret_cast<__nv_bfloat16*>(smem);
@@ -308,8 +310,8 @@ extern "C" int pb2_attention_fwd(const void* qkv, void* out, int NB, int S, int 
         return attn_tc_fwd(qkv, out, NB, S, H, D, causal, drop_p, seed, rng_stream, stream);
     AttnShape a{NB, S, H, D, H * D, 1.f / sqrtf(static_cast<float>(D)), causal, drop_p, seed, rng_stream};
     if (ensure_max_smem(reinterpret_cast<const void*>(attn_fwd_kernel), 227 * 1024)) return -1;
-    attn_fwd_kernel<<<NB * H, kAttnThreads, smem, stream>>>(static_cast<const __nv_bfloat16*>(qkv),
-                                                            static_cast<__nv_bfloat16*>(out), a);
+    PB2_CUDA(launch_pdl(attn_fwd_kernel, dim3(NB * H), dim3(kAttnThreads), smem, stream, static_cast<const __nv_bfloat16*>(qkv),
+                                                            static_cast<__nv_bfloat16*>(out), a));
     PB2_LAUNCHED("attn_fwd_kernel");
     return 0;
 }
@@ -323,9 +325,9 @@ extern "C" int pb2_attention_bwd(const void* qkv, const void* dout, void* dqkv, 
         return attn_tc_bwd(qkv, dout, dqkv, NB, S, H, D, causal, drop_p, seed, rng_stream, stream);
     AttnShape a{NB, S, H, D, H * D, 1.f / sqrtf(static_cast<float>(D)), causal, drop_p, seed, rng_stream};
     if (ensure_max_smem(reinterpret_cast<const void*>(attn_bwd_kernel), 227 * 1024)) return -1;
-    attn_bwd_kernel<<<NB * H, kAttnThreads, smem, stream>>>(static_cast<const __nv_bfloat16*>(qkv),
+    PB2_CUDA(launch_pdl(attn_bwd_kernel, dim3(NB * H), dim3(kAttnThreads), smem, stream, static_cast<const __nv_bfloat16*>(qkv),
                                                             static_cast<const __nv_bfloat16*>(dout),
-                                                            static_cast<__nv_bfloat16*>(dqkv), a);
+                                                            static_cast<__nv_bfloat16*>(dqkv), a));
     PB2_LAUNCHED("attn_bwd_kernel");
     return 0;
 }

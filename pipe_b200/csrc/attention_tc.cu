@@ -227,6 +227,7 @@ template <int CS>
 __global__ void __launch_bounds__(kTcThreads)
 attn_tc_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out, const AttnTc a) {
     pdl_launch_dependents();
+    pdl_wait();          // launched programmatically: nothing below may run before the predecessor is complete
     attn_ts(0);
     constexpr int cs = CS;
     const uint32_t rank = cs > 1 ? cluster_ctarank() : 0u;
@@ -320,6 +321,7 @@ __global__ void __launch_bounds__(kTcThreads)
 attn_tc_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* __restrict__ dout,
                    __nv_bfloat16* __restrict__ dqkv, const AttnTc a) {
     pdl_launch_dependents();
+    pdl_wait();          // launched programmatically: nothing below may run before the predecessor is complete
     attn_ts(8);
     constexpr int cs = CS;
     const uint32_t rank = cs > 1 ? cluster_ctarank() : 0u;
@@ -499,15 +501,22 @@ static int attn_tc_launch(const void* kernel, size_t smem, int ctas, int cs, voi
     cfg.blockDim = dim3(kTcThreads);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    if (cs > 1) {
-        attr[0].id = cudaLaunchAttributeClusterDimension;
-        attr[0].val.clusterDim.x = cs;
-        attr[0].val.clusterDim.y = 1;
-        attr[0].val.clusterDim.z = 1;
-        cfg.attrs = attr;
-        cfg.numAttrs = 1;
+    cudaLaunchAttribute attr[2];
+    int n_attr = 0;
+    if (pdl_enabled()) {
+        attr[n_attr].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[n_attr].val.programmaticStreamSerializationAllowed = 1;
+        ++n_attr;
     }
+    if (cs > 1) {
+        attr[n_attr].id = cudaLaunchAttributeClusterDimension;
+        attr[n_attr].val.clusterDim.x = cs;
+        attr[n_attr].val.clusterDim.y = 1;
+        attr[n_attr].val.clusterDim.z = 1;
+        ++n_attr;
+    }
+    cfg.attrs = attr;
+    cfg.numAttrs = n_attr;
     PB2_CUDA(cudaLaunchKernelExC(&cfg, kernel, args));
     return 0;
 }

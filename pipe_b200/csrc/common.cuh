@@ -9,6 +9,7 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <string.h>
 
 #include <atomic>
 
@@ -31,6 +32,30 @@ int check_cuda(cudaError_t e, const char* what); // 0 on success, else sets erro
         pb2::g_launches.fetch_add(1, std::memory_order_relaxed);   \
         if (pb2::check_cuda(cudaGetLastError(), name)) return -1;  \
     } while (0)
+
+// Launch with programmatic stream serialization (programmatic dependent launch): the grid may be
+// scheduled while its predecessor on the stream is still running, and must execute
+// griddepcontrol.wait (pdl_wait()) before it touches anything the predecessor reads or writes.
+// Every kernel of this library that is launched this way waits first thing, so all it saves is the
+// launch latency between dependent kernels (1.5 - 2.5 us each, ~900 times per training step).
+// PB2_NO_PDL=1 in the environment falls back to plain launches.
+bool pdl_enabled();
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
 
 // Driver entry point for tensor-map encoding, fetched through the runtime so the
 // library does not link against libcuda directly.

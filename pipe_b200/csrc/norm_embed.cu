@@ -77,6 +77,7 @@ add_ln_fwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __re
                   const float* __restrict__ gamma, const float* __restrict__ beta, __nv_bfloat16* __restrict__ y,
                   float* __restrict__ mean_out, float* __restrict__ rstd_out, int E, float eps) {
     pdl_launch_dependents();
+    pdl_wait();          // launched programmatically: nothing below may run before the predecessor is complete
     __shared__ float red[32];
     const size_t row = blockIdx.x;
     const __nv_bfloat16* xr = x + row * E;
@@ -146,6 +147,7 @@ add_ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __r
                   float* __restrict__ dbeta, int E, float drop_p, unsigned long long seed,
                   unsigned long long rng_stream) {
     pdl_launch_dependents();
+    pdl_wait();          // launched programmatically: nothing below may run before the predecessor is complete
     __shared__ float red[32];
     const size_t row = blockIdx.x;
     const float mean = mean_in[row], rstd = rstd_in[row];
@@ -221,6 +223,7 @@ embed_fwd_kernel(const long long* __restrict__ tokens, const float* __restrict__
                  const float* __restrict__ pe, __nv_bfloat16* __restrict__ out, int N, int S, int E, float scale,
                  float drop_p, unsigned long long seed, unsigned long long rng_stream) {
     pdl_launch_dependents();
+    pdl_wait();          // launched programmatically: nothing below may run before the predecessor is complete
     const int row = blockIdx.x;            // row = s * N + n
     const int s = row / N, n = row % N;
     const long long tok = tokens[static_cast<size_t>(n) * S + s];
@@ -251,6 +254,7 @@ embed_bwd_kernel(const long long* __restrict__ tokens, const __nv_bfloat16* __re
                  float* __restrict__ dweight, int N, int S, int E, float scale, float drop_p,
                  unsigned long long seed, unsigned long long rng_stream) {
     pdl_launch_dependents();
+    pdl_wait();          // launched programmatically: nothing below may run before the predecessor is complete
     const int row = blockIdx.x;
     const int s = row / N, n = row % N;
     const long long tok = tokens[static_cast<size_t>(n) * S + s];
@@ -283,6 +287,7 @@ ce_fwd_bwd_kernel(__nv_bfloat16* __restrict__ logits, const long long* __restric
                   float* __restrict__ loss_rows, const float* __restrict__ row_scale, int V, long long ld,
                   int write_grad) {
     pdl_launch_dependents();
+    pdl_wait();          // launched programmatically: nothing below may run before the predecessor is complete
     __shared__ float red[32];
     const size_t row = blockIdx.x;
     __nv_bfloat16* l = logits + row * ld;
@@ -315,6 +320,7 @@ __global__ void __launch_bounds__(256)
 transpose_colsum_kernel(const __nv_bfloat16* __restrict__ src, long long ld_src, __nv_bfloat16* __restrict__ dst,
                         long long ld_dst, int R, int C, float* __restrict__ colsum, float scale) {
     pdl_launch_dependents();
+    pdl_wait();          // launched programmatically: nothing below may run before the predecessor is complete
     __shared__ __nv_bfloat16 tile[32][33];
     const int c0 = blockIdx.x * 32;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;      // 32 x 8
@@ -355,6 +361,7 @@ transpose_colsum_kernel(const __nv_bfloat16* __restrict__ src, long long ld_src,
 __global__ void __launch_bounds__(256)
 transpose_multi_kernel(const pb2_transpose_jobs jobs) {
     pdl_launch_dependents();
+    pdl_wait();          // launched programmatically: nothing below may run before the predecessor is complete
     const pb2_transpose_job j = jobs.job[blockIdx.y];
     if (blockIdx.x * 32 >= j.C) return;
     __shared__ __nv_bfloat16 tile[32][33];
@@ -414,6 +421,7 @@ l2_prefetch_kernel(const char* __restrict__ base, size_t bytes) {
 
 __global__ void __launch_bounds__(256)
 sumsq_kernel(const float* __restrict__ x, size_t n, float* __restrict__ out) {
+    pdl_wait();          // launched programmatically; it does not release its own dependents early (the optimizer follows)
     __shared__ float red[32];
     float s = 0.f;
     const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x * 4;
@@ -445,9 +453,9 @@ extern "C" int pb2_add_layernorm_fwd(const void* x, const void* h, const float* 
                                      float* mean, float* rstd, int rows, int E, float eps, cudaStream_t stream) {
     if (check_e("pb2_add_layernorm_fwd", E)) return -1;
     if (rows <= 0) return 0;
-    add_ln_fwd_kernel<<<rows, kLnThreads, 0, stream>>>(static_cast<const __nv_bfloat16*>(x),
+    PB2_CUDA(launch_pdl(add_ln_fwd_kernel, dim3(rows), dim3(kLnThreads), 0, stream, static_cast<const __nv_bfloat16*>(x),
                                                        static_cast<const __nv_bfloat16*>(h), gamma, beta,
-                                                       static_cast<__nv_bfloat16*>(y), mean, rstd, E, eps);
+                                                       static_cast<__nv_bfloat16*>(y), mean, rstd, E, eps));
     PB2_LAUNCHED("add_ln_fwd_kernel");
     return 0;
 }
@@ -458,10 +466,10 @@ extern "C" int pb2_add_layernorm_bwd(const void* dy, const void* x, const void* 
                                      unsigned long long rng_stream, cudaStream_t stream) {
     if (check_e("pb2_add_layernorm_bwd", E)) return -1;
     if (rows <= 0) return 0;
-    add_ln_bwd_kernel<<<rows, kLnThreads, 0, stream>>>(
+    PB2_CUDA(launch_pdl(add_ln_bwd_kernel, dim3(rows), dim3(kLnThreads), 0, stream, 
         static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x),
         static_cast<const __nv_bfloat16*>(h), gamma, mean, rstd, static_cast<__nv_bfloat16*>(dres),
-        static_cast<__nv_bfloat16*>(dh), dgamma, dbeta, E, drop_p, seed, rng_stream);
+        static_cast<__nv_bfloat16*>(dh), dgamma, dbeta, E, drop_p, seed, rng_stream));
     PB2_LAUNCHED("add_ln_bwd_kernel");
     return 0;
 }
@@ -471,8 +479,8 @@ extern "C" int pb2_embed_fwd(const long long* tokens, const float* weight, const
                              unsigned long long rng_stream, cudaStream_t stream) {
     if (E % 4) { set_error("pb2_embed_fwd: E must be a multiple of 4"); return -1; }
     if (N * S <= 0) return 0;
-    embed_fwd_kernel<<<N * S, 256, 0, stream>>>(tokens, weight, pe, static_cast<__nv_bfloat16*>(out), N, S, E, scale,
-                                                drop_p, seed, rng_stream);
+    PB2_CUDA(launch_pdl(embed_fwd_kernel, dim3(N * S), dim3(256), 0, stream, tokens, weight, pe, static_cast<__nv_bfloat16*>(out), N, S, E, scale,
+                                                drop_p, seed, rng_stream));
     PB2_LAUNCHED("embed_fwd_kernel");
     return 0;
 }
@@ -482,8 +490,8 @@ extern "C" int pb2_embed_bwd(const long long* tokens, const void* dout, float* d
                              cudaStream_t stream) {
     if (E % 4) { set_error("pb2_embed_bwd: E must be a multiple of 4"); return -1; }
     if (N * S <= 0) return 0;
-    embed_bwd_kernel<<<N * S, 256, 0, stream>>>(tokens, static_cast<const __nv_bfloat16*>(dout), dweight, N, S, E,
-                                                scale, drop_p, seed, rng_stream);
+    PB2_CUDA(launch_pdl(embed_bwd_kernel, dim3(N * S), dim3(256), 0, stream, tokens, static_cast<const __nv_bfloat16*>(dout), dweight, N, S, E,
+                                                scale, drop_p, seed, rng_stream));
     PB2_LAUNCHED("embed_bwd_kernel");
     return 0;
 }
@@ -492,8 +500,8 @@ extern "C" int pb2_cross_entropy(void* logits, const long long* targets, float* 
                                  int rows, int V, long long ld, int write_grad, cudaStream_t stream) {
     if (rows <= 0) return 0;
     if (V <= 0 || ld < V) { set_error("pb2_cross_entropy: bad V/ld (%d / %lld)", V, ld); return -1; }
-    ce_fwd_bwd_kernel<<<rows, 512, 0, stream>>>(static_cast<__nv_bfloat16*>(logits), targets, loss_rows, row_scale, V,
-                                                ld, write_grad);
+    PB2_CUDA(launch_pdl(ce_fwd_bwd_kernel, dim3(rows), dim3(512), 0, stream, static_cast<__nv_bfloat16*>(logits), targets, loss_rows, row_scale, V,
+                                                ld, write_grad));
     PB2_LAUNCHED("ce_fwd_bwd_kernel");
     return 0;
 }
@@ -502,9 +510,9 @@ extern "C" int pb2_transpose_colsum(const void* src, long long ld_src, void* dst
                                     float* colsum, float scale, cudaStream_t stream) {
     if (R <= 0 || C <= 0) return 0;
     if (ld_dst < R) { set_error("pb2_transpose_colsum: ld_dst (%lld) < rows (%d)", ld_dst, R); return -1; }
-    transpose_colsum_kernel<<<(C + 31) / 32, 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(src), ld_src,
+    PB2_CUDA(launch_pdl(transpose_colsum_kernel, dim3((C + 31) / 32), dim3(256), 0, stream, static_cast<const __nv_bfloat16*>(src), ld_src,
                                                                static_cast<__nv_bfloat16*>(dst), ld_dst, R, C, colsum,
-                                                               scale);
+                                                               scale));
     PB2_LAUNCHED("transpose_colsum_kernel");
     return 0;
 }
@@ -518,7 +526,7 @@ extern "C" int pb2_transpose_multi(const pb2_transpose_jobs* jobs, cudaStream_t 
         if (jobs->job[i].R <= 0 || jobs->job[i].C <= 0) { set_error("pb2_transpose_multi: empty job %d", i); return -1; }
     }
     dim3 grid((max_c + 31) / 32, jobs->count);
-    transpose_multi_kernel<<<grid, 256, 0, stream>>>(*jobs);
+    PB2_CUDA(launch_pdl(transpose_multi_kernel, grid, dim3(256), 0, stream, *jobs));
     PB2_LAUNCHED("transpose_multi_kernel");
     return 0;
 }
@@ -539,7 +547,7 @@ extern "C" int pb2_sumsq(const float* x, size_t n, float* out, cudaStream_t stre
     size_t blocks = (n / 4 + 255) / 256;
     if (blocks > 148 * 8) blocks = 148 * 8;
     if (blocks < 1) blocks = 1;
-    sumsq_kernel<<<static_cast<unsigned>(blocks), 256, 0, stream>>>(x, n, out);
+    PB2_CUDA(launch_pdl(sumsq_kernel, dim3(static_cast<unsigned>(blocks)), dim3(256), 0, stream, x, n, out));
     PB2_LAUNCHED("sumsq_kernel");
     return 0;
 }

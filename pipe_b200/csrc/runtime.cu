@@ -2,6 +2,7 @@
 // TMA tensor-map encoding through the driver entry point.
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -96,6 +97,15 @@ int make_tmap_bf16_2d(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t
 }
 
 // cudaFuncSetAttribute(max dynamic smem) once per (kernel, device) instead of once per launch.
+bool pdl_enabled() {
+    static int on = -1;
+    if (on < 0) {
+        const char* e = getenv("PB2_NO_PDL");
+        on = (e && atoi(e) != 0) ? 0 : 1;
+    }
+    return on != 0;
+}
+
 int ensure_max_smem(const void* func, int bytes) {
     struct Seen { const void* f; int dev; };
     thread_local Seen seen[32];
