@@ -859,9 +859,12 @@ static int gemm_launch(const pb2_gemm_desc* d, float* partials, unsigned int* co
     const int stage_bytes = (kBlockM + bn) * kBlockK * 2;
     int stages = (200 * 1024) / stage_bytes;
     {
-        // With more CTAs than SMs the ring is sized so that two CTAs fit on an SM and both waves
-        // stream at once.  (Capping single-wave launches too, so that the next GEMM could co-reside
-        // during this one's epilogue, measured slightly slower: PB2_GEMM_RING_KB=108 -> +4 % step time.)
+        // With more CTAs than SMs (and no persistent schedule) the ring is halved.  Measured, for the
+        // record: letting two GEMM CTAs share an SM so that the next GEMM's weight tiles arrive during
+        // this one's epilogue (__launch_bounds__(320, 2) = 96 registers, PB2_GEMM_RING_KB=108) made the
+        // training step 9 % slower, 84 KB 28 % slower: with ~3 us of loaded HBM latency a CTA needs its
+        // full ~180 KB of loads in flight to hold its share of the bandwidth, and an L2 prefetch of the next
+        // GEMM's weights from this kernel's tail changed nothing (12.3 -> 12.0 us per chained E x E GEMM).
         static int cap_kb = -1;
         if (cap_kb < 0) {
             const char* e = getenv("PB2_GEMM_RING_KB");
