@@ -282,7 +282,10 @@ embed_bwd_kernel(const long long* __restrict__ tokens, const __nv_bfloat16* __re
 // softmax cross-entropy over bf16 logits [T, ld] (V valid columns).  One CTA per row:
 //   loss[row] = logsumexp(l) - l[target];   logits <- softmax(l) - onehot(target)   (in place)
 // ---------------------------------------------------------------------------------
-__global__ void __launch_bounds__(512)
+constexpr int kCeThreads = 512;
+constexpr int kCeVecs = 8;           // 16-byte vectors per thread held in registers: rows up to 512 * 8 * 8 = 32768 logits
+
+__global__ void __launch_bounds__(kCeThreads)
 ce_fwd_bwd_kernel(__nv_bfloat16* __restrict__ logits, const long long* __restrict__ targets,
                   float* __restrict__ loss_rows, const float* __restrict__ row_scale, int V, long long ld,
                   int write_grad) {
@@ -291,6 +294,68 @@ ce_fwd_bwd_kernel(__nv_bfloat16* __restrict__ logits, const long long* __restric
     __shared__ float red[32];
     const size_t row = blockIdx.x;
     __nv_bfloat16* l = logits + row * ld;
+    const long long tgt = targets[row];
+
+    if ((ld & 7) == 0 && (reinterpret_cast<uintptr_t>(logits) & 15) == 0 && V <= kCeThreads * kCeVecs * 8) {
+        // One trip through memory: the row (57 KB for the tutorial vocabulary) is read once with 16-byte
+        // loads, lives in registers for the max / sum / gradient passes, and is written back once.
+        uint4 raw[kCeVecs];
+        float mx = -INFINITY;
+#pragma unroll
+        for (int u = 0; u < kCeVecs; ++u) {
+            const int c = (u * kCeThreads + threadIdx.x) * 8;
+            raw[u] = make_uint4(0xff80ff80u, 0xff80ff80u, 0xff80ff80u, 0xff80ff80u);      // bf16 -inf
+            if (c < V) raw[u] = *reinterpret_cast<const uint4*>(l + c);
+        }
+#pragma unroll
+        for (int u = 0; u < kCeVecs; ++u) {
+            const int c = (u * kCeThreads + threadIdx.x) * 8;
+            const __nv_bfloat16* e = reinterpret_cast<const __nv_bfloat16*>(&raw[u]);
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                if (c + j < V) mx = fmaxf(mx, __bfloat162float(e[j]));
+        }
+        mx = block_max(mx, red);
+        float se = 0.f;
+#pragma unroll
+        for (int u = 0; u < kCeVecs; ++u) {
+            const int c = (u * kCeThreads + threadIdx.x) * 8;
+            const __nv_bfloat16* e = reinterpret_cast<const __nv_bfloat16*>(&raw[u]);
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                if (c + j < V) se += __expf(__bfloat162float(e[j]) - mx);
+        }
+        se = block_sum(se, red);
+        const float lse = mx + __logf(se);
+        if (threadIdx.x == 0 && loss_rows) loss_rows[row] = lse - __bfloat162float(l[tgt]);
+        if (write_grad) {
+            const float rs = row_scale ? row_scale[row] : 1.f;
+            __syncthreads();           // thread 0 has read l[tgt]
+#pragma unroll
+            for (int u = 0; u < kCeVecs; ++u) {
+                const int c = (u * kCeThreads + threadIdx.x) * 8;
+                if (c >= ld) continue;
+                __nv_bfloat16* e = reinterpret_cast<__nv_bfloat16*>(&raw[u]);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    float p = 0.f;               // columns [V, ld) are padding: zero gradient
+                    if (c + j < V) {
+                        p = __expf(__bfloat162float(e[j]) - lse);
+                        if (c + j == tgt) p -= 1.f;
+                        p *= rs;
+                    }
+                    e[j] = __float2bfloat16(p);
+                }
+                *reinterpret_cast<uint4*>(l + c) = raw[u];
+            }
+            // padding beyond what the register tile covers (ld much larger than V): never the case for
+            // the LM head, handled for completeness
+            for (long long c = static_cast<long long>(kCeThreads) * kCeVecs * 8 + threadIdx.x; c < ld; c += blockDim.x)
+                l[c] = __float2bfloat16(0.f);
+        }
+        return;
+    }
+
     float mx = -INFINITY;
     for (int c = threadIdx.x; c < V; c += blockDim.x) mx = fmaxf(mx, __bfloat162float(l[c]));
     mx = block_max(mx, red);
@@ -298,7 +363,6 @@ ce_fwd_bwd_kernel(__nv_bfloat16* __restrict__ logits, const long long* __restric
     for (int c = threadIdx.x; c < V; c += blockDim.x) se += __expf(__bfloat162float(l[c]) - mx);
     se = block_sum(se, red);
     const float lse = mx + __logf(se);
-    const long long tgt = targets[row];
     if (threadIdx.x == 0 && loss_rows) loss_rows[row] = lse - __bfloat162float(l[tgt]);
     if (write_grad) {
         const float rs = row_scale ? row_scale[row] : 1.f;
@@ -500,7 +564,7 @@ extern "C" int pb2_cross_entropy(void* logits, const long long* targets, float* 
                                  int rows, int V, long long ld, int write_grad, cudaStream_t stream) {
     if (rows <= 0) return 0;
     if (V <= 0 || ld < V) { set_error("pb2_cross_entropy: bad V/ld (%d / %lld)", V, ld); return -1; }
-    PB2_CUDA(launch_pdl(ce_fwd_bwd_kernel, dim3(rows), dim3(512), 0, stream, static_cast<__nv_bfloat16*>(logits), targets, loss_rows, row_scale, V,
+    PB2_CUDA(launch_pdl(ce_fwd_bwd_kernel, dim3(rows), dim3(kCeThreads), 0, stream, static_cast<__nv_bfloat16*>(logits), targets, loss_rows, row_scale, V,
                                                 ld, write_grad));
     PB2_LAUNCHED("ce_fwd_bwd_kernel");
     return 0;

@@ -86,7 +86,7 @@ def test_embedding_fwd_bwd():
     assert torch.equal(a, b) and 0.45 < (a == 0).float().mean().item() < 0.55
 
 
-@pytest.mark.parametrize("rows,V", [(75, 28782), (8, 1000)])
+@pytest.mark.parametrize("rows,V", [(75, 28782), (8, 1000), (5, 40000), (3, 17)])
 def test_cross_entropy(rows, V):
     from pipe_b200.ops import functional as F2
     ld = (V + 63) // 64 * 64
