@@ -73,6 +73,34 @@ def wait_batch(batch: Batch, prev_stream: AbstractStream, next_stream: AbstractS
     batch[:] = _detach_non_float(Wait.apply(prev_stream, next_stream, *batch))
 
 
+class _cell_range:
+    """``record_function`` label for one (micro-batch, stage) cell, doubled as an NVTX range on CUDA
+    devices so the cells show up in ``ncu`` / Nsight timelines as well as in ``torch.profiler`` traces
+    (reference: ``record_function("chunk%d-part%d")``, pipeline.py:206-207, 226-227)."""
+
+    __slots__ = ("label", "nvtx", "rf")
+
+    def __init__(self, label: Optional[str], device: torch.device) -> None:
+        self.label = label
+        self.nvtx = label is not None and device.type == "cuda"
+        self.rf = None
+
+    def __enter__(self):
+        if self.label is not None:
+            self.rf = record_function(self.label)
+            self.rf.__enter__()
+            if self.nvtx:
+                torch.cuda.nvtx.range_push(self.label)
+        return self
+
+    def __exit__(self, *exc):
+        if self.label is not None:
+            if self.nvtx:
+                torch.cuda.nvtx.range_pop()
+            self.rf.__exit__(*exc)
+        return False
+
+
 class Pipeline:
     """Runs micro-batches through partitions on their devices, in place."""
 
@@ -207,7 +235,7 @@ class Pipeline:
         device = self.devices[j]
 
         def stage(*inputs):
-            with use_skip_tracker(tracker), (record_function(label) if label else nullcontext()):
+            with use_skip_tracker(tracker), _cell_range(label, device):
                 return partition(*inputs)
 
         if checkpointed:
