@@ -142,6 +142,23 @@ typedef struct pb2_transpose_jobs {
 } pb2_transpose_jobs;
 int pb2_transpose_multi(const pb2_transpose_jobs* jobs, cudaStream_t stream);
 
+/* ---- stage-to-stage mailbox over NVLink peer memory (multi-process pipeline) --------------------
+ * A mailbox lives in memory that both ranks of a stage boundary have mapped (symmetric memory or CUDA
+ * IPC).  Per message slot the receiver holds the payload area and PB2_MAILBOX_MAX_CTAS flag words, the
+ * sender holds PB2_MAILBOX_MAX_CTAS acknowledgement words; all words start at zero and `seq` starts at 1
+ * and grows by one per use of the slot.  Both sides must pass the same `bytes` (multiple of 16) and
+ * `ctas`.  pb2_mailbox_send: wait until the previous message of the slot was drained, store `src` into
+ * the peer's slot, publish flag = seq.  pb2_mailbox_recv: wait for flag == seq, copy the slot into
+ * `dst`, acknowledge.  Both are single kernel launches on `stream` (asynchronous, stream-ordered with
+ * the kernels that produce `src` / consume `dst`); a peer that never shows up traps the kernel after
+ * PB2_MAILBOX_TIMEOUT_S seconds (default 20).  No counterpart in the reference (its stages share a
+ * process and use cudaMemcpyPeerAsync); NCCL send/recv is the baseline. */
+#define PB2_MAILBOX_MAX_CTAS 32
+int pb2_mailbox_send(const void* src, size_t bytes, void* remote_slot, unsigned int* remote_flags,
+                     const unsigned int* local_acks, unsigned int seq, int slot, int ctas, cudaStream_t stream);
+int pb2_mailbox_recv(void* dst, size_t bytes, const void* local_slot, const unsigned int* local_flags,
+                     unsigned int* remote_acks, unsigned int seq, int slot, int ctas, cudaStream_t stream);
+
 /* ---- asynchronous L2 prefetch of [ptr, ptr + bytes) (16-byte aligned) -----------------------
  * Returns at once; the lines arrive in L2 in the background.  Used to pull the next GEMM's weights
  * while kernels that do not touch HBM are running. */

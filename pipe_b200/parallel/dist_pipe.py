@@ -26,9 +26,17 @@ micro-batch ``i`` is posted before that micro-batch is recomputed, so recompute
 overlaps the transfer — the property the reference gets from its two-node
 Checkpoint/Recompute split.
 
+On GPUs the process group only carries the first step (it doubles as the shape handshake).  From the
+second step on every boundary talks through an *NVLink mailbox* (``parallel/mailbox.py``,
+``csrc/mailbox.cu``): the sender's kernel stores the activation straight into the receiver's memory and
+raises a flag, the receiver's kernel waits for the flag on its own stream — no NCCL call, no host
+wait, no early posting.  ``transport="nccl"`` (or ``PB2_DIST_TRANSPORT=nccl``) keeps the baseline.
+
 Works with ``gloo`` on CPU (tests) and ``nccl`` on GPUs.
 """
 from __future__ import annotations
+
+import os
 
 from typing import Any, Callable, Dict, List, Optional, Sequence, Tuple
 
@@ -95,8 +103,10 @@ class DistPipe(nn.Module):
 
     def __init__(self, stage: nn.Module, chunks: int = 1, checkpoint: str = "except_last",
                  group: Optional[dist.ProcessGroup] = None, device: Optional[torch.device] = None,
-                 strict_except_last: bool = False) -> None:
+                 strict_except_last: bool = False, transport: str = "auto") -> None:
         super().__init__()
+        if transport not in ("auto", "nccl", "mailbox"):
+            raise ValueError("transport is not one of 'auto', 'nccl', or 'mailbox'")
         chunks = int(chunks)
         if chunks <= 0:
             raise ValueError("number of chunks must be positive integer")
@@ -139,6 +149,16 @@ class DistPipe(nn.Module):
         self._early_grads: Dict[int, Any] = {}
         self.last_bubble = 0.0
 
+        # Boundary transport.  The first step always goes through the process group (it carries the
+        # shape handshake); from the second step on CUDA stages talk through NVLink mailboxes
+        # (parallel/mailbox.py) unless transport="nccl" / PB2_DIST_TRANSPORT=nccl asks for the baseline.
+        self.transport = os.environ.get("PB2_DIST_TRANSPORT", transport)
+        self._mb: Optional[Dict[str, Any]] = None         # {"fwd_in", "fwd_out", "bwd_in", "bwd_out"} once built
+        self._mb_failed = False
+        self._steps = 0
+        self._fwd_seq = 0
+        self._bwd_seq = 0
+
     # -- topology --------------------------------------------------------------
     @property
     def is_first(self) -> bool:
@@ -159,6 +179,56 @@ class DistPipe(nn.Module):
         shape changes)."""
         self._recv_specs.clear()
         self._sent_specs.clear()
+        self._mb = None            # back to the process group until the new shapes are known
+        self._mb_failed = False
+        self._steps = 0
+
+    # -- NVLink mailboxes ----------------------------------------------------------
+    def _mailboxes_wanted(self) -> bool:
+        return (self.transport in ("auto", "mailbox") and self.device.type == "cuda" and self._mb is None
+                and not self._mb_failed and self._steps >= 1 and dist.get_backend() == "nccl")
+
+    def _build_mailboxes(self) -> None:
+        """Collective over the pipeline: every rank builds the mailboxes of its one or two boundaries,
+        boundary by boundary in stage order (so the pairwise rendezvous cannot cycle), and all ranks
+        then agree on whether everybody succeeded."""
+        from .mailbox import PeerMailbox, mailbox_supported
+        mb: Dict[str, Any] = {"fwd_in": None, "fwd_out": None, "bwd_in": None, "bwd_out": None}
+        ok = True
+        try:
+            for b in range(self.n_stages - 1):
+                if self.index not in (b, b + 1):
+                    continue
+                sending = self.index == b
+                specs = self._sent_specs if sending else self._recv_specs
+                fwd = {i: [(tuple(s.shape), s.dtype) for s in v] for i, v in specs.items()}
+                bwd = {i: [(tuple(s.shape), s.dtype) for s in v if s.requires_grad] for i, v in specs.items()}
+                flat = [t for v in fwd.values() for t in v]
+                if not fwd or not mailbox_supported(self.device, flat):
+                    raise RuntimeError("boundary tensors are not mailbox-compatible")
+                f = PeerMailbox(self._fwd_groups[b], self.device, self.ranks[b], fwd)
+                g = PeerMailbox(self._bwd_groups[b], self.device, self.ranks[b + 1], bwd) if any(bwd.values()) else None
+                if sending:
+                    mb["fwd_out"], mb["bwd_in"] = f, g
+                else:
+                    mb["fwd_in"], mb["bwd_out"] = f, g
+        except Exception as e:  # noqa: BLE001 - any failure means "stay on the process group"
+            ok = False
+            self._mb_error = f"{type(e).__name__}: {e}"
+        flag = torch.tensor([1 if ok else 0], dtype=torch.int32, device=self.device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)
+        if int(flag.item()) == 1:
+            self._mb = mb
+            self._fwd_seq = 0
+            self._bwd_seq = 0
+        else:
+            self._mb_failed = True
+            if self.transport == "mailbox":
+                raise RuntimeError("transport='mailbox' requested but not available: "
+                                   + getattr(self, "_mb_error", "a peer could not build its mailbox"))
+
+    def _mb_slot(self, box, i: int, specs: Optional[List[_Spec]]) -> bool:
+        return box is not None and specs is not None and (i, 0) in box.nbytes
 
     # -- boundary transfers ------------------------------------------------------
     def _send_meta(self, specs: List[_Spec], dst: int, group) -> None:
@@ -194,6 +264,11 @@ class DistPipe(nn.Module):
             self._sent_specs[i] = specs
         elif known != specs:
             raise RuntimeError("stage output shapes changed between steps; call DistPipe.reset() on every rank")
+        box = self._mb["fwd_out"] if self._mb else None
+        if known is not None and self._mb_slot(box, i, known):
+            for k, t in enumerate(tensors):
+                box.send(i, k, t.detach().contiguous(), self._fwd_seq)
+            return
         for t in tensors:
             self._sends.append(dist.isend(t.detach().contiguous(), self._next(), group=group))
 
@@ -202,6 +277,8 @@ class DistPipe(nn.Module):
         is already in flight — or done — when the stage gets to it."""
         if i in self._early or i not in self._recv_specs:
             return
+        if self._mb and self._mb_slot(self._mb["fwd_in"], i, self._recv_specs.get(i)):
+            return              # the sender pushes into the mailbox on its own; nothing to post
         group = self._fwd_groups[self.index - 1]
         out, works = [], []
         for s in self._recv_specs[i]:
@@ -213,6 +290,12 @@ class DistPipe(nn.Module):
     def _recv_forward(self, i: int) -> Tuple[Tensor, ...]:
         group = self._fwd_groups[self.index - 1]
         specs = self._recv_specs.get(i)
+        box = self._mb["fwd_in"] if self._mb else None
+        if self._mb_slot(box, i, specs):
+            out = [torch.empty(s.shape, dtype=s.dtype, device=self.device) for s in specs]
+            for k, t in enumerate(out):
+                box.recv(i, k, t, self._fwd_seq)
+            return tuple(t.requires_grad_(s.requires_grad) for t, s in zip(out, specs))
         if specs is None:
             specs = self._recv_specs[i] = self._recv_meta(self._prev(), group)
         if i in self._early:
@@ -226,6 +309,22 @@ class DistPipe(nn.Module):
         for w in works:
             w.wait()
         return tuple(t.requires_grad_(s.requires_grad) for t, s in zip(out, specs))
+
+    def _grads_by_mailbox(self, i: int) -> bool:
+        return bool(self._mb) and self._mb_slot(self._mb["bwd_in"], i, self._sent_specs.get(i))
+
+    def _recv_grads_mailbox(self, i: int):
+        box = self._mb["bwd_in"]
+        bufs, k = [], 0
+        for s in self._sent_specs[i]:
+            if not s.requires_grad:
+                bufs.append(None)
+                continue
+            g = torch.empty(s.shape, dtype=s.dtype, device=self.device)
+            box.recv(i, k, g, self._bwd_seq)
+            bufs.append(g)
+            k += 1
+        return bufs
 
     def _post_recv_grads(self, i: int):
         """Post receives for the gradients of micro-batch ``i``'s outputs."""
@@ -242,11 +341,18 @@ class DistPipe(nn.Module):
 
     def _send_grads(self, i: int, inputs: Tuple[Any, ...]) -> None:
         group = self._bwd_groups[self.index - 1]
+        box = self._mb["bwd_out"] if self._mb else None
+        by_mailbox = self._mb_slot(box, i, self._recv_specs.get(i))
+        k = 0
         for t, s in zip(inputs, self._recv_specs[i]):
             if not s.requires_grad:
                 continue
             g = t.grad if t.grad is not None else torch.zeros_like(t)
-            self._sends.append(dist.isend(g.contiguous(), self._prev(), group=group))
+            if by_mailbox:
+                box.send(i, k, g.contiguous(), self._bwd_seq)
+                k += 1
+            else:
+                self._sends.append(dist.isend(g.contiguous(), self._prev(), group=group))
 
     def _drain_sends(self) -> None:
         for w in self._sends:
@@ -276,6 +382,9 @@ class DistPipe(nn.Module):
             batches = []
             m = -1
         m = self._agree_microbatches(m, num_microbatches)
+        if self._mailboxes_wanted():
+            self._build_mailboxes()
+        self._fwd_seq += 1
 
         stop = self._checkpoint_stop(m)
         self._cells = []
@@ -321,6 +430,7 @@ class DistPipe(nn.Module):
             self._cells.append(cell)
 
         self._drain_sends()
+        self._steps += 1
         if not self.is_last:
             return LocalRRef(None)
         gathered = microbatch.gather([Batch(l[0] if len(l) == 1 else l) for l in self._out_leaves])
@@ -348,6 +458,7 @@ class DistPipe(nn.Module):
 
     def _backward(self, loss: Optional[Tensor]) -> None:
         cells = self._cells
+        self._bwd_seq += 1
         if self.is_last:
             if loss is None:
                 raise ValueError("the last stage must be given the loss")
@@ -358,9 +469,11 @@ class DistPipe(nn.Module):
             if self.is_last:
                 grads = [l.grad if torch.is_tensor(l) else None for l in cell.leaves]
                 works = []
+            elif self._grads_by_mailbox(i):
+                grads, works = None, []             # fetched below, right where they are needed
             else:
                 grads, works = self._early_grads.pop(i, None) or self._post_recv_grads(i)
-                if i > 0:
+                if i > 0 and not self._grads_by_mailbox(i - 1):
                     self._early_grads[i - 1] = self._post_recv_grads(i - 1)   # overlaps this cell's backward
 
             if cell.checkpointed:
@@ -369,6 +482,8 @@ class DistPipe(nn.Module):
                 outs = cell.outputs
             for w in works:
                 w.wait()
+            if grads is None:
+                grads = self._recv_grads_mailbox(i)  # one kernel that waits for the peer's flag on this stream
 
             pairs = [(o, g) for o, g in zip(outs, grads)
                      if torch.is_tensor(o) and o.requires_grad and g is not None]

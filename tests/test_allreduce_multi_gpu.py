@@ -127,3 +127,48 @@ def _hybrid_case(rank, world, stages, backend):
 def test_hybrid_replicas_stay_in_sync(world, stages, backend):
     _need(world)
     _spawn(_hybrid_case, world, stages, backend)
+
+
+def _mailbox_case(rank, world, mode):
+    """The NVLink mailbox transport must train like the NCCL transport (same losses, same weights)."""
+    from pipe_b200.models import TransformerConfig, build_stage
+    from pipe_b200.ops.optim import FusedClipAdam
+    from pipe_b200.parallel import DistPipe
+    dev = torch.device("cuda", rank)
+    cfg = TransformerConfig(ntokens=512, emsize=256, nhid=512, nlayers=4, nhead=4, dropout=0.1, bptt=16, batch=10, chunks=4)
+    g = torch.Generator().manual_seed(11)
+    tokens = torch.randint(0, cfg.ntokens, (cfg.batch, cfg.bptt), generator=g).to(dev)
+    targets = torch.randint(0, cfg.ntokens, (cfg.batch, cfg.bptt), generator=g).to(dev)
+    results = {}
+    for transport in ("nccl", "mailbox"):
+        torch.manual_seed(5)
+        body = build_stage(cfg, rank, world, dev, impl="fused", seed=1)
+        pipe = DistPipe(body, chunks=cfg.chunks, checkpoint=mode, device=dev, transport=transport)
+        opt = FusedClipAdam(body, lr=1e-2, max_norm=0.5, distributed=True)
+        losses = []
+        for step in range(4):
+            opt.zero_grad()
+            out = pipe(tokens, targets) if pipe.is_first else pipe()
+            loss = out.local_value().sum() / (cfg.batch * cfg.bptt) if pipe.is_last else None
+            pipe.backward(loss)
+            opt.step()
+            if pipe.is_last:
+                losses.append(loss.item())
+        torch.cuda.synchronize()
+        if transport == "mailbox":
+            assert pipe._mb is not None, getattr(pipe, "_mb_error", "mailboxes were not built")
+        results[transport] = (losses, torch.cat([p.detach().flatten() for p in body.parameters()]).clone())
+        dist.barrier()
+    # not bit-identical run to run: LayerNorm / embedding gradients use fp32 atomics (summation order varies)
+    for a, b in zip(results["nccl"][0], results["mailbox"][0]):
+        assert abs(a - b) <= 1e-3 * abs(a), (results["nccl"][0], results["mailbox"][0])
+    diff = (results["nccl"][1] - results["mailbox"][1]).abs()
+    # Adam's first steps move a weight by ~lr whatever the gradient's size, so a near-zero gradient whose last
+    # bit differs can flip a step: allow isolated 2 * lr differences, but the weights as a whole must agree
+    assert diff.mean().item() < 5e-4 and diff.max().item() <= 4 * 2 * 1e-2 + 1e-6, (diff.mean().item(), diff.max().item())
+
+
+@pytest.mark.parametrize("world,mode", [(2, "never"), (2, "except_last"), (4, "always")])
+def test_mailbox_transport_matches_nccl(world, mode):
+    _need(world)
+    _spawn(_mailbox_case, world, mode)

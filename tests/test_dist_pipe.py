@@ -36,6 +36,9 @@ def _worker(rank, world, port, mode, q):
             out = pipe(x) if pipe.is_first else pipe()
             loss = out.local_value().pow(2).sum() if pipe.is_last else None
             pipe.backward(loss)
+        assert pipe._mb is None and pipe.transport == "auto"      # CPU / gloo: the process group stays the transport
+        with pytest.raises(ValueError):
+            DistPipe(stages[rank], chunks=4, checkpoint=mode, device=torch.device("cpu"), transport="carrier-pigeon")
         grads = {f"{rank}.{k}": p.grad.clone() for k, p in stages[rank].named_parameters()}
         q.put((rank, grads, out.local_value().detach() if pipe.is_last else None))
     finally:
