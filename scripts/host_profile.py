@@ -5,6 +5,9 @@ import torch
 from pipe_b200.models import CONFIGS
 from pipe_b200.models.trainer import LMTrainer
 cfg = copy.copy(CONFIGS["cfg3"])
+if len(sys.argv) > 1 and sys.argv[1] == "tiny":
+    # same layer / micro-batch structure, tiny width: the GPU never backs up, so the profile is pure host cost
+    cfg.emsize = cfg.nhid = 256; cfg.nhead = 4; cfg.ntokens = 2048
 tr = LMTrainer(cfg, n_stages=1, impl="fused", checkpoint="never")
 tok = torch.randint(0, cfg.ntokens, (cfg.batch, cfg.bptt), device="cuda")
 tgt = torch.randint(0, cfg.ntokens, (cfg.batch * cfg.bptt,), device="cuda")
