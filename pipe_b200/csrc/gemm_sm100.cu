@@ -864,7 +864,9 @@ static int gemm_launch(const pb2_gemm_desc* d, float* partials, unsigned int* co
         // this one's epilogue (__launch_bounds__(320, 2) = 96 registers, PB2_GEMM_RING_KB=108) made the
         // training step 9 % slower, 84 KB 28 % slower: with ~3 us of loaded HBM latency a CTA needs its
         // full ~180 KB of loads in flight to hold its share of the bandwidth, and an L2 prefetch of the next
-        // GEMM's weights from this kernel's tail changed nothing (12.3 -> 12.0 us per chained E x E GEMM).
+        // GEMM's weights from this kernel's tail changed nothing (12.3 -> 12.0 us per chained E x E GEMM); neither
+        // did a look-ahead of 4-16 k-blocks of this kernel's own weight stream into L2 with
+        // cp.async.bulk.prefetch.tensor (12.7 -> 12.6-13.6 us, and no rescue for a 108 KB ring).
         static int cap_kb = -1;
         if (cap_kb < 0) {
             const char* e = getenv("PB2_GEMM_RING_KB");
