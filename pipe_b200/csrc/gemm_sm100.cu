@@ -867,6 +867,13 @@ static int gemm_launch(const pb2_gemm_desc* d, float* partials, unsigned int* co
         // GEMM's weights from this kernel's tail changed nothing (12.3 -> 12.0 us per chained E x E GEMM); neither
         // did a look-ahead of 4-16 k-blocks of this kernel's own weight stream into L2 with
         // cp.async.bulk.prefetch.tensor (12.7 -> 12.6-13.6 us, and no rescue for a 108 KB ring).
+        // Also measured and dropped: (a) half-height tiles instead of split-K — UMMA M = 64 (accumulator row r
+        // sits in TMEM lane r % 16 + 32 * (r / 16); numerics verified), 64 x 2 token halves = 128 CTAs, no
+        // exchange after the main loop — runs the E x E shape in 18.3 us instead of 12.7: the main loop then
+        // needs ~217 ns per 64-wide k-block per CTA whatever the CTA count, the L2 policy of the shared
+        // weight tile or the number of independent accumulators (1/2/4), i.e. SS-mode MMAs at M = 64 cost
+        // ~100 cycles each (cuBLAS's 64-row nvjet kernel for this shape is a cta_group::2 kernel);
+        // (b) issuing the A and B tensor copies from two different threads: no change.
         static int cap_kb = -1;
         if (cap_kb < 0) {
             const char* e = getenv("PB2_GEMM_RING_KB");

@@ -18,7 +18,7 @@ def run(M, N, K, wgrad=False, **kw):
         kw = dict(kw, transpose_out=False)
     else:
         out = torch.empty(N, M, dtype=torch.bfloat16, device=dev)
-        ctas = ((M + 127) // 128) * kw.get("splits", 1)
+        ctas = max(((M + 127) // 128) * kw.get("splits", 1), 256)
         kw = dict(kw, transpose_out=True)
     ts = torch.zeros(ctas * 16, dtype=torch.int64, device=dev)
     gemm_nt(a, b, out=out, **kw)
@@ -28,6 +28,8 @@ def run(M, N, K, wgrad=False, **kw):
     lib.pb2_debug_gemm_timestamps(ctypes.c_void_p(0))
     torch.cuda.synchronize()
     t = ts.view(ctas, 16).cpu()
+    t = t[t[:, 0] > 0]                 # CTAs that actually ran (the buffer is sized generously)
+    ctas = t.size(0)
     t0 = t[:, 0].min()
     kw = {k: (v if not torch.is_tensor(v) else "tensor") for k, v in kw.items()}
     print(f"--- M={M} N={N} K={K} {kw} ctas={ctas}: kernel span {(t[:, 6].max() - t0).item() / 1e3:.1f} us")
@@ -40,6 +42,10 @@ if len(sys.argv) > 1 and sys.argv[1] == "big":
     run(4096, 4096, 512, wgrad=True, stages=4)
     run(6144, 1024, 2048)
     run(6144, 1024, 2048, stages=4)
+    sys.exit(0)
+if len(sys.argv) > 1 and sys.argv[1] == "auto":
+    run(4096, 75, 4096)
+    run(4096, 75, 12288)
     sys.exit(0)
 run(4096, 80, 4096, splits=4, reduce_mode=1)
 run(4096, 80, 4096, splits=4, reduce_mode=2)
