@@ -73,6 +73,10 @@ def wait_batch(batch: Batch, prev_stream: AbstractStream, next_stream: AbstractS
     batch[:] = _detach_non_float(Wait.apply(prev_stream, next_stream, *batch))
 
 
+# the reference's private name for the schedule generator (pipeline.py:63-79), kept for code that imports it
+_clock_cycles = clock_cycles
+
+
 class _cell_range:
     """``record_function`` label for one (micro-batch, stage) cell, doubled as an NVTX range on CUDA
     devices so the cells show up in ``ncu`` / Nsight timelines as well as in ``torch.profiler`` traces
