@@ -111,9 +111,11 @@ __device__ __forceinline__ void tc_gather(const __nv_bfloat16* b0, const __nv_bf
 //   C0[SP x SP] = A0[SP x D] * B0[SP x D]^T   and (if A1)   C1 = A1 * B1^T
 // fp32 results with ld = SP + 8; operands row-major bf16 with ld = D + 8.
 __device__ __forceinline__ void tc_abt(const __nv_bfloat16* A0, const __nv_bfloat16* B0, float* C0,
-                                       const __nv_bfloat16* A1, const __nv_bfloat16* B1, float* C1, int SP, int D) {
+                                       const __nv_bfloat16* A1, const __nv_bfloat16* B1, float* C1, int SP, int D,
+                                       int rows_a = 0) {
+    // rows_a: rows of A (and of C) to compute, default all SP; B always has SP rows (C has SP columns)
     const int warp = threadIdx.x >> 5, tiles = SP / 16, dpad = D + 8, cpad = SP + 8;
-    const int per = tiles * tiles, total = A1 ? 2 * per : per;
+    const int per = (rows_a ? rows_a / 16 : tiles) * tiles, total = A1 ? 2 * per : per;
     for (int t = warp; t < total; t += kTcWarps) {
         const int second = t >= per;
         const int r = t - second * per, ti = r / tiles, tj = r - ti * tiles;
@@ -206,6 +208,61 @@ __device__ __forceinline__ float tc_keep(const CounterRng& rng, const AttnTc& a,
     return dropout_keep(rng, a.rng_stream, idx, thr) ? inv_keep : 0.f;
 }
 
+// Forward: softmax of `rows` score rows starting at global row `row0`, times the dropout mask, written
+// as bf16 *over the fp32 rows they came from* (row pitch bpad = 2 * cpad bf16 elements, the same bytes as
+// the fp32 pitch).  Eight lanes share a row and hold all of it in registers, so once they have all read
+// (one __syncwarp) the row can be overwritten; no second pass over shared memory and no extra buffer.
+template <int NSLOT>
+__device__ __forceinline__ void tc_softmax_drop(float* sc, int slot, int row0, int rows, const AttnTc& a, int n, int h) {
+    const int S = a.S, SP = a.SP, sub = threadIdx.x & 7, cpad = SP + 8, bpad = 2 * cpad;
+    const CounterRng rng(a.seed);
+    const uint32_t thr = static_cast<uint32_t>(fminf(a.drop_p, 0.999999f) * 4294967296.0f);
+    const float inv_keep = a.drop_p > 0.f ? 1.f / (1.f - a.drop_p) : 1.f;
+    __nv_bfloat16* pb = reinterpret_cast<__nv_bfloat16*>(sc);
+    for (int rl = threadIdx.x >> 3; rl < rows; rl += kTcThreads / 8) {
+        const int i = row0 + rl;
+        const float* r = sc + rl * cpad;
+        const int lim = i < S ? (a.causal ? i + 1 : S) : 0;
+        float x[16];
+        float mx = -INFINITY;
+#pragma unroll
+        for (int u = 0; u < 16; ++u) {
+            const int j = sub + u * 8;
+            x[u] = -INFINITY;
+            if (j < lim) {
+                float t = r[j];
+#pragma unroll
+                for (int q = 1; q < NSLOT; ++q) t += r[q * slot + j];
+                x[u] = t * a.scale;
+            }
+            mx = fmaxf(mx, x[u]);
+        }
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 4));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+        float se = 0.f;
+#pragma unroll
+        for (int u = 0; u < 16; ++u) {
+            x[u] = (sub + u * 8 < lim) ? __expf(x[u] - mx) : 0.f;
+            se += x[u];
+        }
+        se += __shfl_xor_sync(0xffffffffu, se, 4);
+        se += __shfl_xor_sync(0xffffffffu, se, 2);
+        se += __shfl_xor_sync(0xffffffffu, se, 1);
+        const float inv = lim > 0 ? 1.f / se : 0.f;
+        __syncwarp();              // every lane of the row has its fp32 scores: the row may be overwritten
+#pragma unroll
+        for (int u = 0; u < 16; ++u) {
+            const int j = sub + u * 8;
+            if (j < SP) {
+                float w = x[u] * inv;
+                if (j < lim) w *= tc_keep(rng, a, thr, inv_keep, n, h, i, j);
+                pb[rl * bpad + j] = __float2bfloat16(w);
+            }
+        }
+    }
+}
+
 // out rows (< S) of a [16 x 16] fp32 tile held in this warp's staging area -> bf16 global;
 // `row_stride` is the distance between consecutive sequence positions in elements
 __device__ __forceinline__ void tc_emit_tile(const float* stage, __nv_bfloat16* dst_row0, size_t row_stride, int row0, int S) {
@@ -233,84 +290,78 @@ attn_tc_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restr
     const uint32_t rank = cs > 1 ? cluster_ctarank() : 0u;
     if (cs > 1) cluster_arrive();            // waited for right before the first DSMEM store: every peer is running by then
     extern __shared__ __align__(128) uint8_t smem[];
-    const int S = a.S, SP = a.SP, Dc = a.Dc, dpad = Dc + 8, cpad = SP + 8, slot = SP * cpad;
+    // Query rows are processed in blocks of RB <= 64: the score block [RB x SP] is the only S^2-sized
+    // buffer, so S = 128 needs ~100 KB instead of ~170 KB and two CTAs share an SM (256 CTAs = one wave).
+    const int S = a.S, SP = a.SP, Dc = a.Dc, dpad = Dc + 8, cpad = SP + 8, bpad = 2 * cpad;
+    const int RB = SP < 64 ? SP : 64, slot = RB * cpad;
     __nv_bfloat16* q = reinterpret_cast<__nv_bfloat16*>(smem);
     __nv_bfloat16* k = q + SP * dpad;
     __nv_bfloat16* v = k + SP * dpad;
-    float* sc = reinterpret_cast<float*>(v + SP * dpad);                     // cs partial score matrices
-    __nv_bfloat16* pb = reinterpret_cast<__nv_bfloat16*>(sc + cs * slot);
-    float* stage = reinterpret_cast<float*>(pb + slot) + (threadIdx.x >> 5) * (16 * 24);
+    float* sc = reinterpret_cast<float*>(v + SP * dpad);                     // cs partial score blocks
+    const __nv_bfloat16* pb = reinterpret_cast<const __nv_bfloat16*>(sc);    // probabilities, written over slot 0
+    float* stage = sc + cs * slot + (threadIdx.x >> 5) * (16 * 24);
     const int pair = blockIdx.x / cs;
     const int n = pair / a.H, h = pair - n * a.H;
     const long long ld = 3LL * a.E;
     const int col0 = h * a.D + static_cast<int>(rank) * Dc;
+    const int warp = threadIdx.x >> 5, ct = Dc / 16;
+    const size_t row_stride = static_cast<size_t>(a.NB) * a.E;
 
     tc_gather(qkv + col0, qkv + a.E + col0, qkv + 2 * a.E + col0, nullptr, ld, 0, q, k, v, nullptr, 3, a.NB, S, SP, Dc, n);
     __syncthreads();
     attn_ts(1);
-    tc_abt(q, k, sc + rank * slot, nullptr, nullptr, nullptr, SP, Dc);
-    __syncthreads();
-    if (cs > 1) {
-        cluster_wait();
-        tc_push(sc + rank * slot, slot, cs, rank);
-        cluster_sync_all();
-    }
-    attn_ts(2);
-    tc_softmax<CS>(sc, slot, S, SP, a.scale, a.causal);
-    __syncthreads();
-    attn_ts(3);
-    {
-        const CounterRng rng(a.seed);
-        const uint32_t thr = static_cast<uint32_t>(fminf(a.drop_p, 0.999999f) * 4294967296.0f);
-        const float inv_keep = a.drop_p > 0.f ? 1.f / (1.f - a.drop_p) : 1.f;
-        // a thread keeps its column and walks rows: no division in the loop
-        const int rows_per_pass = kTcThreads / SP > 0 ? kTcThreads / SP : 1;
-        if (SP <= kTcThreads) {
-            const int j = threadIdx.x % SP;
-            for (int i = threadIdx.x / SP; i < SP; i += rows_per_pass) {
-                float w = sc[i * cpad + j];
-                if (i < S && j < S) w *= tc_keep(rng, a, thr, inv_keep, n, h, i, j);
-                pb[i * cpad + j] = __float2bfloat16(w);
-            }
+    for (int rb0 = 0; rb0 < SP; rb0 += RB) {
+        const int rows = SP - rb0 < RB ? SP - rb0 : RB;          // the last block may be short (SP = 80, 96, 112)
+        tc_abt(q + rb0 * dpad, k, sc + rank * slot, nullptr, nullptr, nullptr, SP, Dc, rows);
+        __syncthreads();
+        if (cs > 1) {
+            if (rb0 == 0) cluster_wait();
+            tc_push(sc + rank * slot, slot, cs, rank);
+            cluster_sync_all();
         }
-    }
-    __syncthreads();
-    attn_ts(4);
+        attn_ts(2);
+        tc_softmax_drop<CS>(sc, slot, rb0, rows, a, n, h);
+        __syncthreads();
+        attn_ts(4);
 
-    // O[:, own columns] = P V: each warp keeps up to four output tiles in flight (independent accumulators)
-    const int warp = threadIdx.x >> 5, rt = SP / 16, ct = Dc / 16, total = rt * ct;
-    const size_t row_stride = static_cast<size_t>(a.NB) * a.E;
-    for (int t0 = warp; t0 < total; t0 += kTcWarps * 4) {
-        FragC acc[4];
-        int ti[4], tc[4];
+        // O[block rows, own columns] = P V: each warp keeps up to four output tiles in flight
+        const int total = (rows / 16) * ct;
+        for (int t0 = warp; t0 < total; t0 += kTcWarps * 4) {
+            FragC acc[4];
+            int ti[4], tc[4];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            wmma::fill_fragment(acc[u], 0.f);
-            const int t = t0 + u * kTcWarps;
-            ti[u] = t / ct;
-            tc[u] = t - ti[u] * ct;
-        }
-        for (int kk = 0; kk < SP; kk += 16) {
+            for (int u = 0; u < 4; ++u) {
+                wmma::fill_fragment(acc[u], 0.f);
+                const int t = t0 + u * kTcWarps;
+                ti[u] = t / ct;
+                tc[u] = t - ti[u] * ct;
+            }
+            for (int kk = 0; kk < SP; kk += 16) {
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    if (t0 + u * kTcWarps < total) {
+                        FragA pa;
+                        FragB vb;
+                        wmma::load_matrix_sync(pa, pb + ti[u] * 16 * bpad + kk, bpad);
+                        wmma::load_matrix_sync(vb, v + kk * dpad + tc[u] * 16, dpad);
+                        wmma::mma_sync(acc[u], pa, vb, acc[u]);
+                    }
+                }
+            }
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
                 if (t0 + u * kTcWarps < total) {
-                    FragA pa;
-                    FragB vb;
-                    wmma::load_matrix_sync(pa, pb + ti[u] * 16 * cpad + kk, cpad);
-                    wmma::load_matrix_sync(vb, v + kk * dpad + tc[u] * 16, dpad);
-                    wmma::mma_sync(acc[u], pa, vb, acc[u]);
+                    const int row = rb0 + ti[u] * 16;
+                    wmma::store_matrix_sync(stage, acc[u], 24, wmma::mem_row_major);
+                    __syncwarp();
+                    tc_emit_tile(stage, out + (static_cast<size_t>(row) * a.NB + n) * a.E + col0 + tc[u] * 16, row_stride, row, S);
+                    __syncwarp();
                 }
             }
         }
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            if (t0 + u * kTcWarps < total) {
-                wmma::store_matrix_sync(stage, acc[u], 24, wmma::mem_row_major);
-                __syncwarp();
-                tc_emit_tile(stage, out + (static_cast<size_t>(ti[u] * 16) * a.NB + n) * a.E + col0 + tc[u] * 16, row_stride,
-                             ti[u] * 16, S);
-                __syncwarp();
-            }
+        if (rb0 + RB < SP) {
+            if (cs > 1) cluster_sync_all();      // peers may still be reading nothing of ours, but they push into sc next
+            else __syncthreads();                // the next block's scores overwrite the probabilities
         }
     }
     attn_ts(5);
@@ -458,9 +509,9 @@ attn_tc_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* _
 size_t attn_tc_smem(int SP, int Dc, int cs, bool bwd) {
     const size_t dpad = Dc + 8, cpad = SP + 8;
     size_t b = (bwd ? 4 : 3) * SP * dpad * 2;             // Q K V (dO), this CTA's columns
-    b += (bwd ? 2 : 1) * cs * SP * cpad * 4;               // fp32 partial score matrices, one per cluster rank
-                                                           // (backward: the bf16 copies alias the first)
-    if (!bwd) b += SP * cpad * 2;                          // forward: bf16 probabilities
+    const size_t rows = bwd ? SP : (SP < 64 ? SP : 64);    // forward walks the query rows in blocks of <= 64
+    b += (bwd ? 2 : 1) * cs * rows * cpad * 4;             // fp32 partial score matrices, one per cluster rank
+                                                           // (the bf16 copies alias the first)
     b += kTcWarps * 16 * 24 * 4;                           // per-warp output staging
     return b + 128;
 }

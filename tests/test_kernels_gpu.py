@@ -135,7 +135,8 @@ def test_sumsq():
 
 
 @pytest.mark.parametrize("NB,S,H,D,causal", [(3, 25, 16, 256, False), (2, 25, 4, 64, True), (2, 128, 2, 64, False),
-                                             (1, 25, 64, 128, False)])
+                                             (1, 25, 64, 128, False), (2, 100, 3, 64, True), (3, 72, 2, 128, False),
+                                             (2, 128, 4, 32, True)])
 def test_attention_fwd_bwd(NB, S, H, D, causal):
     from pipe_b200.ops import functional as F2
     E = H * D
