@@ -26,11 +26,11 @@ micro-batch ``i`` is posted before that micro-batch is recomputed, so recompute
 overlaps the transfer — the property the reference gets from its two-node
 Checkpoint/Recompute split.
 
-On GPUs the process group only carries the first step (it doubles as the shape handshake).  From the
-second step on every boundary talks through an *NVLink mailbox* (``parallel/mailbox.py``,
-``csrc/mailbox.cu``): the sender's kernel stores the activation straight into the receiver's memory and
-raises a flag, the receiver's kernel waits for the flag on its own stream — no NCCL call, no host
-wait, no early posting.  ``transport="nccl"`` (or ``PB2_DIST_TRANSPORT=nccl``) keeps the baseline.
+With ``transport="mailbox"`` (or ``PB2_DIST_TRANSPORT=mailbox``) the process group only carries the
+first step (it doubles as the shape handshake); from the second step on every boundary talks through an
+*NVLink mailbox* (``parallel/mailbox.py``, ``csrc/mailbox.cu``): the sender's kernel stores the activation
+straight into the receiver's memory and raises a flag, the receiver's kernel waits for the flag on its
+own stream — no NCCL call, no host wait, no early posting.  The default is ``transport="nccl"``.
 
 Works with ``gloo`` on CPU (tests) and ``nccl`` on GPUs.
 """
@@ -103,7 +103,7 @@ class DistPipe(nn.Module):
 
     def __init__(self, stage: nn.Module, chunks: int = 1, checkpoint: str = "except_last",
                  group: Optional[dist.ProcessGroup] = None, device: Optional[torch.device] = None,
-                 strict_except_last: bool = False, transport: str = "auto") -> None:
+                 strict_except_last: bool = False, transport: str = "nccl") -> None:
         super().__init__()
         if transport not in ("auto", "nccl", "mailbox"):
             raise ValueError("transport is not one of 'auto', 'nccl', or 'mailbox'")
@@ -149,9 +149,12 @@ class DistPipe(nn.Module):
         self._early_grads: Dict[int, Any] = {}
         self.last_bubble = 0.0
 
-        # Boundary transport.  The first step always goes through the process group (it carries the
-        # shape handshake); from the second step on CUDA stages talk through NVLink mailboxes
-        # (parallel/mailbox.py) unless transport="nccl" / PB2_DIST_TRANSPORT=nccl asks for the baseline.
+        # Boundary transport: "nccl" (default: process-group send / recv, receives pre-posted on their own
+        # communicators), "mailbox" / "auto" (NVLink mailboxes, parallel/mailbox.py: the first step still goes
+        # through the process group because it carries the shape handshake).  PB2_DIST_TRANSPORT overrides.
+        # Measured (config 3, fused): N = 2 20.5 -> 20.1 ms and N = 4 13.06 -> 13.02 ms with mailboxes on
+        # the same box, but N = 8 10.2 ms against 9.7 ms for NCCL on another box — not conclusive, so the
+        # transport that produced the published scaling table stays the default.
         self.transport = os.environ.get("PB2_DIST_TRANSPORT", transport)
         self._mb: Optional[Dict[str, Any]] = None         # {"fwd_in", "fwd_out", "bwd_in", "bwd_out"} once built
         self._mb_failed = False

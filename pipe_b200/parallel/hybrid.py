@@ -60,7 +60,7 @@ class HybridPipe(DistPipe):
     """
 
     def __init__(self, stage: nn.Module, stages: int, chunks: int = 1, checkpoint: str = "except_last",
-                 device: Optional[torch.device] = None, transport: str = "auto") -> None:
+                 device: Optional[torch.device] = None, transport: str = "nccl") -> None:
         pipe_group, rep_group, replica, stage_idx, replicas = hybrid_groups(stages)
         super().__init__(stage, chunks=chunks, checkpoint=checkpoint, group=pipe_group, device=device,
                          transport=transport)

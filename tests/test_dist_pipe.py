@@ -36,7 +36,7 @@ def _worker(rank, world, port, mode, q):
             out = pipe(x) if pipe.is_first else pipe()
             loss = out.local_value().pow(2).sum() if pipe.is_last else None
             pipe.backward(loss)
-        assert pipe._mb is None and pipe.transport == "auto"      # CPU / gloo: the process group stays the transport
+        assert pipe._mb is None and pipe.transport == "nccl"      # the process group is the default transport
         with pytest.raises(ValueError):
             DistPipe(stages[rank], chunks=4, checkpoint=mode, device=torch.device("cpu"), transport="carrier-pigeon")
         grads = {f"{rank}.{k}": p.grad.clone() for k, p in stages[rank].named_parameters()}
