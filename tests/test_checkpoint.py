@@ -130,3 +130,22 @@ def test_pipe_modes_same_gradients(mode):
     pipe(x).local_value().sum().backward()
     for p, w in zip(pipe.parameters(), want):
         assert torch.allclose(p.grad, w, atol=1e-6)
+
+
+@pytest.mark.parametrize("mode,n_ckpt", [("never", 0), ("except_last", 2), ("always", 4)])
+def test_backward_graph_shape_matches_the_reference_slides(mode, n_ckpt):
+    """two stages x two micro-batches — Checkpoint/Recompute pairs only on the
+    checkpointed cells, Fork/Join ordering edges in every mode, Copy/Wait at the one stage boundary."""
+    import importlib.util
+    import io
+    import os
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "scripts", "dump_backward_graph.py")
+    spec = importlib.util.spec_from_file_location("dump_backward_graph", path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    names = mod.dump(mode, out=io.StringIO())
+    assert names[0] == "CatBackward0"
+    assert names.count("CheckpointBackward") == n_ckpt and names.count("RecomputeBackward") == n_ckpt
+    assert names.count("CopyBackward") == 2                      # one boundary, two micro-batches
+    assert names.count("WaitBackward") >= 2 * 2
+    assert names.count("ForkBackward") >= 1 and names.count("JoinBackward") >= 1
