@@ -99,11 +99,15 @@ class DistPipe(nn.Module):
         checkpoint: ``'always' | 'except_last' | 'never'``.
         group: process group whose ranks are the stages, in order (default: world).
         device: this rank's device (default: the stage's parameter device).
+        transport: ``"nccl"`` (process-group send / recv) or ``"mailbox"`` / ``"auto"`` (NVLink mailboxes).
+        pipelines: rank lists of *all* pipelines of the job when there are several (``HybridPipe`` passes them);
+            needed because process groups must be created by every rank of the job in the same order.
     """
 
     def __init__(self, stage: nn.Module, chunks: int = 1, checkpoint: str = "except_last",
                  group: Optional[dist.ProcessGroup] = None, device: Optional[torch.device] = None,
-                 strict_except_last: bool = False, transport: str = "nccl") -> None:
+                 strict_except_last: bool = False, transport: str = "nccl",
+                 pipelines: Optional[Sequence[Sequence[int]]] = None) -> None:
         super().__init__()
         if transport not in ("auto", "nccl", "mailbox"):
             raise ValueError("transport is not one of 'auto', 'nccl', or 'mailbox'")
@@ -132,13 +136,23 @@ class DistPipe(nn.Module):
             device = p.device if p is not None else torch.device("cpu")
         self.device = torch.device(device)
 
-        # A communicator per boundary and direction (see module docstring).
+        # A communicator per boundary and direction (see module docstring).  ``dist.new_group`` is a
+        # collective over the whole job: every rank has to create every group, in the same order, members
+        # or not — so when several pipelines run side by side (``pipelines``: the rank lists of all of
+        # them, this one included) each rank walks all of them and keeps the groups of its own.
         self._fwd_groups: List[dist.ProcessGroup] = []
         self._bwd_groups: List[dist.ProcessGroup] = []
-        for j in range(self.n_stages - 1):
-            pair = [self.ranks[j], self.ranks[j + 1]]
-            self._fwd_groups.append(dist.new_group(pair))
-            self._bwd_groups.append(dist.new_group(pair))
+        all_pipes = [list(p) for p in pipelines] if pipelines is not None else [list(self.ranks)]
+        if list(self.ranks) not in all_pipes:
+            raise ValueError("pipelines must contain this pipeline's own rank list")
+        for ranks in all_pipes:
+            mine = ranks == list(self.ranks)
+            for j in range(len(ranks) - 1):
+                pair = [ranks[j], ranks[j + 1]]
+                f, b = dist.new_group(pair), dist.new_group(pair)
+                if mine:
+                    self._fwd_groups.append(f)
+                    self._bwd_groups.append(b)
 
         self._recv_specs: Dict[int, List[_Spec]] = {}     # micro-batch -> specs of tensors from prev stage
         self._sent_specs: Dict[int, List[_Spec]] = {}

@@ -62,8 +62,10 @@ class HybridPipe(DistPipe):
     def __init__(self, stage: nn.Module, stages: int, chunks: int = 1, checkpoint: str = "except_last",
                  device: Optional[torch.device] = None, transport: str = "nccl") -> None:
         pipe_group, rep_group, replica, stage_idx, replicas = hybrid_groups(stages)
+        world = dist.get_world_size()
+        pipelines = [[r * stages + j for j in range(stages)] for r in range(world // stages)]
         super().__init__(stage, chunks=chunks, checkpoint=checkpoint, group=pipe_group, device=device,
-                         transport=transport)
+                         transport=transport, pipelines=pipelines)
         self.replica_group = rep_group
         self.replica = replica
         self.replicas = replicas

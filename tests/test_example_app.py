@@ -43,3 +43,19 @@ def test_example_app_runs_on_cpu():
                          capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, out.stderr[-2000:]
     assert "Total parameters in model" in out.stdout and "| batch   2 |" in out.stdout
+
+
+def test_multi_process_example_two_pipelines_of_two_stages_on_cpu():
+    """examples/dist_main.py under torchrun with gloo: 2 pipelines x 2 stages.  Also the regression test for
+    process-group creation: every rank must create every pipeline's boundary groups (a pipeline that only
+    created its own deadlocked the other one on gloo)."""
+    import socket
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "4", "--master-addr", "127.0.0.1",
+           "--master-port", str(port), os.path.join(ROOT, "examples", "dist_main.py"), "except_last", "--stages", "2",
+           "--small", "--steps", "3"]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=420)
+    assert out.returncode == 0, (out.stdout + out.stderr)[-3000:]
+    assert "2 pipeline(s) x 2 stages" in out.stdout
