@@ -31,6 +31,7 @@ import threading
 from typing import Any, Dict, List, Optional, Tuple
 
 import torch
+import torch.nn.functional as F
 from torch import Tensor, nn
 
 import ctypes
@@ -323,7 +324,29 @@ class FusedEncoderLayer(_FusedBase):
             self.__dict__["_pb2_desc"] = cached
         return _lib.EncoderLayerDesc.from_buffer_copy(cached[1])
 
+    def reference_forward(self, x: Tensor) -> Tensor:
+        """The same layer with the same parameters in plain PyTorch (fp32): the kernels' oracle and the path
+        taken on non-CUDA devices.  Dropout draws from torch's generator instead of the kernels' counter RNG,
+        so outputs agree with the fused path exactly only at ``dropout = 0`` / in eval mode."""
+        S, N, E = x.shape
+        H, D = self.nhead, E // self.nhead
+        p = self.dropout if self.training else 0.0
+        xf = x.float()
+        qkv = F.linear(xf, self.self_attn.in_proj_weight, self.self_attn.in_proj_bias)
+        q, k, v = (t.reshape(S, N, H, D).permute(1, 2, 0, 3) for t in qkv.chunk(3, dim=-1))
+        a = F.scaled_dot_product_attention(q, k, v, dropout_p=p, is_causal=self.causal)
+        a = a.permute(2, 0, 1, 3).reshape(S, N, E)
+        o = F.linear(a, self.self_attn.out_proj.weight, self.self_attn.out_proj.bias)
+        x1 = F.layer_norm(xf + F.dropout(o, p, True), (E,), self.norm1.weight, self.norm1.bias, self.norm1.eps)
+        hidden = F.dropout(F.relu(F.linear(x1, self.linear1.weight, self.linear1.bias)), p, True)
+        f = F.linear(hidden, self.linear2.weight, self.linear2.bias)
+        y = F.layer_norm(x1 + F.dropout(f, p, True), (E,), self.norm2.weight, self.norm2.bias, self.norm2.eps)
+        return y.to(x.dtype)
+
     def forward(self, x: Tensor, *extra: Any):
+        if not x.is_cuda:
+            y = self.reference_forward(x)
+            return (y, *extra) if extra else y
         params = self.__dict__.get("_pb2_params")
         if params is None:
             params = self.__dict__["_pb2_params"] = tuple(self.parameters())
@@ -385,8 +408,17 @@ class FusedEncoder(nn.Module):
     def forward(self, src: Tensor, *extra: Any):
         if src.size(1) > self.pos_encoder.pe.size(0):
             raise ValueError("sequence longer than the positional table")
+        if not src.is_cuda:
+            out = self.reference_forward(src)
+            return (out, *extra) if extra else out
         out = _EmbedFn.apply(src, self, self.encoder.weight)
         return (out, *extra) if extra else out
+
+    def reference_forward(self, src: Tensor) -> Tensor:
+        """Plain PyTorch of the same module (fp32 out): oracle and non-CUDA path."""
+        S = src.size(1)
+        emb = F.embedding(src, self.encoder.weight).transpose(0, 1) * math.sqrt(self.ninp)
+        return F.dropout(emb + self.pos_encoder.pe[:S], self.dropout, self.training)
 
 
 # ======================================================================================
@@ -484,7 +516,18 @@ class FusedDecoder(_FusedBase):
             return
         self._register_linear("dec", self.decoder.weight, self.decoder.bias)
 
+    def reference_forward(self, inp: Tensor, targets: Optional[Tensor] = None) -> Tensor:
+        """Plain PyTorch of the same module (fp32): oracle and non-CUDA path."""
+        logits = F.linear(inp.float(), self.decoder.weight, self.decoder.bias).permute(1, 0, 2)      # (N, S, V)
+        if targets is None:
+            return logits
+        N, S, V = logits.shape
+        per_token = F.cross_entropy(logits.reshape(N * S, V), targets.reshape(-1), reduction="none")
+        return per_token.view(N, S).sum(dim=1)
+
     def forward(self, inp: Tensor, targets: Optional[Tensor] = None):
+        if not inp.is_cuda:
+            return self.reference_forward(inp, targets)
         if targets is None:
             return _DecoderFn.apply(inp, self, *self.parameters())
         return _DecoderLossFn.apply(inp, targets, self, *self.parameters())
