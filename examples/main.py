@@ -40,7 +40,7 @@ def main() -> int:
     on_gpu = torch.cuda.is_available() and torch.cuda.device_count() >= args.gpus
     devices = list(range(args.gpus)) if on_gpu else ["cpu"] * args.gpus
     if args.impl == "fused" and not on_gpu:
-        raise SystemExit("--impl fused needs CUDA devices")
+        print("no CUDA devices: the fused modules run their plain-PyTorch reference path")
 
     if args.data:
         stream, vocab = build_corpus(args.data)

@@ -69,6 +69,17 @@ class FusedClipAdam:
         self.reduce_ctas = 64
         self.step_count = 0
         self.module = module
+        self._cpu: Optional[torch.optim.Optimizer] = None
+        if not any(p.is_cuda for p in module.parameters()):
+            # Non-CUDA parameters (the fused modules' reference path): same surface, same semantics —
+            # average over replicas, clip by the global norm, Adam — on stock PyTorch ops.
+            self._cpu_params = [p for p in module.parameters() if p.requires_grad]
+            self._cpu = torch.optim.Adam(self._cpu_params, lr=lr, betas=betas, eps=eps, weight_decay=weight_decay)
+            self._cpu_norm = 0.0
+            self.devs = {}
+            self._shadows = {}
+            self._gemm_written = set()
+            return
 
         shadows = {}
         gemm_written = set()
@@ -146,6 +157,9 @@ class FusedClipAdam:
         """Small gradients: one memset.  Matrix gradients: nothing — the next wgrad
         GEMM overwrites them (``set_to_none`` is accepted for API compatibility;
         buffers are always kept)."""
+        if self._cpu is not None:
+            self._cpu.zero_grad(set_to_none=set_to_none)
+            return
         for st in self.devs.values():
             st.flat_small.zero_()
             st.normsq.zero_()
@@ -191,10 +205,34 @@ class FusedClipAdam:
         for st in states[1:]:
             st.total_normsq.copy_(total, non_blocking=True)
 
+    def _step_cpu(self) -> None:
+        params = [p for p in self._cpu_params if p.grad is not None]
+        if self.replicas > 1:
+            for p in params:
+                dist.all_reduce(p.grad, group=self.replica_group)
+                p.grad.mul_(1.0 / self.replicas)
+        if self.grad_scale != 1.0:
+            for p in params:
+                p.grad.mul_(self.grad_scale)
+        total = torch.zeros((), dtype=torch.float32)
+        for p in params:
+            total += p.grad.float().pow(2).sum()
+        if self.distributed:
+            dist.all_reduce(total, group=self.group)
+        self._cpu_norm = float(total.sqrt())
+        if self.max_norm > 0:
+            coef = min(1.0, self.max_norm / (self._cpu_norm + 1e-6))
+            for p in params:
+                p.grad.mul_(coef)
+        self._cpu.step()
+
     @torch.no_grad()
     def step(self) -> None:
         wgrad.flush_pending()
         self.step_count += 1
+        if self._cpu is not None:
+            self._step_cpu()
+            return
         if self.replicas > 1:
             self._reduce_replicas()
         elif self.max_norm > 0:
@@ -215,5 +253,7 @@ class FusedClipAdam:
 
     def grad_norm(self) -> float:
         """The global gradient norm used by the last ``step`` (synchronises)."""
+        if self._cpu is not None:
+            return self._cpu_norm
         first = next(iter(self.devs.values()))
         return float(first.total_normsq.sqrt().item()) * self.grad_scale

@@ -53,3 +53,25 @@ def test_pipe_over_fused_modules_on_cpu_with_targets_and_checkpointing():
     (loss.sum() / tok.numel()).backward()
     assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in pipe.parameters())
     pipe.close()
+
+
+def test_fused_clip_adam_on_cpu_equals_clip_plus_torch_adam():
+    from pipe_b200.ops.optim import FusedClipAdam
+    cfg = _cfg()
+    fused = nn.Sequential(*build_layers(cfg, impl="fused", seed=3))
+    eager = nn.Sequential(*build_layers(cfg, impl="eager", seed=3))
+    eager.load_state_dict(fused.state_dict())
+    o1 = FusedClipAdam(fused, lr=1e-2, max_norm=0.5)
+    o2 = torch.optim.Adam(eager.parameters(), lr=1e-2)
+    tok = torch.randint(0, cfg.ntokens, (cfg.batch, cfg.bptt))
+    for _ in range(3):
+        o1.zero_grad()
+        o2.zero_grad()
+        fused(tok).square().mean().backward()
+        eager(tok).square().mean().backward()
+        norm = torch.nn.utils.clip_grad_norm_(eager.parameters(), 0.5)
+        o1.step()
+        o2.step()
+        assert abs(o1.grad_norm() - float(norm)) < 1e-5
+    for p, q in zip(fused.parameters(), eager.parameters()):
+        assert torch.allclose(p, q, atol=1e-6)
