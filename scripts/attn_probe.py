@@ -1,3 +1,5 @@
+"""Attention core timings at the shapes that matter (CUPTI kernel durations; run with PB2_NO_PDL=1 for per-kernel
+times that do not include waiting for the predecessor) plus the in-kernel phase timestamps of CTA 0."""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch

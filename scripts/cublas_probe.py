@@ -1,3 +1,5 @@
+"""Which kernels does cuBLAS pick for the skinny weight-streaming shapes (name, duration)?  The names encode tile,
+stage count, cluster shape and 1-/2-CTA MMA — the reference point for csrc/gemm_sm100.cu."""
 import torch
 from torch.profiler import profile, ProfilerActivity
 dev="cuda"

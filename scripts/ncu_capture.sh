@@ -6,6 +6,7 @@ cd "$(dirname "$0")/.."
 which=${1:-skinny}
 mkdir -p gpurun_out
 python scripts/one_gemm.py $which > gpurun_out/plain_$which.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:gemm_bf16 -s 6 -c 3 -f \
+skip=6; [ "$which" = "wgrad" ] && skip=2        # the wgrad workload launches 6 GEMMs, the skinny one 12
+ncu --set full --clock-control none --import-source on -k regex:gemm_bf16 -s $skip -c 2 -f \
     -o gpurun_out/gemm_$which python scripts/one_gemm.py $which > gpurun_out/ncu_$which.log 2>&1
 echo "ncu rc=$?"; tail -3 gpurun_out/ncu_$which.log

@@ -1,3 +1,6 @@
+#!/bin/bash
+# Everything that needs more than one GPU, in one call on an 8-GPU box: the GPU test tier, the scaling bench at
+# N = 2 / 4 / 8, the config-5 stress run and the hybrid (2 pipelines x 4 stages) bench.  Results land in gpurun_out/.
 set -u
 mkdir -p gpurun_out
 timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -4 > gpurun_out/r8_pytest.txt
