@@ -282,7 +282,7 @@ static int attn_check(const char* who, int NB, int S, int H, int D, size_t smem)
     return 0;
 }
 
-// tensor-core path for S <= 64 (attention_tc.cu)
+// tensor-core path for S <= 128 while its tiles fit shared memory (attention_tc.cu)
 bool attn_tc_supported(int S, int D);
 int attn_tc_fwd(const void* qkv, void* out, int NB, int S, int H, int D, int causal, float drop_p,
                 unsigned long long seed, unsigned long long rng_stream, cudaStream_t stream);
