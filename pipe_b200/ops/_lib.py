@@ -1,4 +1,7 @@
-"""ctypes binding of ``libpipe_b200.so`` (C ABI declared in ``include/pipe_b200.h``)."""
+"""ctypes binding of ``libpipe_b200.so`` (C ABI declared in ``include/pipe_b200.h``).
+
+The reference has no native code of its own; this is the boundary between the PyTorch
+framework layer and the hand-written sm_100a kernels."""
 from __future__ import annotations
 
 import ctypes

@@ -1,4 +1,7 @@
-"""Thin, shape-checked Python wrappers over the C entry points (no autograd here)."""
+"""Thin, shape-checked Python wrappers over the C entry points (no autograd here).
+
+No counterpart in the reference, whose hot operations are ``torch.nn`` call sites (``main.py:24-73,148,182-184``;
+SURVEY.md §2.5 K1-K11): each wrapper here is the sm_100a replacement of one of those library calls."""
 from __future__ import annotations
 
 import ctypes

@@ -5,6 +5,9 @@ fp32 accumulation in TMEM.  ``a`` rides the 128-wide UMMA M axis and ``b`` the
 flexible N axis, so callers put the *larger* dimension (usually the weight) in
 ``a`` and ask for a transposed store (``transpose_out=True``) to get the usual
 ``[tokens, features]`` result — see :func:`linear_forward`.
+
+Reference counterpart: the cuBLAS GEMMs behind ``nn.Linear`` / ``nn.MultiheadAttention`` (``main.py:45,148``);
+SURVEY.md K2 / K4 / K6 / K7, W5.
 """
 from __future__ import annotations
 

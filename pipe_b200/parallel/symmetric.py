@@ -11,6 +11,9 @@ to classic CUDA IPC handles exchanged with ``all_gather_object`` (no multicast, 
 kernel is used).  On CPU / gloo — the host-logic tests — the "buffer" is a plain tensor and
 :meth:`all_reduce_` falls back to ``dist.all_reduce``.
 
+Reference counterpart: none in code — the reference only remarks that DDP may wrap ``Pipe`` with
+``checkpoint='never'`` (``pipe.py:290-293``); SURVEY.md K18, W11, §5.8.
+
 Layout: ``[data: n fp32][signal pad: pb2_allreduce_pad_bytes()]``; ``n`` is rounded up to a
 multiple of ``4 * world`` elements (the kernel's slice granularity).
 """

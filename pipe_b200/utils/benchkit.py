@@ -1,5 +1,8 @@
 """Helpers shared by ``bench.py`` and the bench scripts: clock sampling during the
-timed region, device-side timing with max-over-ranks, pinned host batches."""
+timed region, device-side timing with max-over-ranks, pinned host batches.
+
+The reference's only measurement harness is ``torch.profiler`` around 8 steps (``main.py:187-220``; SURVEY.md §5.1,
+§5.5); these helpers implement the protocol BASELINE.md §3 states instead."""
 from __future__ import annotations
 
 import os
