@@ -260,10 +260,19 @@ typedef struct pb2_encoder_layer {
     const void* next_weight;
     size_t next_weight_bytes;
     int prefetch;                    /* 1: prefetch each GEMM's weights one GEMM ahead */
+    /* optional (backward): a second stream for the launch that stacks x^T / dy^T for the deferred weight
+     * gradients.  Nothing in backward reads those stacks, so the launch leaves the critical path: it waits
+     * (event) for this call's attention backward and then runs next to the remaining kernels.  The caller
+     * keeps x, the activation buffer and the scratch buffer alive until that stream has passed this point,
+     * and orders whatever consumes the stacks / bias gradients after it (pb2_stream_wait_stream). */
+    void* side_stream;
 } pb2_encoder_layer;
 
 int pb2_encoder_layer_fwd(const pb2_encoder_layer* L, cudaStream_t stream);
 int pb2_encoder_layer_bwd(const pb2_encoder_layer* L, cudaStream_t stream);
+
+/* `waiter` waits (on the device) for everything enqueued on `waited` so far; both on the current device. */
+int pb2_stream_wait_stream(cudaStream_t waiter, cudaStream_t waited);
 
 #ifdef __cplusplus
 }

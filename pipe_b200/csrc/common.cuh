@@ -40,6 +40,7 @@ int check_cuda(cudaError_t e, const char* what); // 0 on success, else sets erro
 // launch latency between dependent kernels (1.5 - 2.5 us each, ~900 times per training step).
 // PB2_NO_PDL=1 in the environment falls back to plain launches.
 bool pdl_enabled();
+int record_and_wait(cudaStream_t recorded_on, cudaStream_t waiter);   // event record on one stream, wait on the other
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
                               Args&&... args) {

@@ -86,6 +86,13 @@ extern "C" int pb2_encoder_layer_bwd(const pb2_encoder_layer* L, cudaStream_t st
     if (pf && pb2_l2_prefetch(L->wt_qkv, w_qt, stream)) return -1;
     if (linear(L, Lin{L->wt_o, L->ldt_o, E, E}, L->do_, T, L->da, nullptr, 0, 0.f, 0, nullptr, 0.f, nullptr, stream)) return -1;
     if (pb2_attention_bwd(L->qkv, L->da, L->dqkv, L->NB, L->S, L->heads, E / L->heads, L->causal, p, L->seed, 0, stream)) return -1;
+    // every source of the wgrad-operand transposes exists once the attention backward is done: from here
+    // on they can run on the side stream, next to the QKV dgrad and the next layer's kernels
+    cudaStream_t tstream = stream;
+    if (L->side_stream) {
+        tstream = static_cast<cudaStream_t>(L->side_stream);
+        if (pb2::record_and_wait(stream, tstream)) return -1;
+    }
     if (pf && L->next_weight && pb2_l2_prefetch(L->next_weight, L->next_weight_bytes, stream)) return -1;
     if (linear(L, Lin{L->wt_qkv, L->ldt_qkv, E, 3 * E}, L->dqkv, T, L->dx, nullptr, 0, 0.f, 0, nullptr, 0.f, L->dr1, stream)) return -1;
 
@@ -106,5 +113,5 @@ extern "C" int pb2_encoder_layer_bwd(const pb2_encoder_layer* L, cudaStream_t st
     add(L->dz1, FF, L->dyt_1, L->ld_stash_1, L->stash_off_1, L->db_1);
     add(L->hmid, FF, L->xt_2, L->ld_stash_2, L->stash_off_2, nullptr);
     add(L->df, E, L->dyt_2, L->ld_stash_2, L->stash_off_2, L->db_2);
-    return pb2_transpose_multi(&jobs, stream);
+    return pb2_transpose_multi(&jobs, tstream);
 }

@@ -97,6 +97,23 @@ int make_tmap_bf16_2d(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t
 }
 
 // cudaFuncSetAttribute(max dynamic smem) once per (kernel, device) instead of once per launch.
+// One timing-less event per device is enough for record-then-wait pairs: cudaStreamWaitEvent captures the
+// work recorded by the most recent cudaEventRecord at the time of the call, later records do not disturb it.
+int record_and_wait(cudaStream_t recorded_on, cudaStream_t waiter) {
+    static cudaEvent_t events[64] = {nullptr};
+    static std::atomic_flag busy = ATOMIC_FLAG_INIT;
+    int dev = 0;
+    PB2_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) { set_error("record_and_wait: device ordinal %d out of range", dev); return -1; }
+    while (busy.test_and_set(std::memory_order_acquire)) {}
+    int rc = 0;
+    if (!events[dev] && check_cuda(cudaEventCreateWithFlags(&events[dev], cudaEventDisableTiming), "cudaEventCreate")) rc = -1;
+    if (!rc && check_cuda(cudaEventRecord(events[dev], recorded_on), "cudaEventRecord")) rc = -1;
+    if (!rc && check_cuda(cudaStreamWaitEvent(waiter, events[dev], 0), "cudaStreamWaitEvent")) rc = -1;
+    busy.clear(std::memory_order_release);
+    return rc;
+}
+
 bool pdl_enabled() {
     static int on = -1;
     if (on < 0) {
@@ -126,3 +143,7 @@ int ensure_max_smem(const void* func, int bytes) {
 extern "C" const char* pb2_last_error(void) { return pb2::t_error; }
 extern "C" long long pb2_launch_count(void) { return pb2::g_launches.load(); }
 extern "C" int pb2_version(void) { return 1; }
+
+extern "C" int pb2_stream_wait_stream(cudaStream_t waiter, cudaStream_t waited) {
+    return pb2::record_and_wait(waited, waiter);
+}

@@ -154,6 +154,21 @@ class _Chain(threading.local):
 
 
 _chain = _Chain()
+
+# The launch that stacks x^T / dy^T for the deferred weight gradients runs on a stream of its own: nothing in
+# backward reads its results, so on the main stream it was ~6.4 us plus a launch dependency between every layer's
+# QKV dgrad and the next layer's LayerNorm backward.  PB2_SIDE_TRANSPOSE=0 puts it back in line.
+_SIDE_TRANSPOSE = os.environ.get("PB2_SIDE_TRANSPOSE", "1") != "0"
+_side_lock = threading.Lock()
+_side_streams: Dict[int, "torch.cuda.Stream"] = {}
+
+
+def _side_stream(device: torch.device) -> "torch.cuda.Stream":
+    with _side_lock:
+        st = _side_streams.get(device.index)
+        if st is None:
+            st = _side_streams[device.index] = torch.cuda.Stream(device)
+        return st
 # Measured on B200 (config 3, 1 GPU): prefetching one GEMM ahead made the step 25 % SLOWER (40.0 -> 49.8 ms):
 # the extra launches serialise the PDL chain and the prefetched lines compete with the streaming GEMM for
 # HBM and L2.  Kept as an opt-in experiment (PB2_PREFETCH=1), off by default.
@@ -267,9 +282,19 @@ class _EncoderLayerFn(torch.autograd.Function):
             setattr(d, "db_" + key, bias.grad.data_ptr())
         ws = workspace(dev, stream)
         d.workspace, d.workspace_bytes = ws.data_ptr(), ws.numel()
+        side = _side_stream(dev) if _SIDE_TRANSPOSE else None
+        d.side_stream = side.cuda_stream if side is not None else None
         with _lib.on_device(dev):
             rc = _lib.load().pb2_encoder_layer_bwd(ctypes.byref(d), ctypes.c_void_p(stream))
         _lib.check(rc, "pb2_encoder_layer_bwd")
+        if side is not None:
+            # the side stream reads the layer input, the saved activations and this call's scratch: keep the
+            # allocator from recycling them before it has; consumers of the stacks wait in wgrad.flush_pending
+            x2.record_stream(side)
+            act.record_stream(side)
+            tmp.record_stream(side)
+            from ..ops import wgrad as _wgrad
+            _wgrad.note_side_stream(dev, stream, side)
         return (dx, None) + (None,) * (len(ctx.needs_input_grad) - 2)
 
 

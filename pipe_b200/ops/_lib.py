@@ -61,7 +61,7 @@ class EncoderLayerDesc(ctypes.Structure):
         + [(n, _ll) for n in ("ld_stash_qkv", "ld_stash_o", "ld_stash_1", "ld_stash_2")]
         + [(n, _ci) for n in ("stash_off_qkv", "stash_off_o", "stash_off_1", "stash_off_2")]
         + [("workspace", _vp), ("workspace_bytes", ctypes.c_size_t)]
-        + [("next_weight", _vp), ("next_weight_bytes", ctypes.c_size_t), ("prefetch", _ci)]
+        + [("next_weight", _vp), ("next_weight_bytes", ctypes.c_size_t), ("prefetch", _ci), ("side_stream", _vp)]
     )
 
 

@@ -19,6 +19,7 @@ once at its end).
 """
 from __future__ import annotations
 
+import ctypes
 import threading
 from contextlib import contextmanager
 from typing import Dict, Iterator, List, Optional, Set, Tuple
@@ -33,6 +34,28 @@ __all__ = ["LinearGrad", "deferred", "outer_backward", "flush_pending", "ensure_
 
 _lock = threading.RLock()
 _pending: "Dict[int, LinearGrad]" = {}
+# Side streams that stacked operands since the last flush: {(device index, main stream handle): side stream}.
+# The transposes that fill ``xt`` / ``dyt`` (and add up the bias gradients) may run on a stream of their own
+# (models/fused.py); whoever consumes their results on the main stream waits for that stream first.
+_side_streams: "Dict[Tuple[int, int], torch.cuda.Stream]" = {}
+
+
+def note_side_stream(device: torch.device, main_stream: int, side: "torch.cuda.Stream") -> None:
+    with _lock:
+        _side_streams[(device.index, main_stream)] = side
+
+
+def wait_side_streams(device: Optional[torch.device] = None) -> None:
+    """Make every main stream that has side-stream work outstanding wait for it (device-side wait)."""
+    with _lock:
+        items = [(k, v) for k, v in _side_streams.items() if device is None or k[0] == device.index]
+        for k, _ in items:
+            del _side_streams[k]
+    for (index, main), side in items:
+        with torch.cuda.device(index):
+            rc = _lib.load().pb2_stream_wait_stream(ctypes.c_void_p(main), ctypes.c_void_p(side.cuda_stream))
+        _lib.check(rc, "pb2_stream_wait_stream")
+
 _defer_depth = 0
 _nested_depth = 0
 _callback_queued = False
@@ -65,6 +88,8 @@ class LinearGrad:
             while new_cap < need:
                 new_cap *= 2
             dev = self.weight.device
+            if self.used and dev.type == "cuda":
+                wait_side_streams(dev)          # the columns copied below may still be in flight on a side stream
             xt = torch.zeros((in_f, new_cap), dtype=torch.bfloat16, device=dev)
             dyt = torch.zeros((out_f, new_cap), dtype=torch.bfloat16, device=dev)
             if self.used:
@@ -142,6 +167,8 @@ def flush_pending() -> None:
     with _lock:
         todo = list(_pending.values())
         _pending.clear()
+    if todo:
+        wait_side_streams()
     for lg in todo:
         lg.flush()
 
