@@ -149,3 +149,9 @@ def test_backward_graph_shape_matches_the_reference_slides(mode, n_ckpt):
     assert names.count("CopyBackward") == 2                      # one boundary, two micro-batches
     assert names.count("WaitBackward") >= 2 * 2
     assert names.count("ForkBackward") >= 1 and names.count("JoinBackward") >= 1
+    if mode == "never":
+        # the author's findings: the ordering edge skips stage 0 (only cell (1,1) is joined to
+        # cell (0,1): pipeline.py:131), and the last stage has no trailing Wait (pipeline.py:253): per micro-batch
+        # one Wait after stage 0 and one before stage 1
+        assert names.count("JoinBackward") == 1 and names.count("ForkBackward") == 1
+        assert names.count("WaitBackward") == 4
