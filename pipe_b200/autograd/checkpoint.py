@@ -21,8 +21,10 @@ queued first and overlap the transfer.  ``Fork`` has two outputs, so
 
 Dropout determinism: CPU and device RNG states are captured in the forward and
 reinstated for the recompute.  The fused sm_100a dropout kernels of this
-package draw their Philox ``(seed, offset)`` from the (captured) CPU generator,
-so they replay bit-identically too.
+package take explicit seeds; inside a checkpointed cell those come from a base
+owned by the cell (``autograd/seeds.py``), not from the process-global CPU
+generator that other stage threads advance concurrently, so they replay
+bit-identically on any thread.
 
 Parity: reference ``pipeline.py:16,195-214`` (call sites),
 ``README.md:446-545`` (excerpts of the absent ``checkpoint`` module),
@@ -41,6 +43,7 @@ from torch import Tensor
 from ..microbatch import Batch
 from .dependency import fork, join
 from .phony import get_phony
+from .seeds import SeedBase, seed_scope
 
 __all__ = [
     "Checkpointing", "Checkpoint", "Recompute", "checkpoint",
@@ -97,6 +100,19 @@ def is_recomputing() -> bool:
 # ----------------------------------------------------------------------------
 # RNG capture / replay
 # ----------------------------------------------------------------------------
+class _RngSlot(deque):
+    """The one-slot RNG mailbox of a cell; also carries the cell's fused-dropout seed base."""
+
+    def __init__(self) -> None:
+        super().__init__(maxlen=1)
+        self.seed_base = SeedBase()
+
+
+def _seed_base(rng_states) -> SeedBase:
+    base = getattr(rng_states, "seed_base", None)
+    return base if base is not None else SeedBase()
+
+
 def save_rng_states(device: torch.device, rng_states: Deque[RNGStates]) -> None:
     cpu_state = torch.get_rng_state()
     dev_state: Optional[Tensor] = None
@@ -141,7 +157,8 @@ class Checkpoint(torch.autograd.Function):
         device = next(x for x in inputs if torch.is_tensor(x)).device
         save_rng_states(device, rng_states)
 
-        with torch.no_grad(), enable_checkpointing():
+        # fused-dropout seeds of this cell come from a base only this cell owns (autograd/seeds.py)
+        with torch.no_grad(), enable_checkpointing(), seed_scope(_seed_base(rng_states)):
             output = function(inputs[0]) if input_atomic else function(*inputs)
         return output
 
@@ -187,8 +204,9 @@ class Recompute(torch.autograd.Function):
         leaves = _detach_leaves(inputs)
         device = inputs[ctx.tensor_at[0]].device
 
+        base = _seed_base(ctx.rng_states)
         with restore_rng_states(device, ctx.rng_states):
-            with torch.enable_grad(), enable_recomputing():
+            with torch.enable_grad(), enable_recomputing(), seed_scope(base):
                 output = ctx.function(leaves[0]) if ctx.input_atomic else ctx.function(*leaves)
 
         ctx.recomputed.append((output, leaves))
@@ -203,7 +221,7 @@ class Checkpointing:
         self.batch = batch
         # One-slot mailboxes shared by the two nodes.
         self.recomputed: Deque[Recomputed] = deque(maxlen=1)
-        self.rng_states: Deque[RNGStates] = deque(maxlen=1)
+        self.rng_states: Deque[RNGStates] = _RngSlot()
 
     def _inputs(self) -> Tuple[bool, Tuple[Any, ...]]:
         if self.batch.atomic:

@@ -36,18 +36,22 @@ class Context:
     next_stream: AbstractStream
 
 
-def _move(tensor: Tensor, src_stream: AbstractStream, dst_stream: AbstractStream) -> Tensor:
+def _move(tensor: Tensor, src_stream: AbstractStream, dst_stream: AbstractStream,
+          consumer: AbstractStream) -> Tensor:
     """Asynchronous copy of one tensor from src_stream's device to dst_stream's.
 
-    Must be called with both streams current.  The source block stays reserved
-    for ``src_stream`` and the destination block for the stream that is current
-    on the destination device, until the copy has drained.
+    Must be called with both copy streams current.  ``consumer`` is the stream that
+    was current on the destination device *before* the copy streams were entered
+    — the compute stream whose kernels will read the result.  The source block
+    stays reserved for ``src_stream``; the destination block is allocated on
+    ``dst_stream`` (its pool) and additionally recorded on ``consumer``, so that
+    dropping the Python reference while compute kernels still read it cannot hand
+    the block to the next allocation on the copy stream (reference README.md:197-208,
+    218-231: ``output_stream`` / ``input_stream`` are captured outside ``use_stream``).
     """
     moved = tensor.to(get_device(dst_stream), non_blocking=True)
     record_stream(tensor, src_stream)
-    # `moved` was allocated on dst device's *current* stream, which is dst_stream
-    # here; recording makes that explicit if an outer context differs.
-    record_stream(moved, current_stream(get_device(dst_stream)))
+    record_stream(moved, consumer)
     return moved
 
 
@@ -59,9 +63,10 @@ class Copy(torch.autograd.Function):
         ctx.next_stream = next_stream
 
         out: List[Any] = []
+        consumer = current_stream(get_device(next_stream))      # captured before the copy streams are entered
         with use_stream(prev_stream), use_stream(next_stream):
             for v in values:
-                out.append(_move(v, prev_stream, next_stream) if torch.is_tensor(v) else v)
+                out.append(_move(v, prev_stream, next_stream, consumer) if torch.is_tensor(v) else v)
         return tuple(out)
 
     @staticmethod
@@ -72,10 +77,11 @@ class Copy(torch.autograd.Function):
         # as its copy is queued, so the sender-side blocks free up early.
         moved: Deque[Optional[Tensor]] = deque(maxlen=len(grads))
         pending = list(grads)
+        consumer = current_stream(get_device(prev_stream))
         with use_stream(prev_stream), use_stream(next_stream):
             while pending:
                 g = pending.pop()
-                moved.appendleft(None if g is None else _move(g, next_stream, prev_stream))
+                moved.appendleft(None if g is None else _move(g, next_stream, prev_stream, consumer))
         return (None, None) + tuple(moved)
 
 

@@ -11,6 +11,7 @@ import torch
 from torch import Tensor
 
 from . import _lib
+from ..autograd import seeds as _seeds
 from ._lib import ptr
 
 __all__ = ["add_layernorm_fwd", "add_layernorm_bwd", "embed_fwd", "embed_bwd", "cross_entropy",
@@ -24,10 +25,10 @@ c_p = ctypes.c_void_p
 
 
 def draw_seed() -> int:
-    """A 63-bit seed from torch's *CPU* generator.  Checkpointing captures and
-    replays that generator, so a recompute draws the same seed and the Philox
-    dropout masks come out bit-identical."""
-    return int(torch.empty((), dtype=torch.int64).random_().item())
+    """A 63-bit seed for one fused-dropout call site.  Inside a checkpointed cell the seeds come from
+    the cell's own base (:mod:`pipe_b200.autograd.seeds`), so a recompute — on whichever thread —
+    regenerates bit-identical masks; elsewhere it is a locked draw from torch's CPU generator."""
+    return _seeds.draw_seed()
 
 
 def _s(t: Tensor) -> c_p:

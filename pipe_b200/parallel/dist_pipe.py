@@ -46,6 +46,7 @@ from torch import Tensor, nn
 
 from .. import microbatch
 from ..autograd.checkpoint import enable_checkpointing, enable_recomputing
+from ..autograd.seeds import SeedBase, seed_scope
 from ..microbatch import Batch
 from ..rref import LocalRRef
 from ..runtime.schedule import bubble_fraction
@@ -79,7 +80,7 @@ class _Spec:
 class _Cell:
     """What one micro-batch leaves behind on this stage between forward and backward."""
 
-    __slots__ = ("inputs", "outputs", "checkpointed", "cpu_rng", "dev_rng", "leaves")
+    __slots__ = ("inputs", "outputs", "checkpointed", "cpu_rng", "dev_rng", "leaves", "seed_base")
 
     def __init__(self) -> None:
         self.inputs: Tuple[Any, ...] = ()
@@ -88,6 +89,7 @@ class _Cell:
         self.cpu_rng: Optional[Tensor] = None
         self.dev_rng: Optional[Tensor] = None
         self.leaves: Tuple[Any, ...] = ()
+        self.seed_base = SeedBase()
 
 
 class DistPipe(nn.Module):
@@ -424,7 +426,7 @@ class DistPipe(nn.Module):
                 cell.cpu_rng = torch.get_rng_state()
                 if self.device.type == "cuda":
                     cell.dev_rng = torch.cuda.get_rng_state(self.device)
-                with torch.no_grad(), enable_checkpointing():
+                with torch.no_grad(), enable_checkpointing(), seed_scope(cell.seed_base):
                     out = self._call(values)
             else:
                 out = self._call(values)
@@ -519,6 +521,6 @@ class DistPipe(nn.Module):
             torch.set_rng_state(cell.cpu_rng)
             if cell.dev_rng is not None:
                 torch.cuda.set_rng_state(cell.dev_rng, self.device)
-            with torch.enable_grad(), enable_recomputing():
+            with torch.enable_grad(), enable_recomputing(), seed_scope(cell.seed_base):
                 out = self._call(cell.inputs)
         return out if isinstance(out, tuple) else (out,)
