@@ -362,3 +362,226 @@ class DistPipe(nn.Module):
     @property
     def _has_skips(self) -> bool:
         return bool(self._skip_out) or bool(self._skip_in)
+
+    # -- NVLink mailboxes ----------------------------------------------------------
+    def _mailboxes_wanted(self) -> bool:
+        return (self.transport in ("auto", "mailbox") and self.device.type == "cuda" and self._mb is None
+                and not self._mb_failed and self._cur is not None and self._cur.steps >= 1
+                and torch.is_grad_enabled() and dist.get_backend() == "nccl")
+
+    def _build_mailboxes(self) -> None:
+        """Collective over the pipeline: every rank builds the mailboxes of its one or two boundaries,
+        boundary by boundary in stage order (so the pairwise rendezvous cannot cycle), and all ranks
+        then agree on whether everybody succeeded."""
+        from .mailbox import PeerMailbox, mailbox_supported
+        mb: Dict[str, Any] = {"fwd_in": None, "fwd_out": None, "bwd_in": None, "bwd_out": None}
+        ok = True
+        cur = self._cur
+        try:
+            for b in range(self.n_stages - 1):
+                if self.index not in (b, b + 1):
+                    continue
+                sending = self.index == b
+                specs = cur.sent if sending else cur.recv
+                fwd = {i: [(tuple(s.shape), s.dtype) for s in v] for i, v in specs.items()}
+                bwd = {i: [(tuple(s.shape), s.dtype) for s in v if s.requires_grad] for i, v in specs.items()}
+                flat = [t for v in fwd.values() for t in v]
+                if not fwd or not mailbox_supported(self.device, flat):
+                    raise RuntimeError("boundary tensors are not mailbox-compatible")
+                f = PeerMailbox(self._fwd_groups[b], self.device, self.ranks[b], fwd)
+                g = PeerMailbox(self._bwd_groups[b], self.device, self.ranks[b + 1], bwd) if any(bwd.values()) else None
+                if sending:
+                    mb["fwd_out"], mb["bwd_in"] = f, g
+                else:
+                    mb["fwd_in"], mb["bwd_out"] = f, g
+        except Exception as e:  # noqa: BLE001 - any failure means "stay on the process group"
+            ok = False
+            self._mb_error = f"{type(e).__name__}: {e}"
+        flag = torch.tensor([1 if ok else 0], dtype=torch.int32, device=self.device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)
+        if int(flag.item()) == 1:
+            self._mb = mb
+            self._mb_shapes = cur
+            self._fwd_seq = 0
+            self._bwd_seq = 0
+        else:
+            self._mb_failed = True
+            if self.transport == "mailbox":
+                raise RuntimeError("transport='mailbox' requested but not available: "
+                                   + getattr(self, "_mb_error", "a peer could not build its mailbox"))
+
+    def _box(self, name: str):
+        """The mailbox of one boundary direction, if mailboxes exist for the current signature."""
+        if self._mb is None or self._mb_shapes is not self._cur:
+            return None
+        return self._mb[name]
+
+    def _mb_slot(self, box, i: int, specs: Optional[List[_Spec]]) -> bool:
+        return box is not None and specs is not None and (i, 0) in box.nbytes
+
+    # -- per-step header -----------------------------------------------------------
+    def _signature(self, inputs: Sequence[Any], m: int) -> int:
+        desc: List[Any] = [m, int(torch.is_grad_enabled()), int(self.stage.training)]
+        for v in inputs:
+            t = v.tensor if isinstance(v, microbatch.NoChunk) else v
+            if torch.is_tensor(t):
+                desc.append((tuple(t.shape), str(t.dtype), bool(t.requires_grad)))
+            else:
+                desc.append(type(t).__name__)
+        return zlib.crc32(repr(desc).encode()) & 0x7FFFFFFF
+
+    def _begin_step(self, inputs: Sequence[Any], m_first: int) -> int:
+        """Agree on (micro-batch count, signature) and select that signature's shape cache."""
+        sig = self._signature(inputs, m_first) if self.is_first else -1
+        if self.static_shapes and self._cur is not None:
+            if self.is_first and sig != self._cur.sig:
+                raise RuntimeError("static_shapes=True but the mini-batch changed (shape, dtype or grad mode); "
+                                   "build the pipe with static_shapes=False, or call reset() on every rank")
+            return self._cur.m
+        if self.n_stages > 1:
+            t = torch.tensor([m_first, sig], dtype=torch.int64, device=self.device)
+            dist.broadcast(t, self.ranks[0], group=self.group)
+            if not self.is_first:
+                m_first, sig = (int(v) for v in t.tolist())
+        cur = self._caches.get(sig)
+        if cur is None or cur.m != m_first:
+            cur = self._caches[sig] = _Shapes(sig, m_first)
+        if cur is not self._cur:
+            self._early.clear()
+            self._early_grads.clear()
+        self._cur = cur
+        return cur.m
+
+    # -- boundary transfers ------------------------------------------------------
+    def _p2p(self, ops: List[Any]) -> List[Any]:
+        """One batched point-to-point operation for all tensors of a micro-batch (NCCL coalesces
+        them into one group launch; gloo issues them one by one)."""
+        if not ops:
+            return []
+        return list(dist.batch_isend_irecv(ops))
+
+    def _send_meta(self, specs: List[_Spec], dst: int, group) -> None:
+        meta = [len(specs)]
+        for s in specs:
+            meta += [_DTYPES.index(s.dtype), int(s.requires_grad), len(s.shape), *s.shape]
+        if len(meta) > _META_LEN * 8:
+            raise ValueError("too many / too high-rank tensors cross the stage boundary")
+        meta += [0] * (_META_LEN * 8 - len(meta))
+        t = torch.tensor(meta, dtype=torch.int64, device=self.device)
+        for w in self._p2p([dist.P2POp(dist.isend, t, dst, group)]):
+            w.wait()
+
+    def _recv_meta(self, src: int, group) -> List[_Spec]:
+        buf = torch.empty(_META_LEN * 8, dtype=torch.int64, device=self.device)
+        for w in self._p2p([dist.P2POp(dist.irecv, buf, src, group)]):
+            w.wait()
+        meta = buf.tolist()
+        specs, at = [], 1
+        for _ in range(meta[0]):
+            code, rg, nd = meta[at:at + 3]
+            shape = meta[at + 3:at + 3 + nd]
+            specs.append(_Spec(shape, _DTYPES[code], bool(rg)))
+            at += 3 + nd
+        return specs
+
+    def _send_forward(self, i: int, values: Tuple[Any, ...], force_grad: bool) -> None:
+        tensors = [v for v in values if torch.is_tensor(v)]
+        if len(tensors) != len(values):
+            raise TypeError("only tensors can cross a DistPipe stage boundary")
+        specs = [_Spec.of(t, force_grad) for t in tensors]
+        group = self._fwd_groups[self.index]
+        known = self._cur.sent.get(i)
+        if known is None:
+            self._send_meta(specs, self._next(), group)
+            self._cur.sent[i] = specs
+        elif known != specs:
+            raise RuntimeError(f"stage {self.index}: output shapes of micro-batch {i} changed for an unchanged input "
+                               f"({known} -> {specs}); call DistPipe.reset() on every rank")
+        box = self._box("fwd_out")
+        if known is not None and self._mb_slot(box, i, known):
+            for k, t in enumerate(tensors):
+                box.send(i, k, t.detach().contiguous(), self._fwd_seq)
+            return
+        ops = [dist.P2POp(dist.isend, t.detach().contiguous(), self._next(), group) for t in tensors]
+        self._sends += self._p2p(ops)
+
+    def _post_recv_forward(self, i: int) -> None:
+        """Queue the receives of micro-batch ``i`` now (its shapes must be known), so the transfer
+        is already in flight — or done — when the stage gets to it."""
+        specs = self._cur.recv.get(i)
+        if i in self._early or specs is None:
+            return
+        if self._mb_slot(self._box("fwd_in"), i, specs):
+            return              # the sender pushes into the mailbox on its own; nothing to post
+        group = self._fwd_groups[self.index - 1]
+        out = [torch.empty(s.shape, dtype=s.dtype, device=self.device) for s in specs]
+        works = self._p2p([dist.P2POp(dist.irecv, t, self._prev(), group) for t in out])
+        self._early[i] = (out, works)
+
+    def _recv_forward(self, i: int) -> Tuple[Tensor, ...]:
+        group = self._fwd_groups[self.index - 1]
+        specs = self._cur.recv.get(i)
+        grad_on = torch.is_grad_enabled()
+        box = self._box("fwd_in")
+        if self._mb_slot(box, i, specs):
+            out = [torch.empty(s.shape, dtype=s.dtype, device=self.device) for s in specs]
+            for k, t in enumerate(out):
+                box.recv(i, k, t, self._fwd_seq)
+            return tuple(t.requires_grad_(s.requires_grad and grad_on) for t, s in zip(out, specs))
+        if specs is None:
+            specs = self._cur.recv[i] = self._recv_meta(self._prev(), group)
+        if i in self._early:
+            out, works = self._early.pop(i)
+        else:
+            out = [torch.empty(s.shape, dtype=s.dtype, device=self.device) for s in specs]
+            works = self._p2p([dist.P2POp(dist.irecv, t, self._prev(), group) for t in out])
+        for w in works:
+            w.wait()
+        return tuple(t.requires_grad_(s.requires_grad and grad_on) for t, s in zip(out, specs))
+
+    def _grads_by_mailbox(self, i: int) -> bool:
+        return self._mb_slot(self._box("bwd_in"), i, self._cur.sent.get(i))
+
+    def _recv_grads_mailbox(self, i: int):
+        box = self._box("bwd_in")
+        bufs, k = [], 0
+        for s in self._cur.sent[i]:
+            if not s.requires_grad:
+                bufs.append(None)
+                continue
+            g = torch.empty(s.shape, dtype=s.dtype, device=self.device)
+            box.recv(i, k, g, self._bwd_seq)
+            bufs.append(g)
+            k += 1
+        return bufs
+
+    def _post_recv_grads(self, i: int):
+        """Post receives for the gradients of micro-batch ``i``'s outputs."""
+        group = self._bwd_groups[self.index]
+        bufs: List[Optional[Tensor]] = []
+        for s in self._cur.sent[i]:
+            bufs.append(torch.empty(s.shape, dtype=s.dtype, device=self.device) if s.requires_grad else None)
+        works = self._p2p([dist.P2POp(dist.irecv, g, self._next(), group) for g in bufs if g is not None])
+        return bufs, works
+
+    def _send_grads(self, i: int, inputs: Tuple[Any, ...]) -> None:
+        group = self._bwd_groups[self.index - 1]
+        box = self._box("bwd_out")
+        by_mailbox = self._mb_slot(box, i, self._cur.recv.get(i))
+        k = 0
+        ops = []
+        for t, s in zip(inputs, self._cur.recv[i]):
+            if not s.requires_grad:
+                continue
+            g = t.grad if t.grad is not None else torch.zeros_like(t)
+            if by_mailbox:
+                box.send(i, k, g.contiguous(), self._bwd_seq)
+                k += 1
+            else:
+                ops.append(dist.P2POp(dist.isend, g.contiguous(), self._prev(), group))
+        self._sends += self._p2p(ops)
+
+    def _drain_sends(self) -> None:
+        for w in self._sends:
+            w.wait()
+        self._sends = []
