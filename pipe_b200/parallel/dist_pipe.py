@@ -585,3 +585,278 @@ class DistPipe(nn.Module):
         for w in self._sends:
             w.wait()
         self._sends = []
+
+    # -- skip tensors: direct rank-to-rank --------------------------------------------
+    def _skip_send(self, i: int, tracker: "_RankSkipTracker", cell: _Cell, first_time: bool) -> None:
+        """Ship this cell's remote stashes to the ranks that pop them (forward only; a recompute
+        refreshes the graph-attached tensors but sends nothing)."""
+        for key in self._skip_out_order:
+            t = tracker.outbox.get(key)
+            if t is None:
+                raise RuntimeError(f"skip '{key[1]}' crosses ranks and must be a tensor (got None)")
+            cell.skip_out[key] = t
+            if not first_time:
+                continue
+            dst = self.ranks[self._skip_out[key]]
+            spec = _Spec.of(t, cell.checkpointed and torch.is_grad_enabled())
+            known = self._cur.skip_sent.get((i, key))
+            if known is None:
+                self._send_meta([spec], dst, self.group)
+                self._cur.skip_sent[(i, key)] = spec
+            elif known != spec:
+                raise RuntimeError(f"shape of skip '{key[1]}' changed for an unchanged input; call reset() on every rank")
+            self._sends += self._p2p([dist.P2POp(dist.isend, t.detach().contiguous(), dst, self.group)])
+
+    def _skip_recv(self, i: int, cell: _Cell) -> None:
+        for key in self._skip_in_order:
+            src = self.ranks[self._skip_in[key]]
+            spec = self._cur.skip_recv.get((i, key))
+            if spec is None:
+                spec = self._cur.skip_recv[(i, key)] = self._recv_meta(src, self.group)[0]
+            t = torch.empty(spec.shape, dtype=spec.dtype, device=self.device)
+            for w in self._p2p([dist.P2POp(dist.irecv, t, src, self.group)]):
+                w.wait()
+            cell.skip_in[key] = t
+
+    def _skip_tracker(self, i: int, cell: _Cell) -> "_RankSkipTracker":
+        tr = _RankSkipTracker(self._skip_out, self._skip_in)
+        grad_on = torch.is_grad_enabled()
+        for key, t in cell.skip_in.items():
+            spec = self._cur.skip_recv[(i, key)]
+            leaf = t.detach().requires_grad_(spec.requires_grad and grad_on)
+            cell.skip_leaves[key] = leaf
+            tr.inbox[key] = leaf
+        return tr
+
+    def _skip_grads_recv(self, i: int, cell: _Cell) -> List[Tuple[Tensor, Tensor]]:
+        """Gradients of this cell's remote stashes, from the ranks that popped them."""
+        pairs = []
+        for key in reversed(self._skip_out_order):
+            spec = self._cur.skip_sent[(i, key)]
+            if not spec.requires_grad:
+                continue
+            src = self.ranks[self._skip_out[key]]
+            g = torch.empty(spec.shape, dtype=spec.dtype, device=self.device)
+            for w in self._p2p([dist.P2POp(dist.irecv, g, src, self.group)]):
+                w.wait()
+            t = cell.skip_out.get(key)
+            if t is not None and t.requires_grad:
+                pairs.append((t, g))
+        return pairs
+
+    def _skip_grads_send(self, i: int, cell: _Cell) -> None:
+        for key in reversed(self._skip_in_order):
+            spec = self._cur.skip_recv[(i, key)]
+            if not spec.requires_grad:
+                continue
+            leaf = cell.skip_leaves[key]
+            g = leaf.grad if leaf.grad is not None else torch.zeros_like(leaf)
+            dst = self.ranks[self._skip_in[key]]
+            self._sends += self._p2p([dist.P2POp(dist.isend, g.contiguous(), dst, self.group)])
+
+    # -- timeline ------------------------------------------------------------------
+    def _mark(self):
+        if not self.timeline:
+            return None
+        if self.device.type == "cuda":
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record(torch.cuda.current_stream(self.device))
+            return ev
+        return time.perf_counter()
+
+    def _elapsed_ms(self, a, b) -> float:
+        if a is None or b is None:
+            return 0.0
+        if self.device.type == "cuda":
+            return float(a.elapsed_time(b))
+        return (b - a) * 1e3
+
+    def _span(self, phase: str, a, b) -> None:
+        if self.timeline and a is not None and b is not None:
+            self._t_spans.append((phase, a, b))
+
+    def timeline_summary(self) -> Optional[List[Dict[str, float]]]:
+        """Collective.  Per stage, for the last step: milliseconds this rank's stream spent inside
+        forward cells, backward cells and recomputes (CUDA events on the rank's own stream; the marks sit
+        after the receive wait and before the send, so waiting for a neighbour is *not* busy time), the
+        span from its first forward cell to its last backward cell, and the measured bubble
+        ``1 - busy / span of stage 0`` — stage 0 starts first and ends last, so its span is the length of
+        the pipelined part of the step.  Compare with the ideal ``(n - 1) / (m + n - 1)`` of equal stages."""
+        if not self.timeline or not self._t_spans:
+            return None
+        if self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)
+        mine: Dict[str, float] = {"fwd_busy_ms": 0.0, "bwd_busy_ms": 0.0, "recompute_ms": 0.0}
+        for phase, a, b in self._t_spans:
+            mine[{"fwd": "fwd_busy_ms", "bwd": "bwd_busy_ms", "rec": "recompute_ms"}[phase]] += self._elapsed_ms(a, b)
+        mine["pipe_span_ms"] = self._elapsed_ms(self._t_spans[0][1], self._t_spans[-1][2])
+        gathered: List[Any] = [None] * self.n_stages
+        dist.all_gather_object(gathered, mine, group=self.group)
+        length = gathered[0]["pipe_span_ms"]
+        for g in gathered:
+            busy = g["fwd_busy_ms"] + g["bwd_busy_ms"] + g["recompute_ms"]
+            g["bubble"] = max(0.0, 1.0 - busy / length) if length > 0 else 0.0
+        return gathered
+
+    # -- forward -------------------------------------------------------------------
+    def _checkpoint_stop(self, m: int) -> int:
+        if not self.stage.training or not torch.is_grad_enabled():
+            return 0
+        basis = m if self.strict_except_last else self.chunks
+        return {"always": basis, "except_last": basis - 1, "never": 0}[self.checkpoint]
+
+    def _call(self, inputs: Tuple[Any, ...], tracker: Optional[SkipTracker] = None):
+        if tracker is None:
+            return self.stage(*inputs)
+        with use_skip_tracker(tracker):
+            return self.stage(*inputs)
+
+    def forward(self, *inputs: Any, num_microbatches: Optional[int] = None):
+        """Run the forward half of a step.  The first stage takes the mini-batch (split along
+        dim 0); later stages take no inputs — they learn the micro-batch count from the step header.
+        ``num_microbatches`` is accepted for compatibility and ignored."""
+        if self.is_first:
+            microbatch.check(self.device, *inputs)
+            batches = microbatch.scatter(*inputs, chunks=self.chunks)
+            m = len(batches)
+        else:
+            batches = []
+            m = -1
+        m = self._begin_step(inputs, m)
+        if self._mailboxes_wanted():
+            self._build_mailboxes()
+        self._fwd_seq += 1
+
+        stop = self._checkpoint_stop(m)
+        grad_on = torch.is_grad_enabled()
+        self._cells = []
+        self._out_leaves = []
+        self._t_spans = []
+        self.last_bubble = bubble_fraction(m, self.n_stages)
+        skips = self._has_skips
+
+        for i in range(m):
+            cell = _Cell()
+            if self.is_first:
+                b = batches[i]
+                values = (b.tensor,) if b.atomic else tuple(b.values)
+            else:
+                values = self._recv_forward(i)
+                if i + 1 < m:
+                    self._post_recv_forward(i + 1)      # next micro-batch's transfer overlaps this cell
+            cell.inputs = values
+            tracker = None
+            if skips:
+                self._skip_recv(i, cell)
+                tracker = self._skip_tracker(i, cell)
+
+            t0 = self._mark()
+            if i < stop:
+                cell.checkpointed = True
+                cell.cpu_rng = torch.get_rng_state()
+                if self.device.type == "cuda":
+                    cell.dev_rng = torch.cuda.get_rng_state(self.device)
+                with torch.no_grad(), enable_checkpointing(), seed_scope(cell.seed_base):
+                    out = self._call(values, tracker)
+            else:
+                out = self._call(values, tracker)
+            self._span("fwd", t0, self._mark())
+            outs = out if isinstance(out, tuple) else (out,)
+
+            if self.is_last:
+                leaves = tuple(o.detach().requires_grad_(o.is_floating_point() and grad_on)
+                               if torch.is_tensor(o) else o for o in outs)
+                self._out_leaves.append(leaves)
+                cell.outputs = outs if not cell.checkpointed else ()
+                cell.leaves = leaves
+            else:
+                # a checkpointed cell ran without a graph; its recompute will produce grad-requiring outputs
+                self._send_forward(i, outs, force_grad=cell.checkpointed and grad_on)
+                cell.outputs = outs if not cell.checkpointed else ()
+            if skips:
+                # after the boundary send: the popping rank first waits for its neighbour's activation, which
+                # (transitively) waits for the send above — the first step's blocking shape handshake of the
+                # skip must not sit in front of it
+                self._skip_send(i, tracker, cell, first_time=True)
+                if cell.checkpointed:
+                    cell.skip_out = {}
+            self._cells.append(cell)
+
+        self._drain_sends()
+        self._cur.steps += 1
+        if not self.is_last:
+            return LocalRRef(None)
+        gathered = microbatch.gather([Batch(l[0] if len(l) == 1 else l) for l in self._out_leaves])
+        return LocalRRef(gathered)
+
+    # -- backward ------------------------------------------------------------------
+    def backward(self, loss: Optional[Tensor] = None) -> None:
+        """Run the backward half.  On the last stage pass the loss computed from
+        ``forward``'s output; elsewhere pass nothing."""
+        from ..ops import wgrad          # pure-Python bookkeeping; no GPU needed to import
+        with wgrad.deferred():           # one wgrad GEMM per Linear for the whole mini-batch
+            self._backward(loss)
+
+    def _backward(self, loss: Optional[Tensor]) -> None:
+        cells = self._cells
+        self._bwd_seq += 1
+        skips = self._has_skips
+        if self.is_last:
+            if loss is None:
+                raise ValueError("the last stage must be given the loss")
+            loss.backward()
+
+        for i in reversed(range(len(cells))):
+            cell = cells[i]
+            if self.is_last:
+                grads = [l.grad if torch.is_tensor(l) else None for l in cell.leaves]
+                works = []
+            elif self._grads_by_mailbox(i):
+                grads, works = None, []             # fetched below, right where they are needed
+            else:
+                grads, works = self._early_grads.pop(i, None) or self._post_recv_grads(i)
+                if i > 0 and not self._grads_by_mailbox(i - 1):
+                    self._early_grads[i - 1] = self._post_recv_grads(i - 1)   # overlaps this cell's backward
+
+            if cell.checkpointed:
+                t0 = self._mark()
+                outs = self._recompute(i, cell)     # overlaps the gradient transfer
+                self._span("rec", t0, self._mark())
+            else:
+                outs = cell.outputs
+            for w in works:
+                w.wait()
+            if grads is None:
+                grads = self._recv_grads_mailbox(i)  # one kernel that waits for the peer's flag on this stream
+
+            pairs = [(o, g) for o, g in zip(outs, grads)
+                     if torch.is_tensor(o) and o.requires_grad and g is not None]
+            if skips:
+                pairs += self._skip_grads_recv(i, cell)
+            t0 = self._mark()
+            if pairs:
+                torch.autograd.backward([o for o, _ in pairs], [g for _, g in pairs])
+            self._span("bwd", t0, self._mark())
+            if not self.is_first:
+                self._send_grads(i, cell.inputs)
+            if skips:
+                self._skip_grads_send(i, cell)
+            cells[i] = _Cell()                      # drop the graph as early as possible
+            for hook in self.cell_backward_hooks:
+                hook(i)
+        self._drain_sends()
+        self._cells = []
+        self._out_leaves = []
+
+    def _recompute(self, i: int, cell: _Cell) -> Tuple[Any, ...]:
+        devices = [self.device] if self.device.type == "cuda" else []
+        tracker = self._skip_tracker(i, cell) if self._has_skips else None
+        with torch.random.fork_rng(devices):
+            torch.set_rng_state(cell.cpu_rng)
+            if cell.dev_rng is not None:
+                torch.cuda.set_rng_state(cell.dev_rng, self.device)
+            with torch.enable_grad(), enable_recomputing(), seed_scope(cell.seed_base):
+                out = self._call(cell.inputs, tracker)
+        if tracker is not None:
+            self._skip_send(i, tracker, cell, first_time=False)
+        return out if isinstance(out, tuple) else (out,)

@@ -17,12 +17,18 @@ __all__ = ["Namespace"]
 class Namespace(metaclass=abc.ABCMeta):
     """A unique, hashable, orderable token.  ``isolate(ns)`` on a skippable
     module scopes its stash/pop names to ``ns`` so two instances of the same
-    class do not collide."""
+    class do not collide.
 
-    __slots__ = ("_id",)
+    ``Namespace()`` is unique to the process that created it.  ``Namespace(key="block3")`` is the
+    same token in every process that uses the same key: the multi-process pipeline
+    (:class:`~pipe_b200.parallel.DistPipe`) needs that to pair a stash on one rank with its pop on
+    another, because each rank builds its own module objects."""
 
-    def __init__(self) -> None:
-        self._id = uuid.uuid4()
+    __slots__ = ("_id", "key")
+
+    def __init__(self, key: "str | None" = None) -> None:
+        self.key = None if key is None else str(key)
+        self._id = uuid.uuid4() if key is None else uuid.uuid5(uuid.NAMESPACE_OID, "pipe_b200.skip/" + self.key)
 
     def __repr__(self) -> str:
         return f"<Namespace '{self._id}'>"
