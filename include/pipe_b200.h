@@ -271,6 +271,43 @@ typedef struct pb2_encoder_layer {
 int pb2_encoder_layer_fwd(const pb2_encoder_layer* L, cudaStream_t stream);
 int pb2_encoder_layer_bwd(const pb2_encoder_layer* L, cudaStream_t stream);
 
+/* ---- a run of consecutive encoder layers (the layers of one pipeline stage): one host call per pass ----
+ * `layers` is a HOST array of n descriptors in which the per-layer constants are filled in: E, heads, FF,
+ * causal, eps, weight shadows and strides, biases, LayerNorm parameters, the gradient pointers
+ * (dg*, dbe*, db_*) and the wgrad stash bases / strides.  Everything per call comes from this struct: the
+ * run's input `x`, one slab `y` of n x [T, E] layer outputs (y[l] feeds layer l + 1; y[n-1] is the result),
+ * one slab `act` of pb2_encoder_stack_act_elems() bf16 elements for the saved activations, `stats` of
+ * n x 4T floats; for the backward additionally `dy`, `dx`, a scratch slab `tmp` of
+ * pb2_encoder_stack_tmp_elems() bf16 elements (kept alive until the side stream has passed it) and the
+ * column `stash_off` at which every linear of the run stacks this micro-batch's wgrad operands.
+ * All layers share E.  Same kernels, same order, same results as n calls of pb2_encoder_layer_fwd / _bwd.
+ * Reference counterpart: one stage's nn.Sequential of nn.TransformerEncoderLayer as run by a worker
+ * thread (pipeline.py:225-230, main.py:147-153); SURVEY.md §3.2, §7.4 item 2. */
+#define PB2_MAX_STACK_LAYERS 64
+typedef struct pb2_encoder_stack {
+    int n_layers;
+    const pb2_encoder_layer* layers;
+    int T, NB, S;
+    float drop_p;
+    const unsigned long long* seeds;   /* n seeds (host), or NULL when drop_p == 0 */
+    const void* x;
+    void* y;
+    void* act;
+    float* stats;
+    const void* dy;
+    void* dx;
+    void* tmp;
+    int stash_off;
+    void* workspace;
+    size_t workspace_bytes;
+    void* side_stream;
+} pb2_encoder_stack;
+
+size_t pb2_encoder_stack_act_elems(const pb2_encoder_layer* layers, int n, int T);
+size_t pb2_encoder_stack_tmp_elems(const pb2_encoder_layer* layers, int n, int T);
+int pb2_encoder_stack_fwd(const pb2_encoder_stack* s, cudaStream_t stream);
+int pb2_encoder_stack_bwd(const pb2_encoder_stack* s, cudaStream_t stream);
+
 /* `waiter` waits (on the device) for everything enqueued on `waited` so far; both on the current device. */
 int pb2_stream_wait_stream(cudaStream_t waiter, cudaStream_t waited);
 

@@ -115,3 +115,127 @@ extern "C" int pb2_encoder_layer_bwd(const pb2_encoder_layer* L, cudaStream_t st
     add(L->df, E, L->dyt_2, L->ld_stash_2, L->stash_off_2, L->db_2);
     return pb2_transpose_multi(&jobs, tstream);
 }
+
+// ---------------------------------------------------------------------------------------
+// A run of consecutive encoder layers of one pipeline stage as ONE host call per pass.
+//
+// With 75-token micro-batches a layer is ~80 us of GPU work forward, ~140 us backward, and the
+// Python side of a per-layer call (buffer allocation, descriptor fill, autograd bookkeeping) costs
+// about as much: a rank that owns two to sixteen layers was launch-bound, which stretched every
+// pipeline tick.  Here the caller passes the per-layer constants once (an array of
+// pb2_encoder_layer with weights, biases, norms, gradient and stash pointers filled in) plus one
+// slab per kind of buffer for the whole run; the per-layer pointers are carved out here.
+namespace {
+
+inline size_t act_elems(const pb2_encoder_layer& L, int T) { return static_cast<size_t>(T) * (7 * static_cast<size_t>(L.E) + L.FF); }
+inline size_t tmp_elems(const pb2_encoder_layer& L, int T) { return static_cast<size_t>(T) * (10 * static_cast<size_t>(L.E) + L.FF); }
+
+// forward activations of one layer inside the slab: qkv | a | o | x1 | hmid | f
+void carve_act(pb2_encoder_layer& d, char* base, int T) {
+    const size_t E = d.E, FF = d.FF, t = T;
+    d.qkv = base;               base += t * 3 * E * 2;
+    d.a = base;                 base += t * E * 2;
+    d.o = base;                 base += t * E * 2;
+    d.x1 = base;                base += t * E * 2;
+    d.hmid = base;              base += t * FF * 2;
+    d.f = base;
+}
+
+int check_stack(const pb2_encoder_stack* s, const char* who) {
+    if (!s || !s->layers || s->n_layers <= 0) { pb2::set_error("%s: empty stack", who); return -1; }
+    if (s->T != s->S * s->NB) { pb2::set_error("%s: T != S * NB", who); return -1; }
+    for (int l = 1; l < s->n_layers; ++l)
+        if (s->layers[l].E != s->layers[0].E) { pb2::set_error("%s: layers of a stack must share the model width", who); return -1; }
+    return 0;
+}
+
+}  // namespace
+
+extern "C" size_t pb2_encoder_stack_act_elems(const pb2_encoder_layer* layers, int n, int T) {
+    size_t total = 0;
+    for (int l = 0; l < n; ++l) total += act_elems(layers[l], T);
+    return total;
+}
+
+extern "C" size_t pb2_encoder_stack_tmp_elems(const pb2_encoder_layer* layers, int n, int T) {
+    size_t total = 0;
+    for (int l = 0; l < n; ++l) total += tmp_elems(layers[l], T);
+    return total;
+}
+
+extern "C" int pb2_encoder_stack_fwd(const pb2_encoder_stack* s, cudaStream_t stream) {
+    if (check_stack(s, "pb2_encoder_stack_fwd")) return -1;
+    const int T = s->T;
+    const size_t E = s->layers[0].E;
+    char* act = static_cast<char*>(s->act);
+    char* y = static_cast<char*>(s->y);
+    for (int l = 0; l < s->n_layers; ++l) {
+        pb2_encoder_layer d = s->layers[l];
+        d.T = T; d.NB = s->NB; d.S = s->S;
+        d.drop_p = s->drop_p;
+        d.seed = s->seeds ? s->seeds[l] : 0ull;
+        d.x = l == 0 ? s->x : y + static_cast<size_t>(l - 1) * T * E * 2;
+        d.y = y + static_cast<size_t>(l) * T * E * 2;
+        carve_act(d, act, T);
+        act += act_elems(d, T) * 2;
+        float* st = s->stats + static_cast<size_t>(l) * 4 * T;
+        d.mean1 = st; d.rstd1 = st + T; d.mean2 = st + 2 * T; d.rstd2 = st + 3 * T;
+        d.workspace = s->workspace; d.workspace_bytes = s->workspace_bytes;
+        d.prefetch = 0; d.next_weight = nullptr; d.next_weight_bytes = 0;
+        if (pb2_encoder_layer_fwd(&d, stream)) return -1;
+    }
+    return 0;
+}
+
+extern "C" int pb2_encoder_stack_bwd(const pb2_encoder_stack* s, cudaStream_t stream) {
+    if (check_stack(s, "pb2_encoder_stack_bwd")) return -1;
+    const int T = s->T, n = s->n_layers;
+    const size_t E = s->layers[0].E;
+    char* y = static_cast<char*>(s->y);
+    // slab offsets of every layer (the walk is last layer first)
+    size_t act_off[PB2_MAX_STACK_LAYERS], tmp_off[PB2_MAX_STACK_LAYERS];
+    if (n > PB2_MAX_STACK_LAYERS) { pb2::set_error("pb2_encoder_stack_bwd: more than %d layers", PB2_MAX_STACK_LAYERS); return -1; }
+    size_t a = 0, t = 0;
+    for (int l = 0; l < n; ++l) {
+        act_off[l] = a; tmp_off[l] = t;
+        a += act_elems(s->layers[l], T) * 2;
+        t += tmp_elems(s->layers[l], T) * 2;
+    }
+    for (int l = n - 1; l >= 0; --l) {
+        pb2_encoder_layer d = s->layers[l];
+        d.T = T; d.NB = s->NB; d.S = s->S;
+        d.drop_p = s->drop_p;
+        d.seed = s->seeds ? s->seeds[l] : 0ull;
+        d.x = l == 0 ? s->x : y + static_cast<size_t>(l - 1) * T * E * 2;
+        d.y = y + static_cast<size_t>(l) * T * E * 2;
+        carve_act(d, static_cast<char*>(s->act) + act_off[l], T);
+        float* st = s->stats + static_cast<size_t>(l) * 4 * T;
+        d.mean1 = st; d.rstd1 = st + T; d.mean2 = st + 2 * T; d.rstd2 = st + 3 * T;
+        // scratch of this layer: dr2 | df | dz1 | dx1 | dr1 | do | da | dqkv | dx
+        char* b = static_cast<char*>(s->tmp) + tmp_off[l];
+        const size_t FF = d.FF, tt = T;
+        d.dr2 = b;  b += tt * E * 2;
+        d.df = b;   b += tt * E * 2;
+        d.dz1 = b;  b += tt * FF * 2;
+        d.dx1 = b;  b += tt * E * 2;
+        d.dr1 = b;  b += tt * E * 2;
+        d.do_ = b;  b += tt * E * 2;
+        d.da = b;   b += tt * E * 2;
+        d.dqkv = b; b += tt * 3 * E * 2;
+        void* dx_here = l == 0 ? s->dx : static_cast<void*>(b);
+        // the gradient entering layer l is what layer l + 1 wrote into its own dx slot
+        if (l == n - 1) {
+            d.dy = s->dy;
+        } else {
+            const pb2_encoder_layer& up = s->layers[l + 1];
+            d.dy = static_cast<char*>(s->tmp) + tmp_off[l + 1] + tt * (9 * E + up.FF) * 2;
+        }
+        d.dx = dx_here;
+        d.stash_off_qkv = d.stash_off_o = d.stash_off_1 = d.stash_off_2 = s->stash_off;
+        d.workspace = s->workspace; d.workspace_bytes = s->workspace_bytes;
+        d.prefetch = 0; d.next_weight = nullptr; d.next_weight_bytes = 0;
+        d.side_stream = s->side_stream;
+        if (pb2_encoder_layer_bwd(&d, stream)) return -1;
+    }
+    return 0;
+}
