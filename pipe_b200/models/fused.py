@@ -135,6 +135,7 @@ class _FusedBase(nn.Module):
         # masters may have been replaced / moved: re-bind shadows and wgrad stashes, drop caches
         self.__dict__.pop("_pb2_params", None)
         self.__dict__.pop("_pb2_desc", None)
+        self.__dict__["_pb2_epoch"] = self.__dict__.get("_pb2_epoch", 0) + 1
         self._rebind()
         return out
 
@@ -145,16 +146,6 @@ class _FusedBase(nn.Module):
 # ======================================================================================
 # encoder layer
 # ======================================================================================
-class _Chain(threading.local):
-    """Which fused layer ran forward last on this thread: lets every layer learn its successor and
-    predecessor at run time, so its executor can prefetch the neighbour's first weight into L2."""
-
-    def __init__(self) -> None:
-        self.last: Optional["FusedEncoderLayer"] = None
-
-
-_chain = _Chain()
-
 # The launch that stacks x^T / dy^T for the deferred weight gradients runs on a stream of its own: nothing in
 # backward reads its results, so on the main stream it was ~6.4 us plus a launch dependency between every layer's
 # QKV dgrad and the next layer's LayerNorm backward.  PB2_SIDE_TRANSPOSE=0 puts it back in line.
@@ -169,11 +160,6 @@ def _side_stream(device: torch.device) -> "torch.cuda.Stream":
         if st is None:
             st = _side_streams[device.index] = torch.cuda.Stream(device)
         return st
-# Measured on B200 (config 3, 1 GPU): prefetching one GEMM ahead made the step 25 % SLOWER (40.0 -> 49.8 ms):
-# the extra launches serialise the PDL chain and the prefetched lines compete with the streaming GEMM for
-# HBM and L2.  Kept as an opt-in experiment (PB2_PREFETCH=1), off by default.
-_PREFETCH = os.environ.get("PB2_PREFETCH", "0") == "1"
-
 
 class _EncoderLayerFn(torch.autograd.Function):
     """Forward and backward of the whole layer, each one call into the C++ layer executor
@@ -201,19 +187,6 @@ class _EncoderLayerFn(torch.autograd.Function):
         d.T, d.NB, d.S = T, NB, S
         d.drop_p, d.seed = p, seed
         d.x, d.y = x2.data_ptr(), y.data_ptr()
-        # learn the layer order on this thread (wraps around from the stage's last layer to its first,
-        # which is what the next micro-batch runs), then prefetch one GEMM / one layer ahead
-        prev = _chain.last
-        if prev is not None and prev is not layer:
-            prev.__dict__["_pb2_next"] = layer
-            layer.__dict__["_pb2_prev"] = prev
-        _chain.last = layer
-        d.prefetch = int(_PREFETCH)
-        nxt = layer.__dict__.get("_pb2_next")
-        if _PREFETCH and nxt is not None and nxt is not layer:
-            w_next, _ = nxt._sh("qkv")
-            if w_next.device == dev:
-                d.next_weight, d.next_weight_bytes = w_next.data_ptr(), w_next.numel() * 2
         base, at = act.data_ptr(), 0
         for name, w in zip(("qkv", "a", "o", "x1", "hmid", "f"), widths):
             setattr(d, name, base + at * 2)
@@ -254,12 +227,6 @@ class _EncoderLayerFn(torch.autograd.Function):
         d.T, d.NB, d.S = T, NB, S
         d.drop_p, d.seed = p, seed
         d.x, d.dy, d.dx = x2.data_ptr(), dy2.data_ptr(), dx.data_ptr()
-        d.prefetch = int(_PREFETCH)
-        before = layer.__dict__.get("_pb2_prev")          # runs its backward right after this one
-        if _PREFETCH and before is not None and before is not layer:
-            _, wt_prev = before._sh("l2")
-            if wt_prev.device == dev:
-                d.next_weight, d.next_weight_bytes = wt_prev.data_ptr(), wt_prev.numel() * 2
         base, at = act.data_ptr(), 0
         for name, w in zip(("qkv", "a", "o", "x1", "hmid", "f"), (3 * E, E, E, E, FF, E)):
             setattr(d, name, base + at * 2)
@@ -368,6 +335,11 @@ class FusedEncoderLayer(_FusedBase):
         y = F.layer_norm(x1 + F.dropout(f, p, True), (E,), self.norm2.weight, self.norm2.bias, self.norm2.eps)
         return y.to(x.dtype)
 
+    @staticmethod
+    def pb2_make_chain(layers: "List[FusedEncoderLayer]") -> "EncoderStack":
+        """Called by ``PipeSequential`` for a run of consecutive layers of this class."""
+        return EncoderStack(layers)
+
     def forward(self, x: Tensor, *extra: Any):
         if not x.is_cuda:
             y = self.reference_forward(x)
@@ -377,6 +349,190 @@ class FusedEncoderLayer(_FusedBase):
             params = self.__dict__["_pb2_params"] = tuple(self.parameters())
         y = _EncoderLayerFn.apply(x, self, *params)
         return (y, *extra) if extra else y
+
+
+# ======================================================================================
+# a run of encoder layers: one native call per (stage, micro-batch) cell and pass
+# ======================================================================================
+_STACK = os.environ.get("PB2_LAYER_STACK", "1") != "0"
+
+
+class EncoderStack:
+    """Executes consecutive :class:`FusedEncoderLayer` modules of one stage through
+    ``pb2_encoder_stack_fwd / _bwd`` (``csrc/layer.cu``): the per-layer constants live in a cached
+    array of launch descriptors, each pass allocates one slab per kind of buffer for the whole run,
+    and the Python cost of a cell no longer grows with the number of layers in the stage — the
+    single-process ``Pipe`` shares one interpreter between all stages, and a one-rank-per-stage
+    pipeline stretches every tick by whatever its slowest host needs (reference: the worker thread
+    running ``partition(*inputs)``, ``pipeline.py:225-230``).
+
+    Not a module: the layers stay where they are (state-dict keys unchanged); this object only
+    caches descriptors.  ``PipeSequential`` builds one per run of chainable layers."""
+
+    def __init__(self, layers: "List[FusedEncoderLayer]") -> None:
+        from ..ops.wgrad import StackStash
+        self.layers = list(layers)
+        self.n = len(self.layers)
+        first = self.layers[0]
+        if any(l.d_model != first.d_model for l in self.layers):
+            raise ValueError("layers of a stack must share d_model")
+        self.E = first.d_model
+        self.anchor = first.self_attn.in_proj_weight
+        self.stash = StackStash([l._lg(k) for l in self.layers for k in ("qkv", "o", "l1", "l2")])
+        self._epoch_seen = self._layer_epoch()
+        self._static: Optional[Dict[str, Any]] = None
+        self._sizes: Dict[int, Tuple[int, int]] = {}
+
+    # -- eligibility ---------------------------------------------------------------
+    def usable(self, x: Tensor) -> bool:
+        if not (_STACK and x.is_cuda and self.n <= 64):
+            return False
+        t0, p0 = self.layers[0].training, self.layers[0].dropout
+        return all(l.training == t0 and l.dropout == p0 for l in self.layers)
+
+    # -- cached per-layer constants ---------------------------------------------------
+    def _layer_epoch(self) -> int:
+        return sum(l.__dict__.get("_pb2_epoch", 0) for l in self.layers)
+
+    def _grad_params(self, layer: "FusedEncoderLayer"):
+        at = layer.self_attn
+        return (layer.norm1.weight, layer.norm1.bias, layer.norm2.weight, layer.norm2.bias,
+                at.in_proj_bias, at.out_proj.bias, layer.linear1.bias, layer.linear2.bias)
+
+    def refresh(self) -> None:
+        """Layers that were moved / cast re-create their shadows and wgrad stashes: follow them."""
+        from ..ops.wgrad import StackStash
+        e = self._layer_epoch()
+        if e != self._epoch_seen:
+            self._epoch_seen = e
+            self.stash = StackStash([l._lg(k) for l in self.layers for k in ("qkv", "o", "l1", "l2")])
+            self._static = None
+        for sh in self._shadows():
+            if sh.param._version != sh.version:
+                sh.ensure()
+
+    def _shadows(self):
+        got = self.__dict__.get("_shadow_list")
+        if got is None or got[0] != self._epoch_seen:
+            got = (self._epoch_seen, [sh for l in self.layers for sh in l.pb2_shadows()])
+            self.__dict__["_shadow_list"] = got
+        return got[1]
+
+    def static(self, device: torch.device, with_grads: bool):
+        """The descriptor array, rebuilt when a layer was moved, a stash was re-allocated or a
+        gradient buffer was replaced (``zero_grad(set_to_none=True)`` of a stock optimizer)."""
+        from ..ops.wgrad import stash_epoch
+        c = self._static
+        if (c is not None and c["device"] == device.index and (c["with_grads"] or not with_grads)
+                and (not c["with_grads"] or (c["stash_epoch"] == stash_epoch()
+                                             and all(p.grad is g for p, g in c["pairs"])))):
+            return c["arr"]
+        arr = (_lib.EncoderLayerDesc * self.n)()
+        pairs = []
+        for k, layer in enumerate(self.layers):
+            d = layer._desc(device)
+            if with_grads:
+                n1w, n1b, n2w, n2b, bq, bo, b1, b2 = self._grad_params(layer)
+                d.dg1, d.dbe1 = ensure_grad(n1w).data_ptr(), ensure_grad(n1b).data_ptr()
+                d.dg2, d.dbe2 = ensure_grad(n2w).data_ptr(), ensure_grad(n2b).data_ptr()
+                for name, bias, lk in (("qkv", bq, "qkv"), ("o", bo, "o"), ("1", b1, "l1"), ("2", b2, "l2")):
+                    lg = layer._lg(lk)
+                    setattr(d, "db_" + name, ensure_grad(bias).data_ptr())
+                    setattr(d, "xt_" + name, lg.xt.data_ptr())
+                    setattr(d, "dyt_" + name, lg.dyt.data_ptr())
+                    setattr(d, "ld_stash_" + name, lg.xt.stride(0))
+                pairs += [(p, p.grad) for p in (n1w, n1b, n2w, n2b, bq, bo, b1, b2)]
+            arr[k] = d
+        self._static = {"device": device.index, "with_grads": with_grads, "stash_epoch": stash_epoch(),
+                        "arr": arr, "pairs": pairs}
+        self._sizes.clear()
+        return arr
+
+    def sizes(self, arr, T: int) -> Tuple[int, int]:
+        got = self._sizes.get(T)
+        if got is None:
+            lib = _lib.load()
+            got = (int(lib.pb2_encoder_stack_act_elems(arr, ctypes.c_int(self.n), ctypes.c_int(T))),
+                   int(lib.pb2_encoder_stack_tmp_elems(arr, ctypes.c_int(self.n), ctypes.c_int(T))))
+            self._sizes[T] = got
+        return got
+
+    def __call__(self, x: Tensor) -> Tensor:
+        return _StackFn.apply(x, self, self.anchor)
+
+
+class _StackFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x: Tensor, stack: EncoderStack, anchor: Tensor) -> Tensor:  # type: ignore[override]
+        S, NB, E = x.shape
+        T = S * NB
+        n = stack.n
+        x2 = x.contiguous().view(T, E)
+        if x2.dtype != torch.bfloat16:
+            x2 = x2.to(torch.bfloat16)
+        first = stack.layers[0]
+        p = first.dropout if first.training else 0.0
+        seeds = (ctypes.c_ulonglong * n)(*[F2.draw_seed() for _ in range(n)]) if p > 0 else None
+        dev = x2.device
+        stack.refresh()
+        arr = stack.static(dev, with_grads=False)
+        act_elems, _ = stack.sizes(arr, T)
+        act = torch.empty(act_elems, dtype=torch.bfloat16, device=dev)
+        stats = torch.empty(4 * T * n, dtype=torch.float32, device=dev)
+        ys = torch.empty((n, S, NB, E), dtype=torch.bfloat16, device=dev)
+        stream = _lib.raw_stream(dev)
+        ws = workspace(dev, stream)
+        c = _lib.EncoderStackDesc()
+        c.n_layers, c.layers = n, ctypes.addressof(arr)
+        c.T, c.NB, c.S, c.drop_p = T, NB, S, p
+        c.seeds = ctypes.addressof(seeds) if seeds is not None else None
+        c.x, c.y, c.act, c.stats = x2.data_ptr(), ys.data_ptr(), act.data_ptr(), stats.data_ptr()
+        c.workspace, c.workspace_bytes = ws.data_ptr(), ws.numel()
+        with _lib.on_device(dev):
+            rc = _lib.load().pb2_encoder_stack_fwd(ctypes.byref(c), ctypes.c_void_p(stream))
+        _lib.check(rc, "pb2_encoder_stack_fwd")
+        ctx.stack = stack
+        ctx.meta = (S, NB, E, p, seeds)
+        ctx.save_for_backward(x2, ys, act, stats)
+        return ys[n - 1]
+
+    @staticmethod
+    def backward(ctx, dy: Tensor):  # type: ignore[override]
+        stack: EncoderStack = ctx.stack
+        S, NB, E, p, seeds = ctx.meta
+        T = S * NB
+        n = stack.n
+        x2, ys, act, stats = ctx.saved_tensors
+        dev = x2.device
+        dy2 = dy.contiguous().view(T, E)
+        if dy2.dtype != torch.bfloat16:
+            dy2 = dy2.to(torch.bfloat16)
+        stream = _lib.raw_stream(dev)
+        stack.refresh()
+        off = stack.stash.reserve(T, dev, stream)          # may (re)allocate the stacks: before static()
+        arr = stack.static(dev, with_grads=True)
+        _, tmp_elems = stack.sizes(arr, T)
+        tmp = torch.empty(tmp_elems, dtype=torch.bfloat16, device=dev)
+        dx = torch.empty((S, NB, E), dtype=torch.bfloat16, device=dev)
+        ws = workspace(dev, stream)
+        side = _side_stream(dev) if _SIDE_TRANSPOSE else None
+        c = _lib.EncoderStackDesc()
+        c.n_layers, c.layers = n, ctypes.addressof(arr)
+        c.T, c.NB, c.S, c.drop_p = T, NB, S, p
+        c.seeds = ctypes.addressof(seeds) if seeds is not None else None
+        c.x, c.y, c.act, c.stats = x2.data_ptr(), ys.data_ptr(), act.data_ptr(), stats.data_ptr()
+        c.dy, c.dx, c.tmp, c.stash_off = dy2.data_ptr(), dx.data_ptr(), tmp.data_ptr(), off
+        c.workspace, c.workspace_bytes = ws.data_ptr(), ws.numel()
+        c.side_stream = side.cuda_stream if side is not None else None
+        with _lib.on_device(dev):
+            rc = _lib.load().pb2_encoder_stack_bwd(ctypes.byref(c), ctypes.c_void_p(stream))
+        _lib.check(rc, "pb2_encoder_stack_bwd")
+        if side is not None:
+            for t in (x2, ys, act, tmp):
+                t.record_stream(side)
+            from ..ops import wgrad as _wgrad
+            _wgrad.note_side_stream(dev, stream, side)
+        return dx, None, None
 
 
 # ======================================================================================

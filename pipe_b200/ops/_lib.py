@@ -65,6 +65,16 @@ class EncoderLayerDesc(ctypes.Structure):
     )
 
 
+class EncoderStackDesc(ctypes.Structure):
+    """Mirror of ``pb2_encoder_stack`` (include/pipe_b200.h)."""
+    _fields_ = [
+        ("n_layers", _ci), ("layers", _vp), ("T", _ci), ("NB", _ci), ("S", _ci), ("drop_p", _cf),
+        ("seeds", _vp), ("x", _vp), ("y", _vp), ("act", _vp), ("stats", _vp), ("dy", _vp), ("dx", _vp),
+        ("tmp", _vp), ("stash_off", _ci), ("workspace", _vp), ("workspace_bytes", ctypes.c_size_t),
+        ("side_stream", _vp),
+    ]
+
+
 def load() -> ctypes.CDLL:
     """Load the native library (once).  Raises :class:`NativeUnavailable` with a
     build hint when it is missing — never falls back silently."""
@@ -82,6 +92,8 @@ def load() -> ctypes.CDLL:
         lib.pb2_last_error.restype = ctypes.c_char_p
         lib.pb2_launch_count.restype = ctypes.c_longlong
         lib.pb2_gemm_workspace_bytes.restype = ctypes.c_size_t
+        lib.pb2_encoder_stack_act_elems.restype = ctypes.c_size_t
+        lib.pb2_encoder_stack_tmp_elems.restype = ctypes.c_size_t
         _lib = lib
     return _lib
 

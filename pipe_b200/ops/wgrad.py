@@ -30,7 +30,7 @@ from torch import Tensor, nn
 from . import _lib
 from .gemm import gemm_nt
 
-__all__ = ["LinearGrad", "deferred", "outer_backward", "flush_pending", "ensure_grad"]
+__all__ = ["LinearGrad", "StackStash", "deferred", "outer_backward", "flush_pending", "ensure_grad", "stash_epoch"]
 
 _lock = threading.RLock()
 _pending: "Dict[int, LinearGrad]" = {}
@@ -55,6 +55,15 @@ def wait_side_streams(device: Optional[torch.device] = None) -> None:
         with torch.cuda.device(index):
             rc = _lib.load().pb2_stream_wait_stream(ctypes.c_void_p(main), ctypes.c_void_p(side.cuda_stream))
         _lib.check(rc, "pb2_stream_wait_stream")
+
+# bumped whenever any LinearGrad (re)allocates its stacks: cached descriptors that hold stash pointers
+# compare it to know when to rebuild
+_stash_epoch = 0
+
+
+def stash_epoch() -> int:
+    return _stash_epoch
+
 
 _defer_depth = 0
 _nested_depth = 0
@@ -90,6 +99,8 @@ class LinearGrad:
             dev = self.weight.device
             if self.used and dev.type == "cuda":
                 wait_side_streams(dev)          # the columns copied below may still be in flight on a side stream
+            global _stash_epoch
+            _stash_epoch += 1
             xt = torch.zeros((in_f, new_cap), dtype=torch.bfloat16, device=dev)
             dyt = torch.zeros((out_f, new_cap), dtype=torch.bfloat16, device=dev)
             if self.used:
@@ -139,6 +150,47 @@ class LinearGrad:
             w._pb2_fresh = False
             w._pb2_sumsq_done = normsq is not None
         self.used = 0
+
+
+class StackStash:
+    """One column reservation per micro-batch for ALL linears of a run of layers.
+
+    Every linear of a stage's layer run sees the same tokens in the same order, so their stacks
+    fill in lock-step; reserving per linear (4 per layer, lock + bookkeeping each) was a visible
+    share of the host time of a backward cell.  The fast path is a handful of attribute writes."""
+
+    def __init__(self, lgs: "List[LinearGrad]") -> None:
+        self.lgs = list(lgs)
+        self._items = {id(lg): lg for lg in self.lgs}
+        self.cap = 0
+        self.epoch = -1
+
+    def reserve(self, tokens: int, device: torch.device, stream: int) -> int:
+        """Returns the column offset shared by every linear of the run."""
+        with _lock:
+            lgs = self.lgs
+            used = lgs[0].used
+            need = used + tokens
+            if self.epoch != _stash_epoch or need > self.cap:
+                offs = {lg._reserve(tokens) for lg in lgs}
+                if len(offs) != 1:
+                    raise RuntimeError("the linears of a layer run were used unevenly within one step "
+                                       "(some through the per-layer path): cannot share a stash offset")
+                self.cap = min(lg.xt.size(1) for lg in lgs)
+                self.epoch = _stash_epoch
+                for lg in lgs:
+                    lg.stream = stream
+                    if lg.bias is not None:
+                        ensure_grad(lg.bias)
+            else:
+                if lgs[-1].used != used:
+                    raise RuntimeError("the linears of a layer run were used unevenly within one step")
+                for lg in lgs:
+                    lg.used = need
+                    lg.stream = stream
+            _pending.update(self._items)
+            _arm()
+        return used
 
 
 def _arm() -> None:

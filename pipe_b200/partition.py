@@ -52,9 +52,54 @@ class PipeSequential(nn.Sequential):
     is passed as one argument."""
 
     def forward(self, *inputs: Any):  # type: ignore[override]
-        for layer in self:
-            inputs = layer(*inputs) if isinstance(inputs, tuple) else layer(inputs)
+        for step in self._plan():
+            if type(step) is tuple:
+                inputs = _run_chain(step, inputs)
+            else:
+                inputs = step(*inputs) if isinstance(inputs, tuple) else step(inputs)
         return inputs
+
+    def _plan(self):
+        """The stage's layers, with every run of two or more consecutive *chainable* layers (a class
+        that offers ``pb2_make_chain``: the fused encoder layer) replaced by ``(chain, layers)`` so the
+        run executes as one native call per pass.  Rebuilt when the children change."""
+        mods = tuple(self._modules.values())
+        cached = self.__dict__.get("_pb2_plan")
+        if cached is not None and cached[0] == tuple(map(id, mods)):
+            return cached[1]
+        plan: List[Any] = []
+        run: List[nn.Module] = []
+
+        def close() -> None:
+            if len(run) >= 2:
+                plan.append((type(run[0]).pb2_make_chain(list(run)), tuple(run)))
+            else:
+                plan.extend(run)
+            run.clear()
+
+        for m in mods:
+            if hasattr(type(m), "pb2_make_chain") and (not run or type(run[0]) is type(m)):
+                run.append(m)
+            else:
+                close()
+                if hasattr(type(m), "pb2_make_chain"):
+                    run.append(m)
+                else:
+                    plan.append(m)
+        close()
+        self.__dict__["_pb2_plan"] = (tuple(map(id, mods)), plan)
+        return plan
+
+
+def _run_chain(step, inputs):
+    chain, layers = step
+    x, extra = (inputs[0], inputs[1:]) if isinstance(inputs, tuple) else (inputs, ())
+    if torch.is_tensor(x) and chain.usable(x):
+        y = chain(x)
+        return (y, *extra) if extra else y
+    for layer in layers:
+        inputs = layer(*inputs) if isinstance(inputs, tuple) else layer(inputs)
+    return inputs
 
 
 class WithDevice(nn.Module):
