@@ -136,9 +136,17 @@ typedef struct pb2_transpose_job {
     float* colsum;        /* optional fp32 [C]: += scale * column sums */
     float scale;
 } pb2_transpose_job;
+#define PB2_MAX_PEERS 7
 typedef struct pb2_transpose_jobs {
     pb2_transpose_job job[PB2_MAX_TRANSPOSES];
     int count;
+    /* Replicated destinations (Pipe-inside-DDP hybrid): every element stored to a job's `dst` is also stored at
+     * the same address + peer_delta[q] bytes, q < n_peers — the same slot of the symmetric wgrad stash in each
+     * data-parallel replica's memory, mapped into this process.  The gradient "all-reduce" of the weight matrices
+     * then happens inside the wgrad GEMM: K runs over all replicas' tokens and the tensor core's fp32 accumulator
+     * is the reduction (see pb2_group_barrier for the ordering).  n_peers = 0: local only. */
+    int n_peers;
+    long long peer_delta[PB2_MAX_PEERS];
 } pb2_transpose_jobs;
 int pb2_transpose_multi(const pb2_transpose_jobs* jobs, cudaStream_t stream);
 
@@ -210,6 +218,14 @@ int pb2_refresh_shadows(const pb2_adam_tensor* table_dev, int n_tensors, int tot
  * (optional, local, n elements) holds a bf16 copy.
  * Reference counterpart: none in code (DDP is only mentioned, pipe.py:290-293); baseline = NCCL
  * all-reduce.  SURVEY.md K18. */
+/* Barrier among the ranks of a replica group, as one tiny kernel on `stream`: everything this rank's earlier
+ * kernels on the stream stored into peers' memory is visible to a peer's kernels that follow the peer's own
+ * barrier call.  `peer_pads[q]` is rank q's signal pad (pb2_allreduce_pad_bytes(), zeroed once) as mapped here;
+ * `epoch` is non-zero and grows by one per call on every rank; `phase` (0 or 1) selects one of two independent
+ * flag sets so that two barriers can alternate.  A missing peer trips the watchdog trap.
+ * No counterpart in the reference. */
+int pb2_group_barrier(void* const* peer_pads, int world, int rank, unsigned int epoch, int phase, cudaStream_t stream);
+
 int pb2_allreduce_max_ctas(void);
 size_t pb2_allreduce_pad_bytes(void);
 int pb2_allreduce_f32(float* const* peer_bufs, void* const* peer_pads, float* multicast, int world, int rank,
@@ -266,6 +282,10 @@ typedef struct pb2_encoder_layer {
      * keeps x, the activation buffer and the scratch buffer alive until that stream has passed this point,
      * and orders whatever consumes the stacks / bias gradients after it (pb2_stream_wait_stream). */
     void* side_stream;
+    /* optional (backward, hybrid): replicate the stacked wgrad operands into the data-parallel peers' stashes
+     * (same meaning as in pb2_transpose_jobs) */
+    int n_peers;
+    long long peer_delta[PB2_MAX_PEERS];
 } pb2_encoder_layer;
 
 int pb2_encoder_layer_fwd(const pb2_encoder_layer* L, cudaStream_t stream);

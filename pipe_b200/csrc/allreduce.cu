@@ -180,15 +180,28 @@ allreduce_kernel(const ArArgs a) {
     cross_gpu_barrier(a, 1);                                   // every peer's pushes have landed here
 
     if (a.cast_out) {
-        // local epilogue: bf16 copy of the full reduced buffer (what a bf16 consumer would read)
+        // local epilogue: bf16 copy of the full reduced buffer (what a bf16 consumer would read).
+        // The barrier above pairs CTA b here with CTA b on every peer and nothing else, so this CTA may
+        // only read what CTA b of some peer pushed: walk every peer's slice with the producers' own
+        // element mapping (offset within the slice = (b * threads + t) * 4 + trip * stride).
         const float* mine = a.bufs[a.rank];
-        for (size_t i = (static_cast<size_t>(blockIdx.x) * kArThreads + threadIdx.x) * 4; i < a.n; i += stride) {
-            const float4 v = __ldcg(reinterpret_cast<const float4*>(mine + i));
-            __nv_bfloat162* o = reinterpret_cast<__nv_bfloat162*>(a.cast_out + i);
-            o[0] = __floats2bfloat162_rn(v.x, v.y);
-            o[1] = __floats2bfloat162_rn(v.z, v.w);
+        for (int q = 0; q < a.world; ++q) {
+            const size_t base = slice * q;
+            for (size_t off = (static_cast<size_t>(blockIdx.x) * kArThreads + threadIdx.x) * 4; off < slice; off += stride) {
+                const float4 v = __ldcg(reinterpret_cast<const float4*>(mine + base + off));
+                __nv_bfloat162* o = reinterpret_cast<__nv_bfloat162*>(a.cast_out + base + off);
+                o[0] = __floats2bfloat162_rn(v.x, v.y);
+                o[1] = __floats2bfloat162_rn(v.z, v.w);
+            }
         }
     }
+}
+
+// One CTA: the flag exchange of cross_gpu_barrier on its own, for protocols whose data moves in other kernels
+// (the replicated wgrad stash: pushes happen in the transpose kernels, the consumer is the wgrad GEMM).
+__global__ void __launch_bounds__(32)
+group_barrier_kernel(const ArArgs a, const int phase) {
+    cross_gpu_barrier(a, phase);
 }
 
 }  // namespace pb2
@@ -198,6 +211,27 @@ using namespace pb2;
 extern "C" int pb2_allreduce_max_ctas(void) { return kArMaxCtas; }
 extern "C" size_t pb2_allreduce_pad_bytes(void) {
     return static_cast<size_t>(2) * kArMaxCtas * kArMaxWorld * sizeof(uint32_t);
+}
+
+extern "C" int pb2_group_barrier(void* const* peer_pads, int world, int rank, unsigned int epoch, int phase,
+                                 cudaStream_t stream) {
+    if (world < 1 || world > kArMaxWorld || rank < 0 || rank >= world) {
+        set_error("pb2_group_barrier: world %d / rank %d out of range (max world %d)", world, rank, kArMaxWorld);
+        return -1;
+    }
+    if (epoch == 0 || phase < 0 || phase > 1) { set_error("pb2_group_barrier: epoch must be non-zero, phase 0 or 1"); return -1; }
+    ArArgs a;
+    memset(&a, 0, sizeof(a));
+    for (int q = 0; q < world; ++q) {
+        if (!peer_pads[q]) { set_error("pb2_group_barrier: null pad %d", q); return -1; }
+        a.pads[q] = static_cast<uint32_t*>(peer_pads[q]);
+    }
+    a.world = world; a.rank = rank; a.epoch = epoch;
+    a.spin_budget = 4000000000ull;
+    // uses CTA slot 0 of the pad: give the barrier a pad of its own, not one an all-reduce is using
+    group_barrier_kernel<<<1, 32, 0, stream>>>(a, phase);
+    PB2_LAUNCHED("group_barrier_kernel");
+    return 0;
 }
 
 extern "C" int pb2_allreduce_f32(float* const* peer_bufs, void* const* peer_pads, float* multicast, int world,

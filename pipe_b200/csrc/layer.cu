@@ -113,6 +113,8 @@ extern "C" int pb2_encoder_layer_bwd(const pb2_encoder_layer* L, cudaStream_t st
     add(L->dz1, FF, L->dyt_1, L->ld_stash_1, L->stash_off_1, L->db_1);
     add(L->hmid, FF, L->xt_2, L->ld_stash_2, L->stash_off_2, nullptr);
     add(L->df, E, L->dyt_2, L->ld_stash_2, L->stash_off_2, L->db_2);
+    jobs.n_peers = L->n_peers;
+    for (int q = 0; q < L->n_peers && q < PB2_MAX_PEERS; ++q) jobs.peer_delta[q] = L->peer_delta[q];
     return pb2_transpose_multi(&jobs, tstream);
 }
 

@@ -448,7 +448,14 @@ transpose_multi_kernel(const pb2_transpose_jobs jobs) {
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
             const int c = c0 + ty + k * 8, r = r0 + tx;
-            if (c < j.C && r < j.R) dst[static_cast<size_t>(c) * j.ld_dst + r] = tile[tx][ty + k * 8];
+            if (c < j.C && r < j.R) {
+                __nv_bfloat16* at = dst + static_cast<size_t>(c) * j.ld_dst + r;
+                const __nv_bfloat16 v = tile[tx][ty + k * 8];
+                *at = v;
+                // the same slot of every data-parallel replica's stash (peer-mapped memory over NVLink)
+                for (int q = 0; q < jobs.n_peers; ++q)
+                    *reinterpret_cast<__nv_bfloat16*>(reinterpret_cast<char*>(at) + jobs.peer_delta[q]) = v;
+            }
         }
         __syncthreads();
     }
@@ -584,6 +591,7 @@ extern "C" int pb2_transpose_colsum(const void* src, long long ld_src, void* dst
 extern "C" int pb2_transpose_multi(const pb2_transpose_jobs* jobs, cudaStream_t stream) {
     if (!jobs || jobs->count <= 0) return 0;
     if (jobs->count > PB2_MAX_TRANSPOSES) { set_error("pb2_transpose_multi: too many jobs (%d)", jobs->count); return -1; }
+    if (jobs->n_peers < 0 || jobs->n_peers > PB2_MAX_PEERS) { set_error("pb2_transpose_multi: n_peers %d out of range", jobs->n_peers); return -1; }
     int max_c = 0;
     for (int i = 0; i < jobs->count; ++i) {
         if (jobs->job[i].C > max_c) max_c = jobs->job[i].C;

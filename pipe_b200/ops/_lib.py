@@ -62,6 +62,7 @@ class EncoderLayerDesc(ctypes.Structure):
         + [(n, _ci) for n in ("stash_off_qkv", "stash_off_o", "stash_off_1", "stash_off_2")]
         + [("workspace", _vp), ("workspace_bytes", ctypes.c_size_t)]
         + [("next_weight", _vp), ("next_weight_bytes", ctypes.c_size_t), ("prefetch", _ci), ("side_stream", _vp)]
+        + [("n_peers", _ci), ("peer_delta", _ll * 7)]
     )
 
 

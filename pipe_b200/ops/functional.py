@@ -140,15 +140,21 @@ class _TransposeJob(ctypes.Structure):
 
 
 class _TransposeJobs(ctypes.Structure):
-    _fields_ = [("job", _TransposeJob * 8), ("count", c_i)]
+    _fields_ = [("job", _TransposeJob * 8), ("count", c_i), ("n_peers", c_i), ("peer_delta", c_ll * 7)]
 
 
-def transpose_multi(jobs: Sequence[Tuple[Tensor, Tensor, int, Optional[Tensor], float]]) -> None:
+def transpose_multi(jobs: Sequence[Tuple[Tensor, Tensor, int, Optional[Tensor], float]],
+                    peer_deltas: Sequence[int] = ()) -> None:
     """Each job is ``(src [R, C], dst_base [C, ld], dst_col_offset, colsum or None, scale)``:
-    writes ``dst_base[c, off + r] = src[r, c]`` for all jobs in one launch."""
-    assert 0 < len(jobs) <= 8
+    writes ``dst_base[c, off + r] = src[r, c]`` for all jobs in one launch.  ``peer_deltas`` (bytes): every
+    stored element is also stored at the same address plus each delta — the same slot of a symmetric
+    stash in the data-parallel replicas' memory."""
+    assert 0 < len(jobs) <= 8 and len(peer_deltas) <= 7
     packed = _TransposeJobs()
     packed.count = len(jobs)
+    packed.n_peers = len(peer_deltas)
+    for q, delta in enumerate(peer_deltas):
+        packed.peer_delta[q] = delta
     dev = jobs[0][0].device
     for k, (src, dst, off, colsum, scale) in enumerate(jobs):
         assert src.dtype == torch.bfloat16 and dst.dtype == torch.bfloat16 and src.stride(1) == 1 and dst.stride(1) == 1

@@ -759,7 +759,8 @@ class DistPipe(nn.Module):
                 with torch.no_grad(), enable_checkpointing(), seed_scope(cell.seed_base):
                     out = self._call(values, tracker)
             else:
-                out = self._call(values, tracker)
+                with seed_scope(cell.seed_base):      # same seed derivation in every checkpoint mode
+                    out = self._call(values, tracker)
             self._span("fwd", t0, self._mark())
             outs = out if isinstance(out, tuple) else (out,)
 

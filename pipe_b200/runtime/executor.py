@@ -39,6 +39,7 @@ from torch.autograd.profiler import record_function
 from ..autograd.checkpoint import Checkpointing
 from ..autograd.copy import Copy, Wait
 from ..autograd.dependency import fork, join
+from ..autograd.seeds import SeedBase, seed_scope
 from ..autograd.stream import AbstractStream, current_stream, use_device
 from ..microbatch import Batch
 from ..skip.layout import SkipLayout
@@ -258,7 +259,10 @@ class Pipeline:
         def compute_plain() -> Batch:
             if timeline is not None:
                 timeline.mark("fwd", i, j, "start", device)
-            out = batch.call(stage)
+            # same seed derivation as a checkpointed cell (one draw from the CPU generator per cell, the
+            # call sites' seeds derived from it): 'never' and 'always' see identical dropout masks
+            with seed_scope(SeedBase()):
+                out = batch.call(stage)
             if timeline is not None:
                 timeline.mark("fwd", i, j, "end", device)
             return out

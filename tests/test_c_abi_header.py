@@ -33,8 +33,10 @@ def test_ctypes_struct_layouts_match_the_header():
         #include <stddef.h>
         #include "pipe_b200.h"
         int main(void) {
-            printf("%zu %zu %zu %zu\\n", sizeof(pb2_gemm_desc), offsetof(pb2_gemm_desc, persistent),
-                   sizeof(pb2_encoder_layer), offsetof(pb2_encoder_layer, side_stream));
+            printf("%zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(pb2_gemm_desc), offsetof(pb2_gemm_desc, persistent),
+                   sizeof(pb2_encoder_layer), offsetof(pb2_encoder_layer, side_stream),
+                   offsetof(pb2_encoder_layer, peer_delta), sizeof(pb2_encoder_stack),
+                   offsetof(pb2_encoder_stack, side_stream), sizeof(pb2_transpose_jobs));
             return 0;
         }
     """)
@@ -46,7 +48,12 @@ def test_ctypes_struct_layouts_match_the_header():
                              capture_output=True, text=True)
         assert res.returncode == 0, res.stderr
         out = subprocess.run([exe], capture_output=True, text=True).stdout.split()
-    gemm_size, gemm_off, layer_size, layer_off = map(int, out)
+    gemm_size, gemm_off, layer_size, layer_off, peer_off, stack_size, stack_off, jobs_size = map(int, out)
+    from pipe_b200.ops import functional as F2
+    assert _lib.EncoderLayerDesc.peer_delta.offset == peer_off
+    assert ctypes.sizeof(_lib.EncoderStackDesc) == stack_size
+    assert _lib.EncoderStackDesc.side_stream.offset == stack_off
+    assert ctypes.sizeof(F2._TransposeJobs) == jobs_size
     assert ctypes.sizeof(_lib.GemmDesc) == gemm_size
     assert _lib.GemmDesc.persistent.offset == gemm_off
     assert ctypes.sizeof(_lib.EncoderLayerDesc) == layer_size
