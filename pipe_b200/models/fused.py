@@ -247,6 +247,10 @@ class _EncoderLayerFn(torch.autograd.Function):
             setattr(d, "ld_stash_" + key, lg.xt.stride(0))
             setattr(d, "stash_off_" + key, off)
             setattr(d, "db_" + key, bias.grad.data_ptr())
+        deltas = layer._lg("qkv").peer_deltas       # data-parallel replicas' stashes (hybrid), same for all four
+        d.n_peers = len(deltas)
+        for q, delta in enumerate(deltas):
+            d.peer_delta[q] = delta
         ws = workspace(dev, stream)
         d.workspace, d.workspace_bytes = ws.data_ptr(), ws.numel()
         side = _side_stream(dev) if _SIDE_TRANSPOSE else None
@@ -441,6 +445,10 @@ class EncoderStack:
                     setattr(d, "xt_" + name, lg.xt.data_ptr())
                     setattr(d, "dyt_" + name, lg.dyt.data_ptr())
                     setattr(d, "ld_stash_" + name, lg.xt.stride(0))
+                deltas = layer._lg("qkv").peer_deltas
+                d.n_peers = len(deltas)
+                for q, delta in enumerate(deltas):
+                    d.peer_delta[q] = delta
                 pairs += [(p, p.grad) for p in (n1w, n1b, n2w, n2b, bq, bo, b1, b2)]
             arr[k] = d
         self._static = {"device": device.index, "with_grads": with_grads, "stash_epoch": stash_epoch(),
@@ -636,7 +644,8 @@ class _DecoderFn(torch.autograd.Function):
         dl = buf[:, :V]
         _, w16t = module._sh("dec")
         dx = gemm_nt(w16t[:, :V], dl, transpose_out=True)
-        F2.transpose_multi(module._lg("dec").jobs(x2, dl))
+        lg = module._lg("dec")
+        F2.transpose_multi(lg.jobs(x2, dl), lg.peer_deltas)
         return (dx.view(S, NB, E), None) + (None,) * (len(ctx.needs_input_grad) - 2)
 
 
@@ -674,7 +683,8 @@ class _DecoderLossFn(torch.autograd.Function):
         dl = buf[:, :V]
         _, w16t = module._sh("dec")
         dx = gemm_nt(w16t[:, :V], dl, transpose_out=True)
-        F2.transpose_multi(module._lg("dec").jobs(x2, dl))
+        lg = module._lg("dec")
+        F2.transpose_multi(lg.jobs(x2, dl), lg.peer_deltas)
         return (dx.view(S, NB, E), None, None) + (None,) * (len(ctx.needs_input_grad) - 3)
 
 

@@ -50,26 +50,47 @@ class _DeviceState:
 
 class FusedClipAdam:
     """Args mirror ``torch.optim.Adam`` plus ``max_norm`` (<= 0 disables clipping),
-    ``grad_scale`` (multiplies every gradient, e.g. ``1/replicas``) and
-    ``distributed`` (sum the squared norm over the ranks of ``group`` — one stage
-    per rank)."""
+    ``grad_scale`` (multiplies every gradient) and ``distributed`` (sum the squared norm over the
+    ranks of ``group`` — one stage per rank).
+
+    ``replica_group`` / ``replicas`` switch on data parallelism across pipeline replicas (the Pipe-inside-DDP
+    hybrid).  ``reduce_backend`` picks how the gradients are averaged over the replica group:
+
+    ``"gather"`` (default; ``"fused"`` is an alias)
+        weight matrices: the replicas exchange the stacked wgrad *operands* while backward runs (the transpose
+        kernels store into every replica's stash over NVLink) and the averaging happens inside the wgrad GEMM
+        (:mod:`pipe_b200.parallel.replica_stash`); needs ``max_tokens``.  Small gradients (biases, LayerNorm,
+        embedding) go through the all-reduce kernel on a side stream, next to the wgrad GEMMs.
+    ``"allreduce"``
+        every gradient lives in ONE symmetric buffer; the hand-written NVLink all-reduce kernel
+        (``csrc/allreduce.cu``: scale fused) runs per bucket — one bucket per weight matrix — on a side
+        stream as soon as that matrix's wgrad GEMM has been enqueued, i.e. under the remaining GEMMs.
+    ``"nccl"``
+        the baseline: the same buckets, ``dist.all_reduce(async_op=True)`` per bucket as it becomes ready
+        (what DDP does), ``1/k`` folded into the optimizer's gradient scale.
+    """
 
     def __init__(self, module: nn.Module, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
                  weight_decay: float = 0.0, max_norm: float = 0.0, grad_scale: float = 1.0,
                  distributed: bool = False, group=None, replica_group=None, replicas: int = 1,
-                 reduce_backend: str = "fused") -> None:
-        """``replica_group`` / ``replicas`` switch on data parallelism across pipeline replicas: all
-        gradients of this rank's stage then live in ONE symmetric buffer and are averaged over the
-        replica group by the fused NVSwitch all-reduce (``reduce_backend="fused"``) or by NCCL
-        (``"nccl"``, the baseline) between backward and the update."""
+                 reduce_backend: str = "gather", max_tokens: int = 0, reduce_ctas: int = 32) -> None:
         self.lr, self.betas, self.eps, self.weight_decay = lr, betas, eps, weight_decay
         self.max_norm, self.grad_scale = max_norm, grad_scale
         self.distributed, self.group = distributed, group
+        if reduce_backend == "fused":
+            reduce_backend = "gather"
+        if reduce_backend not in ("gather", "allreduce", "nccl"):
+            raise ValueError("reduce_backend is not one of 'gather', 'allreduce', or 'nccl'")
         self.replica_group, self.replicas, self.reduce_backend = replica_group, int(replicas), reduce_backend
-        self.reduce_ctas = 64
+        self.reduce_ctas = int(reduce_ctas)
         self.step_count = 0
         self.module = module
         self._cpu: Optional[torch.optim.Optimizer] = None
+        self._armed = True             # zero_grad() ran since the last step()
+        self._works: List = []
+        self._reduce_stream: Optional[torch.cuda.Stream] = None
+        self._stash = None
+        self.exposed_reduce_events = None
         if not any(p.is_cuda for p in module.parameters()):
             # Non-CUDA parameters (the fused modules' reference path): same surface, same semantics —
             # average over replicas, clip by the global norm, Adam — on stock PyTorch ops.
@@ -83,12 +104,15 @@ class FusedClipAdam:
 
         shadows = {}
         gemm_written = set()
+        lgs = []
         for sub in module.modules():
             for sh in getattr(sub, "pb2_shadows", lambda: [])():
                 shadows[id(sh.param)] = sh
             for lg in getattr(sub, "pb2_linear_grads", lambda: [])():
                 gemm_written.add(id(lg.weight))
+                lgs.append(lg)
         self._shadows = shadows
+        self._lgs = lgs
 
         self.devs: Dict[torch.device, _DeviceState] = {}
         seen = set()
@@ -104,35 +128,48 @@ class FusedClipAdam:
         hybrid = self.replicas > 1
         if hybrid and len(self.devs) != 1:
             raise ValueError("replicated (hybrid) mode expects one stage = one device per rank")
+        # dense: every gradient of the stage in one flat buffer [matrices | small], reduced bucket by bucket
+        dense = hybrid and self.reduce_backend in ("allreduce", "nccl")
+        pad = 32                       # bucket granularity: a multiple of 4 * world for every world <= 8
         for st in self.devs.values():
             small = [p for p in st.params if id(p) not in gemm_written]
             big = [p for p in st.params if id(p) in gemm_written]
-            n_small = sum((p.numel() + 3) // 4 * 4 for p in small)
-            n_big = sum((p.numel() + 3) // 4 * 4 for p in big) if hybrid else 0
+            n_small = max(sum((p.numel() + pad - 1) // pad * pad for p in small), pad)
+            n_big = sum((p.numel() + pad - 1) // pad * pad for p in big) if dense else 0
+            st.symm = None
+            st.buckets = {}
             if hybrid:
-                # one symmetric buffer for every gradient of the stage: [matrices | small]
                 from ..parallel.symmetric import SymmetricBuffer
-                st.symm = SymmetricBuffer(n_big + max(n_small, 4), self.replica_group, st.device)
-                flat = st.symm.data
-                st.flat_small = flat[n_big:n_big + max(n_small, 4)]
+                if self.reduce_backend == "nccl":
+                    flat = torch.zeros(n_big + n_small, dtype=torch.float32, device=st.device)
+                else:
+                    st.symm = SymmetricBuffer(n_big + n_small, self.replica_group, st.device)
+                    flat = st.symm.data
+                st.flat = flat
+                st.flat_small = flat[n_big:n_big + n_small]
+                st.small_range = (n_big, n_big + n_small)
                 at = 0
                 for p in big:
-                    p.grad = flat[at:at + p.numel()].view_as(p)
-                    at += (p.numel() + 3) // 4 * 4
+                    if dense:
+                        p.grad = flat[at:at + p.numel()].view_as(p)
+                        st.buckets[id(p)] = (at, at + (p.numel() + pad - 1) // pad * pad)
+                        at += (p.numel() + pad - 1) // pad * pad
             else:
-                st.symm = None
-                st.flat_small = torch.zeros(max(n_small, 4), dtype=torch.float32, device=st.device)
+                st.flat = None
+                st.flat_small = torch.zeros(n_small, dtype=torch.float32, device=st.device)
             at = 0
             for p in small:
                 p.grad = st.flat_small[at:at + p.numel()].view_as(p)
-                at += (p.numel() + 3) // 4 * 4
+                at += (p.numel() + pad - 1) // pad * pad
             rows_desc = np.zeros(len(st.params), dtype=_DESC)
             tile = 0
             for k, p in enumerate(st.params):
                 if id(p) in gemm_written:
-                    if not hybrid:
+                    if not dense:
                         p.grad = torch.zeros_like(p)
-                        p._pb2_normsq = st.normsq      # local norm is the global norm: fuse it into wgrad
+                        p._pb2_normsq = st.normsq      # every replica writes the final gradient: fuse its norm into wgrad
+                    elif hasattr(p, "_pb2_normsq"):
+                        del p._pb2_normsq
                     p._pb2_fresh = True
                     p._pb2_sumsq_done = False
                 m = torch.zeros_like(p)
@@ -152,6 +189,19 @@ class FusedClipAdam:
             st.total_tiles = tile
         self._gemm_written = gemm_written
 
+        if hybrid:
+            (st,) = self.devs.values()
+            self._reduce_stream = torch.cuda.Stream(st.device)
+            if self.reduce_backend == "gather":
+                if max_tokens <= 0:
+                    raise ValueError("reduce_backend='gather' needs max_tokens (tokens a replica stacks per step)")
+                from ..parallel.replica_stash import ReplicaStash
+                self._stash = ReplicaStash(lgs, self.replica_group, st.device, max_tokens)
+            else:
+                for lg in lgs:
+                    lg.on_flushed = self._bucket_ready
+            wgrad.pre_flush_hooks.append(self._backward_done)
+
     # -- torch.optim-like surface --------------------------------------------------
     def zero_grad(self, set_to_none: bool = True) -> None:
         """Small gradients: one memset.  Matrix gradients: nothing — the next wgrad
@@ -167,24 +217,66 @@ class FusedClipAdam:
                 if id(p) in self._gemm_written:
                     p._pb2_fresh = True
                     p._pb2_sumsq_done = False
+        self._armed = True
 
-    def _reduce_replicas(self) -> None:
-        """Average the stage's gradients over the pipeline replicas (and collect this rank's share
-        of the squared norm of the averaged gradients in the same pass)."""
+    # -- replica reduction (hybrid) ----------------------------------------------------
+    def _side(self) -> "torch.cuda.Stream":
+        """The reduce stream, made to wait for everything enqueued so far on the current stream."""
+        side = self._reduce_stream
+        side.wait_stream(torch.cuda.current_stream(side.device))
+        return side
+
+    def _backward_done(self, todo) -> None:
+        """Pre-flush hook: backward has ended (the side-stream transposes were joined), the deferred wgrad
+        GEMMs are about to be enqueued.  The small gradients are final: start their reduction on the reduce
+        stream so that it runs next to the GEMMs."""
+        if not any(id(lg.weight) in self._gemm_written for lg in todo):
+            return
         (st,) = self.devs.values()
-        want = st.normsq if self.max_norm > 0 else None
-        if self.reduce_backend == "fused":
-            st.symm.all_reduce_(scale=1.0 / self.replicas, sumsq=want, ctas=self.reduce_ctas)
+        lo, hi = st.small_range
+        if self.reduce_backend == "nccl":
+            self._works.append(dist.all_reduce(st.flat[lo:hi], group=self.replica_group, async_op=True))
+            return
+        side = self._side()
+        st.flat.record_stream(side)
+        st.symm.all_reduce_(scale=1.0 / self.replicas, ctas=self.reduce_ctas, stream=side.cuda_stream, lo=lo, hi=hi)
+
+    def _bucket_ready(self, lg) -> None:
+        """A weight matrix's wgrad GEMM has been enqueued (dense backends): reduce its bucket under the
+        GEMMs that follow."""
+        (st,) = self.devs.values()
+        rng = st.buckets.get(id(lg.weight))
+        if rng is None:
+            return
+        lo, hi = rng
+        if self.reduce_backend == "nccl":
+            self._works.append(dist.all_reduce(st.flat[lo:hi], group=self.replica_group, async_op=True))
+            return
+        side = self._side()
+        st.symm.all_reduce_(scale=1.0 / self.replicas, ctas=self.reduce_ctas, stream=side.cuda_stream, lo=lo, hi=hi)
+
+    def _join_reduction(self) -> None:
+        """Make the current stream wait for every reduction launched since backward ended."""
+        for w in self._works:
+            w.wait()
+        self._works = []
+        if self._reduce_stream is not None:
+            torch.cuda.current_stream(self._reduce_stream.device).wait_stream(self._reduce_stream)
+
+    def _hybrid_normsq(self) -> None:
+        """Squared norm of the averaged gradients of all stages, on every rank."""
+        (st,) = self.devs.values()
+        if self.reduce_backend == "gather":
+            # matrices: summed into st.normsq by the wgrad epilogues (identical on every replica)
+            F2.sumsq(st.flat_small, st.normsq)
+            for p in st.params:
+                if id(p) in self._gemm_written and not getattr(p, "_pb2_sumsq_done", False):
+                    F2.sumsq(p.grad.view(-1), st.normsq)
         else:
-            dist.all_reduce(st.symm.data, group=self.replica_group)
-            st.symm.data.mul_(1.0 / self.replicas)
-            if want is not None:
-                n = st.symm.numel // st.symm.world
-                lo = n * st.symm.rank
-                F2.sumsq(st.symm.data[lo:lo + n], want)
-        if want is not None:
-            st.total_normsq.copy_(st.normsq)
-            dist.all_reduce(st.total_normsq)          # slices of every stage, over all ranks
+            F2.sumsq(st.flat, st.normsq)
+        st.total_normsq.copy_(st.normsq)
+        if self.distributed:
+            dist.all_reduce(st.total_normsq, group=self.group)          # over the stages of this pipeline
 
     def _total_normsq(self) -> None:
         """Finish the squared norm on every device, then share the total."""
@@ -233,10 +325,27 @@ class FusedClipAdam:
         if self._cpu is not None:
             self._step_cpu()
             return
-        if self.replicas > 1:
-            self._reduce_replicas()
-        elif self.max_norm > 0:
-            self._total_normsq()
+        if not self._armed:
+            # step() without zero_grad() since the last one (gradient accumulation, a retried step): the norm
+            # scalar still holds the previous step's sum and the matrix gradients were accumulated outside the
+            # fused epilogue sums — start the norm over from the gradients as they are now
+            for st in self.devs.values():
+                st.normsq.zero_()
+                for p in st.params:
+                    if id(p) in self._gemm_written:
+                        p._pb2_sumsq_done = False
+        self._armed = False
+        hybrid = self.replicas > 1
+        if hybrid:
+            self._join_reduction()
+        scale = self.grad_scale
+        if hybrid and self.reduce_backend == "nccl":
+            scale = self.grad_scale / self.replicas           # the sum was reduced; the mean is folded into the update
+        if self.max_norm > 0:
+            if hybrid:
+                self._hybrid_normsq()
+            else:
+                self._total_normsq()
         lib = _lib.load()
         for st in self.devs.values():
             with torch.cuda.device(st.device):
@@ -245,7 +354,7 @@ class FusedClipAdam:
                                        ctypes.c_float(self.lr), ctypes.c_float(self.betas[0]),
                                        ctypes.c_float(self.betas[1]), ctypes.c_float(self.eps),
                                        ctypes.c_float(self.weight_decay), ctypes.c_int(self.step_count),
-                                       ctypes.c_float(self.max_norm), ctypes.c_float(self.grad_scale),
+                                       ctypes.c_float(self.max_norm), ctypes.c_float(scale),
                                        _lib.stream_ptr(st.device))
             _lib.check(rc, "pb2_adam_step")
         for sh in self._shadows.values():
@@ -256,4 +365,13 @@ class FusedClipAdam:
         if self._cpu is not None:
             return self._cpu_norm
         first = next(iter(self.devs.values()))
-        return float(first.total_normsq.sqrt().item()) * self.grad_scale
+        scale = self.grad_scale / self.replicas if (self.replicas > 1 and self.reduce_backend == "nccl") else self.grad_scale
+        return float(first.total_normsq.sqrt().item()) * scale
+
+    def close(self) -> None:
+        """Detach from the wgrad flush hooks (a second optimizer on the same process would otherwise be
+        notified too)."""
+        if self._backward_done in wgrad.pre_flush_hooks:
+            wgrad.pre_flush_hooks.remove(self._backward_done)
+        if self._stash is not None:
+            self._stash.close()

@@ -78,7 +78,15 @@ def ensure_grad(p: nn.Parameter) -> Tensor:
 
 
 class LinearGrad:
-    """Stacked operands and the deferred wgrad GEMM of one weight ``[out, in]``."""
+    """Stacked operands and the deferred wgrad GEMM of one weight ``[out, in]``.
+
+    *Replicated* mode (Pipe-inside-DDP hybrid, :class:`pipe_b200.parallel.replica_stash.ReplicaStash`): the two
+    stacks are views into a symmetric slab that every data-parallel replica maps, ``k * cap`` columns wide;
+    replica ``r`` stacks its micro-batches at columns ``r * cap + ...`` of its own copy *and of every peer's*
+    (the transposes store to all of them), so after a barrier each replica holds all replicas' operands and
+    ONE GEMM with K = all replicas' tokens, scaled by ``1/k``, writes the averaged gradient: the
+    all-reduce of the weight matrices happens in the tensor core's accumulator, and what crosses NVLink is
+    ``(in + out) * tokens`` bf16 instead of ``in * out`` fp32."""
 
     def __init__(self, weight: nn.Parameter, bias: Optional[nn.Parameter]) -> None:
         self.weight = weight
@@ -87,10 +95,39 @@ class LinearGrad:
         self.dyt: Optional[Tensor] = None     # [out, cap] bf16
         self.used = 0
         self.stream: Optional[int] = None       # raw handle of the stream the operands were stacked on
+        self.col0 = 0                           # first column of this replica's region
+        self.rep: Optional[Tuple[int, int]] = None      # (columns per replica, replicas) in replicated mode
+        self.peer_deltas: Tuple[int, ...] = ()  # byte offsets from this replica's slab to each peer's
+        self.high = 0                           # most columns any flush has used (replicated: tail zeroing)
+        self.on_flushed = None                  # optional callable(self) after the GEMM was enqueued
+
+    def bind_replicated(self, xt: Tensor, dyt: Tensor, replica: int, cap: int, replicas: int,
+                        peer_deltas: Tuple[int, ...]) -> None:
+        global _stash_epoch
+        out_f, in_f = self.weight.shape
+        assert xt.shape == (in_f, replicas * cap) and dyt.shape == (out_f, replicas * cap) and not self.used
+        with _lock:
+            self.xt, self.dyt = xt, dyt
+            self.col0, self.rep, self.peer_deltas = replica * cap, (cap, replicas), tuple(peer_deltas)
+            self.high = 0
+            _stash_epoch += 1
+
+    def capacity(self) -> int:
+        """Columns one step may stack."""
+        if self.rep is not None:
+            return self.rep[0]
+        return 0 if self.xt is None else self.xt.size(1)
 
     def _reserve(self, tokens: int) -> int:
         out_f, in_f = self.weight.shape
         need = self.used + tokens
+        if self.rep is not None:
+            if need > self.rep[0]:
+                raise RuntimeError(f"replicated wgrad stash holds {self.rep[0]} tokens per step and replica, "
+                                   f"{need} were stacked: raise max_tokens of the hybrid optimizer")
+            off = self.col0 + self.used
+            self.used = need
+            return off
         cap = 0 if self.xt is None else self.xt.size(1)
         if need > cap or self.xt.device != self.weight.device:
             new_cap = max(64, cap)
@@ -126,7 +163,8 @@ class LinearGrad:
 
     def jobs(self, x: Tensor, dy: Tensor) -> List[Tuple[Tensor, Tensor, int, Optional[Tensor], float]]:
         """Reserve a column block for one micro-batch and return the two transpose
-        jobs that fill it (``dy``'s job also accumulates the bias gradient)."""
+        jobs that fill it (``dy``'s job also accumulates the bias gradient).  Pass ``self.peer_deltas``
+        to ``transpose_multi`` along with them."""
         tokens = x.size(0)
         assert dy.size(0) == tokens
         with _lock:
@@ -144,12 +182,25 @@ class LinearGrad:
         grad = ensure_grad(w)
         fresh = getattr(w, "_pb2_fresh", False)
         normsq = getattr(w, "_pb2_normsq", None) if fresh else None
-        gemm_nt(self.dyt[:, : self.used], self.xt[:, : self.used], out=grad, accumulate=not fresh,
-                sumsq=normsq, stream=self.stream)
+        if self.rep is None:
+            gemm_nt(self.dyt[:, : self.used], self.xt[:, : self.used], out=grad, accumulate=not fresh,
+                    sumsq=normsq, stream=self.stream)
+        else:
+            cap, k = self.rep
+            if self.used < self.high:
+                # a shorter step than before: stale columns of every replica's region would be summed in
+                with torch.cuda.stream(torch.cuda.ExternalStream(self.stream, device=self.xt.device)):
+                    for r in range(k):
+                        self.xt[:, r * cap + self.used: r * cap + self.high].zero_()
+                        self.dyt[:, r * cap + self.used: r * cap + self.high].zero_()
+            self.high = self.used
+            gemm_nt(self.dyt, self.xt, out=grad, accumulate=not fresh, alpha=1.0 / k, sumsq=normsq, stream=self.stream)
         if fresh:
             w._pb2_fresh = False
             w._pb2_sumsq_done = normsq is not None
         self.used = 0
+        if self.on_flushed is not None:
+            self.on_flushed(self)
 
 
 class StackStash:
@@ -163,6 +214,7 @@ class StackStash:
         self.lgs = list(lgs)
         self._items = {id(lg): lg for lg in self.lgs}
         self.cap = 0
+        self.col0 = 0
         self.epoch = -1
 
     def reserve(self, tokens: int, device: torch.device, stream: int) -> int:
@@ -172,11 +224,13 @@ class StackStash:
             used = lgs[0].used
             need = used + tokens
             if self.epoch != _stash_epoch or need > self.cap:
+                used = lgs[0].used
                 offs = {lg._reserve(tokens) for lg in lgs}
                 if len(offs) != 1:
                     raise RuntimeError("the linears of a layer run were used unevenly within one step "
                                        "(some through the per-layer path): cannot share a stash offset")
-                self.cap = min(lg.xt.size(1) for lg in lgs)
+                self.cap = min(lg.capacity() for lg in lgs)
+                self.col0 = lgs[0].col0
                 self.epoch = _stash_epoch
                 for lg in lgs:
                     lg.stream = stream
@@ -190,7 +244,7 @@ class StackStash:
                     lg.stream = stream
             _pending.update(self._items)
             _arm()
-        return used
+        return self.col0 + used
 
 
 def _arm() -> None:
@@ -214,15 +268,27 @@ def _engine_done() -> None:
     flush_pending()
 
 
+#: ``hook(todo)`` callables run by :func:`flush_pending` right before / after the wgrad GEMMs of a non-empty
+#: flush (after the side streams were joined).  The hybrid layout hangs its replica barriers and the launch of
+#: the small-gradient reduction here.
+pre_flush_hooks: List = []
+post_flush_hooks: List = []
+
+
 def flush_pending() -> None:
     """Run the deferred wgrad GEMM of every Linear that stacked operands."""
     with _lock:
         todo = list(_pending.values())
         _pending.clear()
-    if todo:
-        wait_side_streams()
+    if not todo:
+        return
+    wait_side_streams()
+    for hook in list(pre_flush_hooks):
+        hook(todo)
     for lg in todo:
         lg.flush()
+    for hook in list(post_flush_hooks):
+        hook(todo)
 
 
 @contextmanager

@@ -8,13 +8,16 @@ its own shard of the global batch.
 The reference only notes that DDP *may* wrap ``Pipe`` and only with ``checkpoint='never'``
 (``pipe.py:290-293``): DDP's per-parameter hooks fire inside ``Checkpoint.backward``'s nested
 autograd pass.  Here the reduction is not hook-driven.  Every gradient of a stage lives in one
-symmetric buffer; when the stage's backward (all micro-batches, all checkpoint modes) and its
-deferred wgrad GEMMs are done, ONE fused kernel per rank averages the buffer over the replica
-group through NVLink / NVSwitch (``csrc/allreduce.cu``), scaling by ``1/k`` and accumulating the
-squared norm for clipping in the same pass.  Later stages finish their backward first, so their
-reduction overlaps the backward of the earlier stages; only stage 0's is exposed.
+autograd pass.  Here the reduction is not hook-driven, so all three checkpoint modes work.
 
-``reduce_backend="nccl"`` swaps the kernel for ``dist.all_reduce`` — the baseline to beat.
+Default (``reduce_backend="gather"``): the weight matrices are never all-reduced at all.  The transpose kernels
+that stack the wgrad operands of every micro-batch during backward store them into every replica's stash over
+NVLink; the one deferred wgrad GEMM per Linear then runs over all replicas' tokens and averages in its fp32
+accumulator (``parallel/replica_stash.py``).  Small gradients use the all-reduce kernel on a side stream, under
+the wgrad GEMMs.  ``"allreduce"`` keeps dense gradients and runs the NVLink all-reduce kernel
+(``csrc/allreduce.cu``) per weight-matrix bucket as each wgrad GEMM is enqueued; ``"nccl"`` does the same with
+asynchronous ``dist.all_reduce`` calls — the DDP-style baseline to beat.  Later stages finish their backward
+first, so their reduction overlaps the backward of the earlier stages.
 """
 from __future__ import annotations
 
@@ -70,9 +73,12 @@ class HybridPipe(DistPipe):
         self.replica = replica
         self.replicas = replicas
 
-    def make_optimizer(self, reduce_backend: str = "fused", **adam_kwargs):
-        """A :class:`~pipe_b200.ops.optim.FusedClipAdam` whose step first averages this stage's
-        gradients over the replica group (fused NVSwitch all-reduce, or NCCL as the baseline)."""
+    def make_optimizer(self, reduce_backend: str = "gather", max_tokens: int = 0, **adam_kwargs):
+        """A :class:`~pipe_b200.ops.optim.FusedClipAdam` that averages this stage's gradients over the replica
+        group: ``"gather"`` (operand exchange during backward, reduction inside the wgrad GEMM; needs
+        ``max_tokens`` = tokens of one replica's mini-batch), ``"allreduce"`` (bucketed NVLink all-reduce kernel
+        under the wgrad GEMMs) or ``"nccl"`` (bucketed asynchronous NCCL all-reduce, the baseline)."""
         from ..ops.optim import FusedClipAdam
-        return FusedClipAdam(self.stage, distributed=True, replica_group=self.replica_group,
-                             replicas=self.replicas, reduce_backend=reduce_backend, **adam_kwargs)
+        return FusedClipAdam(self.stage, distributed=True, group=self.group, replica_group=self.replica_group,
+                             replicas=self.replicas, reduce_backend=reduce_backend, max_tokens=max_tokens,
+                             **adam_kwargs)

@@ -107,21 +107,29 @@ class SymmetricBuffer:
 
     # -- the collective ----------------------------------------------------------------
     def all_reduce_(self, scale: float = 1.0, sumsq: Optional[Tensor] = None, cast_out: Optional[Tensor] = None,
-                    ctas: int = 64, use_multimem: Optional[bool] = None, stream: Optional[int] = None) -> None:
-        """In-place ``data <- scale * sum over ranks(data)`` with the fused kernel; every rank
-        must call it at the same point of its stream."""
+                    ctas: int = 64, use_multimem: Optional[bool] = None, stream: Optional[int] = None,
+                    lo: int = 0, hi: Optional[int] = None) -> None:
+        """In-place ``data[lo:hi] <- scale * sum over ranks(data[lo:hi])`` with the fused kernel; every rank
+        must call it at the same point of its stream.  ``lo`` and ``hi - lo`` are multiples of ``4 * world``
+        (a *bucket*: successive calls on one stream may cover different ranges of the same buffer)."""
+        hi = self.numel if hi is None else hi
+        n = hi - lo
+        if lo % (4 * self.world) or n % (4 * self.world) or n < 0 or hi > self.numel:
+            raise ValueError(f"bucket [{lo}, {hi}) is not aligned to 4 * world = {4 * self.world} elements")
+        if n == 0:
+            return
         if self.mode == "torch":
+            part = self.data[lo:hi]
             if self.world > 1:
-                dist.all_reduce(self.data, group=self.group)
+                dist.all_reduce(part, group=self.group)
             if scale != 1.0:
-                self.data.mul_(scale)
+                part.mul_(scale)
             if sumsq is not None:
                 # every rank holds the full result: count each slice once, like the kernel does
-                lo = self.numel // self.world * self.rank
-                hi = lo + self.numel // self.world
-                sumsq.add_(self.data[lo:hi].float().pow(2).sum())
+                a = n // self.world * self.rank
+                sumsq.add_(part[a:a + n // self.world].float().pow(2).sum())
             if cast_out is not None:
-                cast_out.copy_(self.data)
+                cast_out.copy_(part)
             return
 
         from ..ops import _lib
@@ -131,14 +139,35 @@ class SymmetricBuffer:
             # in-switch reduction pays off once several peers contribute; with two, P2P pull/push wins
             use_multimem = bool(self.multicast_ptr) and self.world >= 4
         arr = ctypes.c_void_p * self.world
-        bufs = arr(*self.peer_data)
+        bufs = arr(*[p + lo * 4 for p in self.peer_data])
         pads = arr(*self.peer_pads)
         if stream is None:
             stream = _lib.raw_stream(self.device)
         with _lib.on_device(self.device):
-            rc = lib.pb2_allreduce_f32(bufs, pads, ctypes.c_void_p(self.multicast_ptr or None), ctypes.c_int(self.world),
-                                       ctypes.c_int(self.rank), ctypes.c_size_t(self.numel), ctypes.c_float(scale),
+            mc = (self.multicast_ptr + lo * 4) if self.multicast_ptr else None
+            rc = lib.pb2_allreduce_f32(bufs, pads, ctypes.c_void_p(mc), ctypes.c_int(self.world),
+                                       ctypes.c_int(self.rank), ctypes.c_size_t(n), ctypes.c_float(scale),
                                        ctypes.c_void_p(_lib.ptr(sumsq)), ctypes.c_void_p(_lib.ptr(cast_out)),
                                        ctypes.c_uint(self.epoch), ctypes.c_int(ctas), ctypes.c_int(int(use_multimem)),
                                        ctypes.c_void_p(stream))
         _lib.check(rc, "pb2_allreduce_f32")
+
+    def barrier(self, phase: int = 0, stream: Optional[int] = None) -> None:
+        """A device-side barrier among the ranks of the group on ``stream`` (one tiny kernel, no host wait):
+        what this rank's earlier kernels stored into peers' copies is visible to the kernels a peer launches
+        after its own call.  Uses this buffer's signal pad: do not mix with :meth:`all_reduce_` on one buffer."""
+        if self.mode == "torch":
+            if self.world > 1 and self.device.type != "cuda":
+                dist.barrier(group=self.group)
+            return
+        from ..ops import _lib
+        lib = _lib.load()
+        self.epoch += 1
+        arr = ctypes.c_void_p * self.world
+        pads = arr(*self.peer_pads)
+        if stream is None:
+            stream = _lib.raw_stream(self.device)
+        with _lib.on_device(self.device):
+            rc = lib.pb2_group_barrier(pads, ctypes.c_int(self.world), ctypes.c_int(self.rank), ctypes.c_uint(self.epoch),
+                                       ctypes.c_int(phase), ctypes.c_void_p(stream))
+        _lib.check(rc, "pb2_group_barrier")
