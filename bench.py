@@ -15,10 +15,20 @@ Arms (``--impl``):
   reference  the unmodified reference from baseline/_ref (not installable: prints why)
 
 Prints ONE JSON line on rank 0.  ``value`` is device-timed (CUDA events, barrier +
-synchronize on both sides, max over ranks) with inputs resident on the device;
+synchronize on both sides, max over ranks) with inputs resident on the device: the
+K-step region is timed three times back to back and the median is reported (all three
+are in ``regions_ms``; a single 0.2 s region on 8 ranks moved by 25 % run to run).
 ``e2e`` repeats the measurement through the public API with a pinned-host -> device
 copy of every step's tokens/targets and a device -> host read of the loss inside the
 timed region.
+
+Extra keys (fused arm; ``PB2_BENCH_MINIMAL=1`` skips them), each measured after the
+headline so that it cannot disturb it:
+  bubble            measured idle share per stage from CUDA-event cell timelines, next to the ideal
+  recompute         ms/step with checkpoint='always' on the same model -> overhead vs the headline mode
+  eager_same_precision   this scheduler with stock torch.nn bodies under bf16 autocast, same step
+  pipe_single_process    (N > 1) the in-process ``Pipe`` over the same N GPUs, driven by rank 0 alone
+  hybrid            (N >= 2) 2 pipelines x N/2 stages: step time per gradient-reduction backend
 """
 from __future__ import annotations
 
@@ -46,7 +56,8 @@ def parse_args():
     ap.add_argument("--checkpoint", default="never", choices=["never", "except_last", "always"])
     ap.add_argument("--precision", default="bf16", choices=["bf16", "tf32", "fp32"])
     ap.add_argument("--layers", type=int, default=None, help="override layer count (debug only; marks result invalid)")
-    ap.add_argument("--timeline", action="store_true", help="also report the measured bubble (single-process only)")
+    ap.add_argument("--timeline", action="store_true", help="(kept for compatibility; the bubble is always measured)")
+    ap.add_argument("--minimal", action="store_true", help="headline and e2e only (same as PB2_BENCH_MINIMAL=1)")
     return ap.parse_args()
 
 
@@ -70,10 +81,36 @@ def reference_arm(args) -> int:
     return 0
 
 
+def _free(*objs) -> None:
+    import gc
+
+    import torch
+    for o in objs:
+        if o is not None and hasattr(o, "close"):
+            try:
+                o.close()
+            except Exception:  # noqa: BLE001
+                pass
+    gc.collect()
+    torch.cuda.empty_cache()
+
+
+def _store_wait(key: str, rank: int, setter: bool) -> None:
+    """Host-side rendezvous through the job's TCP store: no kernel sits on the waiting ranks' GPUs."""
+    import torch.distributed as dist
+    store = dist.distributed_c10d._get_default_store()
+    if setter:
+        store.set(key, "1")
+    else:
+        store.wait([key])
+
+
 def main() -> int:
     args = parse_args()
     if args.impl == "reference":
         return reference_arm(args)
+
+    import statistics
 
     import torch
     import torch.distributed as dist
@@ -85,6 +122,7 @@ def main() -> int:
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    minimal = args.minimal or bool(os.environ.get("PB2_BENCH_MINIMAL"))
     if world > 1:
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
@@ -104,7 +142,7 @@ def main() -> int:
         ops.require_native()            # fail loudly rather than fall back
 
     trainer = LMTrainer(cfg, n_stages=args.gpus, impl=args.impl, precision=args.precision,
-                        checkpoint=args.checkpoint, chunks=cfg.chunks)
+                        checkpoint=args.checkpoint, chunks=cfg.chunks, static_shapes=True)
     dev = trainer.device
 
     # ---- synthetic data: pinned host batches + device-resident copies ----------
@@ -112,21 +150,24 @@ def main() -> int:
     n_host = 4
     host_tok = [torch.randint(0, cfg.ntokens, (cfg.batch, cfg.bptt), generator=g).pin_memory() for _ in range(n_host)]
     host_tgt = [torch.randint(0, cfg.ntokens, (cfg.batch * cfg.bptt,), generator=g).pin_memory() for _ in range(n_host)]
-    # eager arm: targets go to the last stage (reference main.py:217); fused arm: they ride through
-    # the pipe next to the tokens so the last stage can fuse the loss behind the vocab projection
-    tgt_device = trainer.first_device if args.impl == "fused" else trainer.last_device
-    feeds_tgt = trainer.is_first if args.impl == "fused" else trainer.is_last
-    dev_tok = [t.to(trainer.first_device) for t in host_tok] if trainer.is_first else [None] * n_host
-    dev_tgt = [t.to(tgt_device) for t in host_tgt] if feeds_tgt else [None] * n_host
+
+    def feeds(tr, impl):
+        # eager arm: targets go to the last stage (reference main.py:217); fused arm: they ride through
+        # the pipe next to the tokens so the last stage can fuse the loss behind the vocab projection
+        tgt_device = tr.first_device if impl == "fused" else tr.last_device
+        feeds_tgt = tr.is_first if impl == "fused" else tr.is_last
+        tok = [t.to(tr.first_device) for t in host_tok] if tr.is_first else [None] * n_host
+        tgt = [t.to(tgt_device) for t in host_tgt] if feeds_tgt else [None] * n_host
+        return tok, tgt, tgt_device, feeds_tgt
+
+    dev_tok, dev_tgt, tgt_device, feeds_tgt = feeds(trainer, args.impl)
 
     def step_resident(k: int):
         trainer.step(dev_tok[k % n_host], dev_tgt[k % n_host])
 
-    h2d = d2h = 0
     last_loss = [float("nan")]
 
     def step_e2e(k: int):
-        nonlocal h2d, d2h
         tok = tgt = None
         if trainer.is_first:
             tok = host_tok[k % n_host].to(trainer.first_device, non_blocking=True)
@@ -136,19 +177,18 @@ def main() -> int:
         if trainer.is_last:
             last_loss[0] = float(loss.item())           # device -> host read of the step's result
 
-    launches0 = 0
     for k in range(args.warmup):
         step_resident(k)
     torch.cuda.synchronize()
 
-    if args.impl == "fused":
-        launches0 = ops.launch_count()
+    launches0 = ops.launch_count() if args.impl == "fused" else 0
     sampler = ClockSampler(local_rank)
     if rank == 0 and not os.environ.get("PB2_BENCH_NO_SAMPLER"):
         sampler.start()
-    ms = timed_steps(step_resident, args.steps, dev)
+    regions = [timed_steps(step_resident, args.steps, dev) for _ in range(3)]
     clocks = sampler.stop() if rank == 0 else {}
-    launches = (ops.launch_count() - launches0) if args.impl == "fused" else 0
+    ms = statistics.median(regions)
+    launches = (ops.launch_count() - launches0) // 3 if args.impl == "fused" else 0
     if world > 1:
         t = torch.tensor([launches], dtype=torch.int64, device=dev)
         dist.all_reduce(t)
@@ -167,16 +207,16 @@ def main() -> int:
     value = tokens * args.steps / (ms / 1e3)
     e2e = tokens * args.steps / (ms_e2e / 1e3)
     m_actual = len(torch.empty(cfg.batch).chunk(cfg.chunks))
+    dtype = "bf16" if args.precision == "bf16" else args.precision
 
     out = {
         "metric": METRIC, "value": round(value, 2), "unit": "tokens/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 4),
         "higher_is_better": True, "scaling": "strong",
-        # BASELINE.md's only throughput figure: ~3.2-4.1k tokens/s eyeballed from the
-        # reference's screenshots (other model size, 2 unnamed GPUs, profiler on); use 4.1k.
-        "vs_baseline": round(value / 4100.0, 3),
-        "dtype": "bf16" if args.precision == "bf16" else args.precision, "data": "synthetic",
-        "impl": args.impl,
+        # BASELINE.md holds no throughput number for this config (the reference publishes only memory
+        # screenshots of another configuration, its traces were stripped): nothing to divide by
+        "vs_baseline": None,
+        "dtype": dtype, "data": "synthetic", "impl": args.impl,
         "config": {
             "model": f"tutorial TransformerModel emsize {cfg.emsize} d_hid {cfg.nhid} layers {cfg.nlayers} "
                      f"nhead {cfg.nhead} vocab {cfg.ntokens}",
@@ -184,8 +224,10 @@ def main() -> int:
             "checkpoint": args.checkpoint, "parallelism": f"pp{args.gpus}",
             "step": "zero_grad+fwd+CE+bwd+clip_grad_norm(0.5)+Adam",
             "l2": "no flush: per-step working set (weights+grads+Adam state, >3 GB/GPU) >> 126 MB L2",
-            "launcher": "DistPipe (rank per stage, NCCL p2p)" if world > 1 else "Pipe (single process)",
+            "launcher": "DistPipe (rank per stage, batched NCCL p2p, static_shapes)" if world > 1 else "Pipe (single process)",
+            "timing": "median of 3 back-to-back regions of `steps` steps each",
         },
+        "regions_ms": [round(r, 3) for r in regions],
         "bubble_ideal": round(trainer.bubble, 4),
         "e2e": {"value": round(e2e, 2), "unit": "tokens/s", "ms_per_step": round(ms_e2e / args.steps, 4),
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "last_loss": last_loss[0]},
@@ -199,12 +241,187 @@ def main() -> int:
         t = torch.tensor([last_loss[0] if trainer.is_last else 0.0], dtype=torch.float64, device=dev)
         dist.all_reduce(t)
         out["e2e"]["last_loss"] = float(t.item())
+
+    if args.impl == "fused" and not minimal:
+        try:
+            extras(args, cfg, trainer, out, step_resident, dev, world, rank, local_rank, feeds, host_tok, host_tgt)
+        except Exception as e:  # noqa: BLE001 - the headline must survive a failing extra
+            import traceback
+            out["extras_error"] = f"{type(e).__name__}: {e}"
+            if rank == 0:
+                traceback.print_exc()
     if rank == 0:
         print(json.dumps(out), flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
     return 0
+
+
+def extras(args, cfg, trainer, out, step_resident, dev, world, rank, local_rank, feeds, host_tok, host_tgt) -> None:
+    """Measurements reported next to the headline (see the module docstring).  Every rank runs the same
+    sequence; a watchdog prints the headline alone if anything here stalls."""
+    import threading
+
+    import torch
+    import torch.distributed as dist
+
+    from pipe_b200.models.trainer import LMTrainer
+    from pipe_b200.utils.benchkit import timed_steps
+
+    budget_s = float(os.environ.get("PB2_BENCH_EXTRAS_BUDGET_S", "420"))
+
+    def bail():
+        if rank == 0:
+            out["extras_error"] = f"extras exceeded {budget_s:.0f} s; reporting what was measured"
+            print(json.dumps(out), flush=True)
+        os._exit(0)
+
+    dog = threading.Timer(budget_s, bail)
+    dog.daemon = True
+    dog.start()
+    steps = max(3, min(args.steps, 10))
+    n_host = len(host_tok)
+    tokens = cfg.tokens_per_step
+
+    # ---- measured bubble ---------------------------------------------------------------------
+    if world > 1:
+        trainer.pipe.timeline = True
+        for k in range(3):
+            step_resident(k)
+        summary = trainer.pipe.timeline_summary()
+        trainer.pipe.timeline = False
+        if summary:
+            out["bubble"] = {
+                "ideal": out["bubble_ideal"],
+                "measured_per_stage": [round(s["bubble"], 4) for s in summary],
+                "measured_mean": round(sum(s["bubble"] for s in summary) / len(summary), 4),
+                "fwd_busy_ms": [round(s["fwd_busy_ms"], 3) for s in summary],
+                "bwd_busy_ms": [round(s["bwd_busy_ms"], 3) for s in summary],
+                "pipe_span_ms": round(summary[0]["pipe_span_ms"], 3),
+                "how": "CUDA events around every cell on each rank's stream; bubble = 1 - busy / stage-0 span",
+            }
+    else:
+        out["bubble"] = {"ideal": 0.0, "measured_mean": 0.0, "how": "one stage: no fill / drain"}
+
+    # ---- recompute overhead: checkpoint='always' on the same model ----------------------------------
+    base_ms = out["ms_per_step"]
+    if args.checkpoint == "never":
+        trainer.set_checkpoint("always")
+        for k in range(2):
+            step_resident(k)
+        ms_always = timed_steps(step_resident, steps, dev) / steps
+        trainer.set_checkpoint(args.checkpoint)
+        peak = torch.cuda.max_memory_allocated(dev) / 2**20
+        out["recompute"] = {"always_ms_per_step": round(ms_always, 4),
+                            "overhead_vs_never": round(ms_always / base_ms - 1.0, 4),
+                            "note": "with 20 rows / 8 chunks 'except_last' checkpoints every micro-batch too (reference quirk)"}
+        out["peak_mib_rank0"] = round(peak, 1)
+
+    # ---- the same step on stock torch.nn bodies, same precision ---------------------------------------
+    _free(trainer)          # closes the pipe / optimizer and drops the model (the caller's reference stays, hollow)
+    if not os.environ.get("PB2_BENCH_NO_EAGER"):
+        eager = LMTrainer(cfg, n_stages=args.gpus, impl="eager", precision="bf16", checkpoint=args.checkpoint,
+                          chunks=cfg.chunks, static_shapes=True)
+        e_tok, e_tgt, _, _ = feeds(eager, "eager")
+
+        def step_eager(k: int):
+            eager.step(e_tok[k % n_host], e_tgt[k % n_host])
+
+        for k in range(3):
+            step_eager(k)
+        ms_eager = timed_steps(step_eager, steps, dev) / steps
+        out["eager_same_precision"] = {"ms_per_step": round(ms_eager, 4), "value": round(tokens / (ms_eager / 1e3), 2),
+                                       "dtype": "bf16 autocast", "what": "this scheduler, stock torch.nn stage bodies (cuBLAS + ATen)"}
+        _free(eager)
+        del eager, e_tok, e_tgt
+        _free()
+
+    # ---- the in-process Pipe over the same GPUs, driven by rank 0 alone --------------------------------
+    if world > 1 and not os.environ.get("PB2_BENCH_NO_PIPE"):
+        dist.barrier()
+        torch.cuda.synchronize()
+        if rank == 0:
+            try:
+                single = _SingleProcess(cfg, args, host_tok, host_tgt)
+                out["pipe_single_process"] = single.run(steps)
+            except Exception as e:  # noqa: BLE001
+                out["pipe_single_process"] = {"error": f"{type(e).__name__}: {e}"}
+            torch.cuda.set_device(local_rank)
+        _store_wait("pb2_pipe_single_done", rank, setter=rank == 0)
+
+    # ---- Pipe-inside-DDP hybrid: 2 pipelines x world/2 stages ------------------------------------------
+    if world >= 2 and world % 2 == 0 and not os.environ.get("PB2_BENCH_NO_HYBRID"):
+        stages = world // 2
+        hy = {"layout": f"2 pipelines x {stages} stages", "global_batch": 2 * cfg.batch, "steps": steps}
+        tr = None
+        for backend in ("nccl", "allreduce", "none", "gather"):
+            if tr is None:
+                tr = LMTrainer(cfg, n_stages=stages, impl="fused", checkpoint=args.checkpoint, chunks=cfg.chunks,
+                               replicas=2, reduce_backend=backend, static_shapes=True)
+                h_tok, h_tgt, _, _ = feeds(tr, "fused")
+            else:
+                tr.opt.close()
+                tr.opt = tr.pipe.make_optimizer(reduce_backend=backend, max_tokens=cfg.batch * cfg.bptt, lr=1e-4,
+                                                max_norm=0.5)
+
+            def step_h(k: int):
+                tr.step(h_tok[k % n_host], h_tgt[k % n_host])
+
+            for k in range(3):
+                step_h(k)
+            ms_h = timed_steps(step_h, steps, dev) / steps
+            hy[f"{backend}_ms"] = round(ms_h, 4)
+        hy["tokens_per_s_gather"] = round(2 * tokens / (hy["gather_ms"] / 1e3), 2)
+        for backend in ("nccl", "allreduce", "gather"):
+            hy[f"exposed_reduce_us_{backend}"] = round((hy[f"{backend}_ms"] - hy["none_ms"]) * 1e3, 1)
+        stash = getattr(tr.opt, "_stash", None)
+        if stash is not None:
+            hy["gather_nvlink_bytes_per_step_per_rank"] = stash.bytes_pushed_per_token * cfg.batch * cfg.bptt
+        (st,) = tr.opt.devs.values()
+        hy["dense_grad_bytes_per_rank"] = sum(p.numel() for p in st.params) * 4
+        hy["what"] = ("nccl = bucketed async dist.all_reduce under the wgrad GEMMs (DDP-style baseline); allreduce = the "
+                      "NVLink all-reduce kernel per bucket under the wgrad GEMMs; gather = wgrad operands stored into "
+                      "every replica during backward, averaged inside the wgrad GEMM; none = no reduction (timing only)")
+        out["hybrid"] = hy
+        _free(tr)
+    dog.cancel()
+
+
+class _SingleProcess:
+    """The reference-shaped launcher — one process, one worker thread per GPU — on the same config."""
+
+    def __init__(self, cfg, args, host_tok, host_tgt) -> None:
+        from pipe_b200.models.trainer import LMTrainer
+        self.trainer = LMTrainer(cfg, n_stages=args.gpus, impl="fused", checkpoint=args.checkpoint, chunks=cfg.chunks,
+                                 single_process=True)
+        self.tok = [t.to(self.trainer.first_device) for t in host_tok]
+        self.tgt = [t.to(self.trainer.first_device) for t in host_tgt]
+        self.cfg = cfg
+
+    def run(self, steps: int):
+        import torch
+        tr = self.trainer
+        n = len(self.tok)
+        devices = list(tr.pipe.devices)
+
+        def sync():
+            for d in devices:
+                torch.cuda.synchronize(d)
+
+        for k in range(3):
+            tr.step(self.tok[k % n], self.tgt[k % n])
+        sync()
+        t0 = time.perf_counter()
+        for k in range(steps):
+            tr.step(self.tok[k % n], self.tgt[k % n])
+        sync()
+        ms = (time.perf_counter() - t0) * 1e3 / steps
+        res = {"ms_per_step": round(ms, 4), "value": round(self.cfg.tokens_per_step / (ms / 1e3), 2),
+               "launcher": "Pipe (one process, worker thread per GPU, peer copies on copy streams)",
+               "timing": "host clock between full device synchronisations (the other ranks idle on the host)"}
+        _free(tr)
+        return res
 
 
 if __name__ == "__main__":

@@ -82,7 +82,9 @@ int pb2_gemm_bf16(const pb2_gemm_desc* desc, void* workspace, size_t workspace_b
  * The first call on each device also resolves the array's device address (cudaGetSymbolAddress with
  * that device current): issue it at start-up, before any stream capture begins.  Every call uses the
  * same array and inherits its previous contents; the counters are cleared on `stream` before each
- * launch.  Calls that may overlap on the GPU race on it: serialise them.  Allocates nothing. */
+ * launch.  Calls that may overlap on the GPU race on it: serialise them.  `stream` must be a stream of the
+ * device that is current when the call is made (the scratch address is looked up for the current device).
+ * Allocates nothing. */
 #define PB2_GEMM_STATIC_SCRATCH_BYTES (16u * 1024u * 1024u)
 size_t pb2_gemm_noalloc_max_scratch_bytes(void);
 int pb2_gemm_bf16_noalloc(const pb2_gemm_desc* desc, cudaStream_t stream);

@@ -34,6 +34,8 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <thread>
+
 #include "common.cuh"
 #include "pipe_b200.h"
 
@@ -1031,6 +1033,9 @@ extern "C" int pb2_gemm_bf16(const pb2_gemm_desc* d, void* workspace, size_t wor
 // Two calls that can overlap on the GPU (different streams, or different host threads on
 // different streams) would race on the array: serialise them.
 //
+// The array is looked up for the device that is current at the time of the call, so `stream` must
+// belong to the current device (a stream of another GPU would be given this GPU's scratch address).
+//
 // Nothing here calls cudaMalloc, cudaFree or any allocating library routine.
 // ---------------------------------------------------------------------------------------
 static __device__ __align__(256) unsigned char g_static_scratch[PB2_GEMM_STATIC_SCRATCH_BYTES + PB2_GEMM_COUNTER_BYTES];
@@ -1054,8 +1059,7 @@ extern "C" int pb2_gemm_bf16_noalloc(const pb2_gemm_desc* d, cudaStream_t stream
     }
     if (s_scratch_state[dev].load(std::memory_order_acquire) == 0) {
         // one-time set-up for this device (the current one): resolve the symbol to a device address
-        while (s_scratch_lock.test_and_set(std::memory_order_acquire)) {
-        }
+        while (s_scratch_lock.test_and_set(std::memory_order_acquire)) std::this_thread::yield();
         int rc = 0;
         if (s_scratch_state[dev].load(std::memory_order_relaxed) == 0) {
             void* p = nullptr;

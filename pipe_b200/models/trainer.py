@@ -73,15 +73,26 @@ def clip_grad_norm_(parameters: Iterable[nn.Parameter], max_norm: float,
 
 
 class LMTrainer:
+    """``replicas > 1`` (with ``torchrun``: world = ``replicas * n_stages``) builds the Pipe-inside-DDP hybrid:
+    rank = ``replica * n_stages + stage``; every replica is fed its own mini-batch of ``cfg.batch`` rows and the
+    stages' gradients are averaged over the replica group (``reduce_backend``: ``gather | allreduce | nccl``,
+    see :class:`~pipe_b200.ops.optim.FusedClipAdam`)."""
+
     def __init__(self, cfg: TransformerConfig, *, n_stages: int = 1, impl: str = "eager",
                  precision: str = "bf16", checkpoint: str = "never", chunks: Optional[int] = None,
-                 lr: float = 1e-4, max_norm: float = 0.5, seed: int = 0) -> None:
+                 lr: float = 1e-4, max_norm: float = 0.5, seed: int = 0, replicas: int = 1,
+                 reduce_backend: str = "gather", static_shapes: bool = False, timeline: bool = False,
+                 single_process: bool = False) -> None:
+        """``single_process=True`` builds the in-process :class:`~pipe_b200.Pipe` over ``n_stages`` local
+        GPUs even when a process group exists (benchmarks compare the two launchers inside one job)."""
         self.cfg = cfg
         self.impl = impl
         self.precision = precision
         self.max_norm = max_norm
         self.chunks = chunks or cfg.chunks
-        self.distributed = dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+        self.replicas = int(replicas)
+        self.distributed = (not single_process and dist.is_available() and dist.is_initialized()
+                            and dist.get_world_size() > 1)
         torch.manual_seed(seed)
 
         if precision == "tf32":
@@ -91,17 +102,26 @@ class LMTrainer:
         if self.distributed:
             self.rank = dist.get_rank()
             self.world = dist.get_world_size()
-            if n_stages != self.world:
-                raise ValueError("with torchrun, n_stages must equal the world size")
+            if n_stages * self.replicas != self.world:
+                raise ValueError("with torchrun, n_stages * replicas must equal the world size")
             self.device = torch.device("cuda", torch.cuda.current_device())
-            body: nn.Module = build_stage(cfg, self.rank, self.world, self.device, impl, seed)
+            stage_idx = self.rank % n_stages
+            body: nn.Module = build_stage(cfg, stage_idx, n_stages, self.device, impl, seed)
             body = self._wrap(body)
-            self.pipe: nn.Module = DistPipe(body, chunks=self.chunks, checkpoint=checkpoint, device=self.device)
+            if self.replicas > 1:
+                from ..parallel.hybrid import HybridPipe
+                self.pipe = HybridPipe(body, stages=n_stages, chunks=self.chunks, checkpoint=checkpoint,
+                                       device=self.device, static_shapes=static_shapes, timeline=timeline)
+            else:
+                self.pipe = DistPipe(body, chunks=self.chunks, checkpoint=checkpoint, device=self.device,
+                                     static_shapes=static_shapes, timeline=timeline)
             self.first_device = self.device
             self.last_device = self.device
             self.is_first = self.pipe.is_first
             self.is_last = self.pipe.is_last
         else:
+            if self.replicas != 1:
+                raise ValueError("replicas > 1 needs one process per GPU (torchrun)")
             self.rank, self.world = 0, 1
             devices = list(range(n_stages))
             model = build_stages(cfg, devices, impl, seed=seed)
@@ -117,10 +137,36 @@ class LMTrainer:
         self.params = params
         if impl == "fused":
             from ..ops.optim import FusedClipAdam
-            self.opt = FusedClipAdam(self.pipe, lr=lr, max_norm=max_norm,
-                                     distributed=self.distributed)
+            if self.replicas > 1:
+                self.opt = self.pipe.make_optimizer(reduce_backend=reduce_backend, max_tokens=cfg.batch * cfg.bptt,
+                                                    lr=lr, max_norm=max_norm)
+            else:
+                self.opt = FusedClipAdam(self.pipe, lr=lr, max_norm=max_norm, distributed=self.distributed)
         else:
+            if self.replicas > 1:
+                raise ValueError("the hybrid layout is implemented for impl='fused'")
             self.opt = torch.optim.Adam(params, lr=lr, fused=True)
+
+    def set_checkpoint(self, mode: str) -> None:
+        """Switch the checkpoint mode of the running pipeline (benchmarks sweep the modes on one model)."""
+        if mode not in ("always", "except_last", "never"):
+            raise ValueError("checkpoint is not one of 'always', 'except_last', or 'never'")
+        if isinstance(self.pipe, DistPipe):
+            self.pipe.checkpoint = mode
+        else:
+            self.pipe.checkpoint = mode
+            self.pipe.pipeline.checkpoint_stop = {"always": self.pipe.chunks, "except_last": self.pipe.chunks - 1,
+                                                  "never": 0}[mode]
+
+    def close(self) -> None:
+        """Stop worker threads, detach optimizer hooks and drop the model so its memory can be reused."""
+        if getattr(self, "opt", None) is not None and hasattr(self.opt, "close"):
+            self.opt.close()
+        if getattr(self, "pipe", None) is not None and hasattr(self.pipe, "close"):
+            self.pipe.close()
+        self.opt = None
+        self.pipe = None
+        self.params = []
 
     def _wrap(self, stage: nn.Module) -> nn.Module:
         if self.impl == "eager" and self.precision == "bf16":

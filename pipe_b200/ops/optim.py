@@ -373,5 +373,8 @@ class FusedClipAdam:
         notified too)."""
         if self._backward_done in wgrad.pre_flush_hooks:
             wgrad.pre_flush_hooks.remove(self._backward_done)
+        for lg in getattr(self, "_lgs", []):
+            if lg.on_flushed == self._bucket_ready:
+                lg.on_flushed = None
         if self._stash is not None:
             self._stash.close()

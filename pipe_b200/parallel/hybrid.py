@@ -63,12 +63,12 @@ class HybridPipe(DistPipe):
     """
 
     def __init__(self, stage: nn.Module, stages: int, chunks: int = 1, checkpoint: str = "except_last",
-                 device: Optional[torch.device] = None, transport: str = "nccl") -> None:
+                 device: Optional[torch.device] = None, transport: str = "nccl", **dist_pipe_kwargs) -> None:
         pipe_group, rep_group, replica, stage_idx, replicas = hybrid_groups(stages)
         world = dist.get_world_size()
         pipelines = [[r * stages + j for j in range(stages)] for r in range(world // stages)]
         super().__init__(stage, chunks=chunks, checkpoint=checkpoint, group=pipe_group, device=device,
-                         transport=transport, pipelines=pipelines)
+                         transport=transport, pipelines=pipelines, **dist_pipe_kwargs)
         self.replica_group = rep_group
         self.replica = replica
         self.replicas = replicas
@@ -79,6 +79,9 @@ class HybridPipe(DistPipe):
         ``max_tokens`` = tokens of one replica's mini-batch), ``"allreduce"`` (bucketed NVLink all-reduce kernel
         under the wgrad GEMMs) or ``"nccl"`` (bucketed asynchronous NCCL all-reduce, the baseline)."""
         from ..ops.optim import FusedClipAdam
+        if reduce_backend == "none":
+            # measurement only: no averaging at all (the replicas drift apart); what a step costs without the reduction
+            return FusedClipAdam(self.stage, distributed=True, group=self.group, **adam_kwargs)
         return FusedClipAdam(self.stage, distributed=True, group=self.group, replica_group=self.replica_group,
                              replicas=self.replicas, reduce_backend=reduce_backend, max_tokens=max_tokens,
                              **adam_kwargs)
