@@ -221,7 +221,11 @@ def test_layer_stack_is_bit_identical_to_per_layer_calls(dropout):
             assert torch.equal(xa.grad, xb.grad)
             for a, b in zip(layers_a, layers_b):
                 for (n, pa), pb in zip(a.named_parameters(), b.parameters()):
-                    assert torch.equal(pa.grad, pb.grad), (step, n)
+                    if pa.dim() >= 2:
+                        assert torch.equal(pa.grad, pb.grad), (step, n)       # one GEMM, same operands
+                    else:
+                        # bias / LayerNorm gradients are summed with fp32 atomics: order varies run to run
+                        assert rel(pa.grad, pb.grad) < 1e-5, (step, n, rel(pa.grad, pb.grad))
         else:
             assert torch.isfinite(ya.float()).all() and torch.isfinite(xa.grad.float()).all()
         for l in layers_a + layers_b:
