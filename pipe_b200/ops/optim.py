@@ -275,8 +275,17 @@ class FusedClipAdam:
         else:
             F2.sumsq(st.flat, st.normsq)
         st.total_normsq.copy_(st.normsq)
-        if self.distributed:
-            dist.all_reduce(st.total_normsq, group=self.group)          # over the stages of this pipeline
+        # The local sums come from fp32 atomics, so two replicas holding identical gradients can still differ in
+        # the last bits of their norm — and then in the clip factor and the weights.  Summing every rank's value
+        # and dividing by the replica count gives all ranks the same number.
+        stages = dist.get_world_size(self.group) if self.distributed else 1
+        if self.distributed and dist.get_world_size() == stages * self.replicas:
+            dist.all_reduce(st.total_normsq)                             # stages x replicas = the whole job
+        else:
+            dist.all_reduce(st.total_normsq, group=self.replica_group)
+            if self.distributed:
+                dist.all_reduce(st.total_normsq, group=self.group)      # over the stages of this pipeline
+        st.total_normsq.mul_(1.0 / self.replicas)
 
     def _total_normsq(self) -> None:
         """Finish the squared norm on every device, then share the total."""

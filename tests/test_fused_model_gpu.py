@@ -249,7 +249,7 @@ def test_layer_stack_replays_dropout_under_checkpoint():
             return t.transpose(0, 1).contiguous()
 
     from pipe_b200 import WithDevice
-    pipe = Pipe(nn.Sequential(WithDevice(SeqFirst(), dev), *layers, WithDevice(SeqFirst(), dev)), chunks=2, checkpoint="always")
+    pipe = Pipe(nn.Sequential(WithDevice(SeqFirst(), "cuda:0"), *layers, WithDevice(SeqFirst(), "cuda:0")), chunks=2, checkpoint="always")
     out = pipe(x.clone().requires_grad_()).local_value()
     # forward under no_grad + recompute under grad must produce the same output bits
     out.float().sum().backward()
