@@ -87,6 +87,7 @@ class FusedClipAdam:
         self.module = module
         self._cpu: Optional[torch.optim.Optimizer] = None
         self._armed = True             # zero_grad() ran since the last step()
+        self._accumulated_seen = wgrad.accumulated_flushes
         self._works: List = []
         self._reduce_stream: Optional[torch.cuda.Stream] = None
         self._stash = None
@@ -334,6 +335,9 @@ class FusedClipAdam:
         if self._cpu is not None:
             self._step_cpu()
             return
+        if wgrad.accumulated_flushes != self._accumulated_seen:
+            self._accumulated_seen = wgrad.accumulated_flushes
+            self._armed = False            # gradients were accumulated over several backward passes
         if not self._armed:
             # step() without zero_grad() since the last one (gradient accumulation, a retried step): the norm
             # scalar still holds the previous step's sum and the matrix gradients were accumulated outside the

@@ -65,6 +65,11 @@ def stash_epoch() -> int:
     return _stash_epoch
 
 
+#: number of wgrad GEMMs that *accumulated* into an existing gradient (gradient accumulation over several
+#: backward passes); :class:`~pipe_b200.ops.optim.FusedClipAdam` re-derives the norm when it moved
+accumulated_flushes = 0
+
+
 _defer_depth = 0
 _nested_depth = 0
 _callback_queued = False
@@ -198,6 +203,12 @@ class LinearGrad:
         if fresh:
             w._pb2_fresh = False
             w._pb2_sumsq_done = normsq is not None
+        else:
+            # a second backward pass before the optimizer step: the squared norm summed by the first pass's
+            # epilogue no longer describes this gradient — the optimizer has to measure it again
+            global accumulated_flushes
+            accumulated_flushes += 1
+            w._pb2_sumsq_done = False
         self.used = 0
         if self.on_flushed is not None:
             self.on_flushed(self)

@@ -257,3 +257,76 @@ def test_layer_stack_replays_dropout_under_checkpoint():
     g_always = [p.grad.clone() for p in pipe.parameters()]
     assert all(torch.isfinite(g).all() for g in g_always)
     pipe.close()
+
+
+# ---------------------------------------------------------------------------------------------------
+# the autograd contract of the fused modules (INTEGRATION.md "Weight gradients and autograd")
+# ---------------------------------------------------------------------------------------------------
+def test_gradient_accumulation_over_two_backward_passes():
+    """Two backward passes without zero_grad() accumulate (the second wgrad GEMM adds), and the optimizer clips
+    with the norm of the accumulated gradient, not with a stale or double-counted one."""
+    from pipe_b200.models.fused import FusedEncoderLayer
+    from pipe_b200.ops import wgrad
+    from pipe_b200.ops.optim import FusedClipAdam
+    torch.manual_seed(0)
+    E, H, FF, S, NB = 256, 4, 512, 16, 4
+    layer = FusedEncoderLayer(E, H, FF, 0.0).to(dev)
+    opt = FusedClipAdam(layer, lr=1e-3, max_norm=1e9)
+    xa = torch.randn(S, NB, E, device=dev).bfloat16()
+    xb = torch.randn(S, NB, E, device=dev).bfloat16()
+    single = {}
+    for name, x in (("a", xa), ("b", xb)):
+        opt.zero_grad()
+        layer(x).float().pow(2).sum().backward()
+        wgrad.flush_pending()
+        single[name] = {n: p.grad.clone() for n, p in layer.named_parameters()}
+    opt.zero_grad()
+    layer(xa).float().pow(2).sum().backward()
+    layer(xb).float().pow(2).sum().backward()
+    wgrad.flush_pending()
+    total_sq = 0.0
+    for n, p in layer.named_parameters():
+        want = single["a"][n] + single["b"][n]
+        assert rel(p.grad, want) < 1e-3, (n, rel(p.grad, want))
+        total_sq += float(p.grad.double().pow(2).sum())
+    opt.step()
+    assert abs(opt.grad_norm() - total_sq ** 0.5) / total_sq ** 0.5 < 1e-3
+    # ... and a step() repeated without zero_grad() measures the same gradients again instead of adding up
+    opt.step()
+    assert abs(opt.grad_norm() - total_sq ** 0.5) / total_sq ** 0.5 < 1e-3
+
+
+def test_stock_optimizer_and_set_to_none_work_with_fused_modules():
+    """torch.optim.Adam + zero_grad(set_to_none=True): gradient buffers are re-created every step, the bf16
+    weight shadows follow the in-place update through the version counter."""
+    from pipe_b200.models.fused import FusedEncoderLayer
+    torch.manual_seed(0)
+    E, H, FF, S, NB = 256, 4, 512, 16, 4
+    layers = nn.Sequential(*[FusedEncoderLayer(E, H, FF, 0.0).to(dev) for _ in range(2)])
+    from pipe_b200.partition import PipeSequential
+    model = PipeSequential(*layers)
+    opt = torch.optim.Adam(model.parameters(), lr=1e-3)
+    x = torch.randn(S, NB, E, device=dev).bfloat16()
+    target = torch.randn(S, NB, E, device=dev)
+    losses = []
+    for _ in range(8):
+        opt.zero_grad(set_to_none=True)
+        loss = (model(x).float() - target).pow(2).mean()
+        loss.backward()
+        assert all(p.grad is not None for p in model.parameters())
+        opt.step()
+        losses.append(loss.item())
+    assert losses[-1] < losses[0], losses
+
+
+def test_autograd_grad_does_not_see_weight_gradients():
+    """Documented limit: weight gradients are written to ``.grad`` by the deferred wgrad GEMM, outside the
+    autograd graph, so ``torch.autograd.grad`` with respect to a fused weight yields nothing."""
+    from pipe_b200.models.fused import FusedEncoderLayer
+    from pipe_b200.ops import wgrad
+    layer = FusedEncoderLayer(256, 4, 512, 0.0).to(dev)
+    x = torch.randn(8, 2, 256, device=dev).bfloat16().requires_grad_()
+    y = layer(x)
+    gx, gw = torch.autograd.grad(y.float().sum(), [x, layer.linear1.weight], allow_unused=True)
+    wgrad.flush_pending()
+    assert gx is not None and gw is None
