@@ -186,6 +186,16 @@ int pb2_attention_fwd(const void* qkv, void* out, int NB, int S, int H, int D, i
 int pb2_attention_bwd(const void* qkv, const void* dout, void* dqkv, int NB, int S, int H, int D, int causal,
                       float drop_p, unsigned long long seed, unsigned long long rng_stream, cudaStream_t stream);
 
+/* ---- flash attention on tcgen05 / TMEM / TMA: any S, head_dim 64 / 128 / 256, same packed layout ------------
+ * softmax(QK^T/sqrt(D)) V with probability dropout and optional causal mask, computed in blocks of keys with a
+ * running maximum / sum (no S x S matrix anywhere).  `lse` (optional for inference, required by the backward)
+ * receives log-sum-exp of the scaled scores per (sequence, head, query): fp32 [NB * H, S].
+ * Reference counterpart: nn.MultiheadAttention core (main.py:148) at sequence lengths up to the positional
+ * table's 5000 (main.py:59); SURVEY.md K3. */
+int pb2_flash_attention_fwd(const void* qkv, void* out, float* lse, int NB, int S, int H, int D, int causal,
+                            float drop_p, unsigned long long seed, unsigned long long rng_stream,
+                            cudaStream_t stream);
+
 /* ---- multi-tensor fused clip + Adam ---------------------------------------------------------
  * `table_dev` is a device array of n_tensors descriptors sorted by tile_start; a tensor of
  * [rows, cols] owns ceil(rows/32) * ceil(cols/64) consecutive tiles.  w/g/m/v are fp32; w16

@@ -1,0 +1,400 @@
+// Flash attention for sm_100a on tcgen05 / TMEM / TMA: any sequence length, head_dim 64 / 128 / 256 (forward),
+// causal flag, probability dropout, on the packed QKV layout of the encoder layer ([T, 3E], row = s * NB + n).
+//
+// Forward, one CTA per (128 query rows, head, sequence):
+//   warp 0      TMA producer: Q once, then K / V blocks of BN keys through a 2-stage ring.  The tiles come
+//               straight out of the packed tensor with a 3-D tensor map (column, n, s) and land 128-byte
+//               swizzled; nothing is gathered or transposed by threads.
+//   warp 1      one elected lane issues the MMAs: S = Q K^T (both operands K-major) into one of two S
+//               accumulators in TMEM, and O += P V with P read from shared memory (K-major) and V used as it
+//               lies in memory, [keys, D] with D contiguous, as an MN-major B operand — no V^T copy.
+//   warps 2-5   online softmax, one thread per query row (the TMEM lane it can read): S from TMEM, running
+//               max / sum in registers, dropout from the counter RNG, P to shared memory as bf16; when the
+//               running max moved, the O accumulator is rescaled in place (tcgen05.ld / tcgen05.st).
+// The two S accumulators let the tensor core compute S of block j + 1 while the softmax warps work on block j.
+// Per row the kernel also writes LSE = log sum exp of the scaled scores, which is all the backward needs to
+// recompute the probabilities.
+//
+// Backward: see the second half of this file.
+//
+// Reference counterpart: the attention core of nn.MultiheadAttention (main.py:148) for sequences up to the
+// positional table's 5000 (main.py:59); SURVEY.md K3, W6.  The S <= 32 single-tile kernels of
+// attention_tc.cu stay the path for BASELINE's 25-token sequences (a UMMA pipeline costs more than it saves
+// there); this file is the path beyond.
+#include <math.h>
+
+#include "common.cuh"
+#include "pipe_b200.h"
+
+namespace pb2 {
+
+constexpr int kFaBM = 128;          // query rows per CTA = TMEM lanes
+constexpr int kFaThreads = 192;     // producer warp, MMA warp, four softmax warps
+
+// 3-D tile load: coordinates (column, n, s)
+__device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int32_t c0,
+                                            int32_t c1, int32_t c2) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+        ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
+
+__device__ __forceinline__ void tmem_st_32x16(uint32_t taddr, const uint32_t (&r)[16]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+        ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
+        "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+        : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() {
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+}
+
+// Shared-memory descriptor of an MN-major bf16 operand stored as rows of 64 MN-elements (128 bytes, the row
+// index is K) with the 128-byte swizzle: 8-row K groups are 1024 bytes apart (SBO); further 64-element MN
+// atoms start `lbo_bytes` apart (LBO).  This is what a TMA box of [rows, 64 columns] of a row-major matrix
+// whose *rows* are the reduction dimension gives (V for P V, dO for P^T dO, ...).
+__device__ __forceinline__ uint64_t umma_desc_mn_sw128(uint32_t smem_addr, uint32_t lbo_bytes) {
+    uint64_t d = 0;
+    d |= static_cast<uint64_t>((smem_addr & 0x3FFFF) >> 4);
+    d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFF) << 16;
+    d |= static_cast<uint64_t>(1024 >> 4) << 32;
+    d |= static_cast<uint64_t>(1) << 46;
+    d |= static_cast<uint64_t>(2) << 61;
+    return d;
+}
+
+// bf16 x bf16 -> fp32 instruction descriptor with explicit operand majors (0 = K-major, 1 = MN-major)
+__host__ __device__ __forceinline__ uint32_t umma_idesc_bf16_major(uint32_t m, uint32_t n, uint32_t a_mn, uint32_t b_mn) {
+    return umma_idesc_bf16(m, n) | (a_mn << 15) | (b_mn << 16);
+}
+
+struct FaArgs {
+    int NB, S, H, D;
+    int causal;
+    float scale_log2;        // 1/sqrt(D) * log2(e)
+    float drop_p;
+    unsigned long long seed, stream;
+    __nv_bfloat16* out;      // [T, E]
+    float* lse;              // [NB * H, S] natural log of the row sums of exp(scaled scores)
+    long long ld_out;        // E
+};
+
+struct __align__(8) FaCtl {
+    uint64_t q_full;
+    uint64_t kv_full[2];
+    uint64_t kv_empty[2];
+    uint64_t s_full[2];
+    uint64_t p_full;
+    uint64_t pv_done;
+    uint32_t tmem_base;
+    uint32_t pad;
+};
+
+// element (row, col) of a [rows][64] bf16 tile with the 128-byte swizzle, as a byte offset
+__device__ __forceinline__ uint32_t sw128_offset(uint32_t row, uint32_t col) {
+    return row * 128u + ((((col >> 3) ^ (row & 7u)) << 4) | ((col & 7u) << 1));
+}
+
+template <int D, int BN>
+__global__ void __launch_bounds__(kFaThreads, 1)
+flash_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_constant__ CUtensorMap tmap_kv, const FaArgs a) {
+    constexpr int KB = D / 64;                       // 64-wide blocks of the head dimension
+    constexpr uint32_t kQBytes = kFaBM * D * 2;
+    constexpr uint32_t kKBytes = BN * D * 2;
+    constexpr uint32_t kPBytes = kFaBM * BN * 2;
+    constexpr uint32_t kTmemCols = (2 * 128 + D) > 256 ? 512 : 256;
+    constexpr uint32_t kOCol = 256;                  // O accumulator behind the two S accumulators
+    static_assert(2 * 128 + D <= 512, "TMEM budget");
+
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sQ = smem;
+    uint8_t* sK = sQ + kQBytes;                      // [2][KB][BN][128 B]
+    uint8_t* sV = sK + 2 * kKBytes;                  // [2][KB][BN][128 B]
+    uint8_t* sP = sV + 2 * kKBytes;                  // [BN / 64][128][128 B]
+    FaCtl* ctl = reinterpret_cast<FaCtl*>(sP + kPBytes);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int q0 = blockIdx.x * kFaBM;
+    const int h = blockIdx.y, n = blockIdx.z;
+    const int E = a.H * D;
+    int n_blocks = (a.S + BN - 1) / BN;
+    if (a.causal) {
+        const int last = (q0 + kFaBM - 1 < a.S - 1 ? q0 + kFaBM - 1 : a.S - 1);
+        n_blocks = last / BN + 1;
+    }
+
+    pdl_launch_dependents();
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmap_qkv);
+        tma_prefetch_desc(&tmap_kv);
+        mbar_init(&ctl->q_full, 1);
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&ctl->kv_full[s], 1);
+            mbar_init(&ctl->kv_empty[s], 1);
+            mbar_init(&ctl->s_full[s], 1);
+        }
+        mbar_init(&ctl->p_full, 128);
+        mbar_init(&ctl->pv_done, 1);
+        fence_mbar_init();
+    }
+    if (warp == 1) {
+        tmem_alloc(&ctl->tmem_base, kTmemCols);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = ctl->tmem_base;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (elect_one()) {
+            pdl_wait();
+            mbar_expect_tx(&ctl->q_full, kQBytes);
+            for (int kb = 0; kb < KB; ++kb)
+                tma_load_3d(sQ + kb * (kFaBM * 128), &tmap_qkv, &ctl->q_full, h * D + kb * 64, n, q0);
+            for (int j = 0; j < n_blocks; ++j) {
+                const int s = j & 1;
+                mbar_wait(&ctl->kv_empty[s], ((j >> 1) & 1) ^ 1);
+                mbar_expect_tx(&ctl->kv_full[s], 2 * kKBytes);
+                for (int kb = 0; kb < KB; ++kb) {
+                    tma_load_3d(sK + s * kKBytes + kb * (BN * 128), &tmap_kv, &ctl->kv_full[s], E + h * D + kb * 64, n, j * BN);
+                    tma_load_3d(sV + s * kKBytes + kb * (BN * 128), &tmap_kv, &ctl->kv_full[s], 2 * E + h * D + kb * 64, n, j * BN);
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        const uint32_t idesc_s = umma_idesc_bf16_major(kFaBM, BN, 0, 0);
+        const uint32_t idesc_o = umma_idesc_bf16_major(kFaBM, D, 0, 1);
+        auto issue_qk = [&](int j) {
+            const int s = j & 1;
+            mbar_wait(&ctl->kv_full[s], (j >> 1) & 1);
+            tc_fence_after();
+            if (elect_one()) {
+                const uint32_t d_tmem = tmem + (j & 1) * 128;
+#pragma unroll
+                for (int kb = 0; kb < KB; ++kb) {
+                    const uint64_t da = umma_desc_k_sw128(smem_u32(sQ + kb * (kFaBM * 128)));
+                    const uint64_t db = umma_desc_k_sw128(smem_u32(sK + s * kKBytes + kb * (BN * 128)));
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) umma_bf16(d_tmem, da + 2 * k, db + 2 * k, idesc_s, (kb | k) ? 1u : 0u);
+                }
+                umma_commit(&ctl->s_full[j & 1]);
+            }
+            __syncwarp();
+        };
+        mbar_wait(&ctl->q_full, 0);
+        issue_qk(0);
+        for (int j = 0; j < n_blocks; ++j) {
+            if (j + 1 < n_blocks) issue_qk(j + 1);          // S of the next block while softmax works on this one
+            mbar_wait(&ctl->p_full, j & 1);
+            tc_fence_after();
+            if (elect_one()) {
+                const int s = j & 1;
+                const uint32_t v_base = smem_u32(sV + s * kKBytes);
+#pragma unroll
+                for (int t = 0; t < BN / 16; ++t) {
+                    // A: P[128, BN] K-major, 16 keys = 32 bytes inside the 64-key block t / 4
+                    const uint64_t da = umma_desc_k_sw128(smem_u32(sP + (t >> 2) * (kFaBM * 128))) + 2 * (t & 3);
+                    // B: V[keys, D] MN-major, 16 keys = two 8-row groups = 2048 bytes; D atoms BN * 128 bytes apart
+                    const uint64_t db = umma_desc_mn_sw128(v_base + t * 2048, BN * 128);
+                    umma_bf16(tmem + kOCol, da, db, idesc_o, (j | t) ? 1u : 0u);
+                }
+                umma_commit(&ctl->kv_empty[s]);
+                umma_commit(&ctl->pv_done);
+            }
+            __syncwarp();
+        }
+    } else {
+        // ===================== softmax / correction / epilogue (warps 2..5) =====================
+        const int quarter = warp & 3;
+        const int row = quarter * 32 + lane;               // query row inside the tile = TMEM lane
+        const int q = q0 + row;
+        const uint32_t lane_addr = static_cast<uint32_t>(quarter * 32) << 16;
+        const CounterRng rng(a.seed);
+        const uint32_t thr = static_cast<uint32_t>(fminf(a.drop_p, 0.999999f) * 4294967296.0f);
+        const bool drop = a.drop_p > 0.f;
+        const uint64_t row_base = (static_cast<uint64_t>(n * a.H + h) * a.S + (q < a.S ? q : 0)) * static_cast<uint64_t>(a.S);
+        float m_run = -INFINITY, l_run = 0.f;
+        for (int j = 0; j < n_blocks; ++j) {
+            mbar_wait(&ctl->s_full[j & 1], (j >> 1) & 1);
+            tc_fence_after();
+            const uint32_t s_addr = tmem + lane_addr + (j & 1) * 128;
+            // pass 1: row maximum of this block
+            float m_blk = -INFINITY;
+#pragma unroll
+            for (int c = 0; c < BN; c += 16) {
+                uint32_t r[16];
+                tmem_ld_32x16(s_addr + c, r);
+                tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    const int key = j * BN + c + i;
+                    const bool ok = key < a.S && (!a.causal || key <= q);
+                    const float v = ok ? __uint_as_float(r[i]) * a.scale_log2 : -INFINITY;
+                    m_blk = fmaxf(m_blk, v);
+                }
+            }
+            const float m_new = fmaxf(m_run, m_blk);
+            const float m_use = m_new == -INFINITY ? 0.f : m_new;
+            const float alpha = exp2f(m_run - m_use);          // 0 on the first block (m_run = -inf)
+            // the previous block's P V must be complete before P is overwritten and O rescaled
+            if (j > 0) {
+                mbar_wait(&ctl->pv_done, (j - 1) & 1);
+                tc_fence_after();
+                if (__any_sync(0xffffffffu, m_new != m_run)) {
+                    const uint32_t o_addr = tmem + lane_addr + kOCol;
+#pragma unroll
+                    for (int c = 0; c < D; c += 16) {
+                        uint32_t r[16];
+                        tmem_ld_32x16(o_addr + c, r);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
+                        tmem_st_32x16(o_addr + c, r);
+                    }
+                    tmem_st_wait();
+                }
+            }
+            // pass 2: probabilities -> bf16 P tile (dropout applied), row sum before dropout
+            float l_blk = 0.f;
+#pragma unroll
+            for (int c = 0; c < BN; c += 16) {
+                uint32_t r[16];
+                tmem_ld_32x16(s_addr + c, r);
+                tmem_ld_wait();
+                uint32_t packed[8];
+#pragma unroll
+                for (int i = 0; i < 16; i += 2) {
+                    float pv[2];
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        const int key = j * BN + c + i + e;
+                        const bool ok = key < a.S && (!a.causal || key <= q);
+                        float p = ok ? exp2f(__uint_as_float(r[i + e]) * a.scale_log2 - m_use) : 0.f;
+                        l_blk += p;
+                        if (drop && ok && !dropout_keep(rng, a.stream, row_base + key, thr)) p = 0.f;
+                        pv[e] = p;
+                    }
+                    __nv_bfloat162 h2 = __floats2bfloat162_rn(pv[0], pv[1]);
+                    packed[i >> 1] = *reinterpret_cast<uint32_t*>(&h2);
+                }
+                // 16 keys = two 16-byte chunks of this row in the 64-key block c / 64
+                uint8_t* tile = sP + (c >> 6) * (kFaBM * 128);
+                const uint32_t col = c & 63;
+                *reinterpret_cast<uint4*>(tile + sw128_offset(row, col)) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+                *reinterpret_cast<uint4*>(tile + sw128_offset(row, col + 8)) = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+            }
+            l_run = l_run * alpha + l_blk;
+            m_run = m_new;
+            fence_proxy_async();            // P was written by the generic proxy, the tensor core reads it through the async proxy
+            tc_fence_before();
+            mbar_arrive(&ctl->p_full);
+        }
+        // epilogue: O / l (and the dropout rescale), bf16, straight to [T, E]
+        mbar_wait(&ctl->pv_done, (n_blocks - 1) & 1);
+        tc_fence_after();
+        const float inv = (l_run > 0.f ? 1.f / l_run : 0.f) * (drop ? 1.f / (1.f - a.drop_p) : 1.f);
+        const uint32_t o_addr = tmem + lane_addr + kOCol;
+        __nv_bfloat16* dst = a.out + (static_cast<size_t>(q) * a.NB + n) * a.ld_out + h * D;
+#pragma unroll
+        for (int c = 0; c < D; c += 16) {
+            uint32_t r[16];
+            tmem_ld_32x16(o_addr + c, r);
+            tmem_ld_wait();
+            if (q < a.S) {
+                uint4 pk[2];
+                __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(pk);
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+                    h2[i] = __floats2bfloat162_rn(__uint_as_float(r[2 * i]) * inv, __uint_as_float(r[2 * i + 1]) * inv);
+                reinterpret_cast<uint4*>(dst + c)[0] = pk[0];
+                reinterpret_cast<uint4*>(dst + c)[1] = pk[1];
+            }
+        }
+        if (q < a.S && a.lse)
+            a.lse[static_cast<size_t>(n * a.H + h) * a.S + q] = (m_run == -INFINITY ? 0.f : m_run) * 0.6931471805599453f + logf(l_run);
+        tc_fence_before();
+    }
+
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem, kTmemCols);
+    }
+}
+
+}  // namespace pb2
+
+using namespace pb2;
+
+namespace {
+
+// [T, cols] bf16 with row = s * NB + n, seen as (column, n, s); box = 64 columns x 1 x box_s rows, 128-byte swizzle
+int make_tmap_seq3d(CUtensorMap* out, const void* ptr, int cols, int NB, int S, int box_s) {
+    struct Key { const void* p; int cols, NB, S, box; };
+    struct Slot { Key k; CUtensorMap m; bool valid; };
+    thread_local Slot cache[64];
+    const size_t slot_i = (reinterpret_cast<uintptr_t>(ptr) >> 8 ^ static_cast<size_t>(S) * 131 ^ static_cast<size_t>(box_s)) % 64;
+    Slot& sl = cache[slot_i];
+    if (sl.valid && sl.k.p == ptr && sl.k.cols == cols && sl.k.NB == NB && sl.k.S == S && sl.k.box == box_s) {
+        *out = sl.m;
+        return 0;
+    }
+    EncodeTiledFn enc = get_encode_tiled();
+    if (!enc) return -1;
+    cuuint64_t dims[3] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(NB), static_cast<cuuint64_t>(S)};
+    cuuint64_t strides[2] = {static_cast<cuuint64_t>(cols) * 2, static_cast<cuuint64_t>(cols) * NB * 2};
+    cuuint32_t box[3] = {64, 1, static_cast<cuuint32_t>(box_s)};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled (3-D) failed (%d) for cols %d NB %d S %d box %d", static_cast<int>(r), cols, NB, S, box_s);
+        return -1;
+    }
+    sl.k = Key{ptr, cols, NB, S, box_s};
+    sl.m = *out;
+    sl.valid = true;
+    return 0;
+}
+
+template <int D, int BN>
+int launch_fwd(const void* qkv, const FaArgs& a, cudaStream_t stream) {
+    CUtensorMap tq, tkv;
+    if (make_tmap_seq3d(&tq, qkv, 3 * a.H * D, a.NB, a.S, kFaBM)) return -1;
+    if (make_tmap_seq3d(&tkv, qkv, 3 * a.H * D, a.NB, a.S, BN)) return -1;
+    const size_t smem = static_cast<size_t>(kFaBM) * D * 2 + 4 * static_cast<size_t>(BN) * D * 2 + static_cast<size_t>(kFaBM) * BN * 2 +
+                        sizeof(FaCtl) + 1024;
+    if (ensure_max_smem(reinterpret_cast<const void*>(flash_fwd_kernel<D, BN>), 227 * 1024)) return -1;
+    dim3 grid((a.S + kFaBM - 1) / kFaBM, a.H, a.NB);
+    PB2_CUDA(launch_pdl(flash_fwd_kernel<D, BN>, grid, dim3(kFaThreads), smem, stream, tq, tkv, a));
+    PB2_LAUNCHED("flash_fwd_kernel");
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int pb2_flash_attention_fwd(const void* qkv, void* out, float* lse, int NB, int S, int H, int D, int causal,
+                                       float drop_p, unsigned long long seed, unsigned long long rng_stream,
+                                       cudaStream_t stream) {
+    if (NB <= 0 || S <= 0 || H <= 0) { set_error("pb2_flash_attention_fwd: empty problem"); return -1; }
+    if (D != 64 && D != 128 && D != 256) { set_error("pb2_flash_attention_fwd: head_dim %d not in {64, 128, 256}", D); return -1; }
+    if (reinterpret_cast<uintptr_t>(qkv) & 15) { set_error("pb2_flash_attention_fwd: qkv must be 16-byte aligned"); return -1; }
+    FaArgs a;
+    memset(&a, 0, sizeof(a));
+    a.NB = NB; a.S = S; a.H = H; a.D = D; a.causal = causal;
+    a.scale_log2 = 1.4426950408889634f / sqrtf(static_cast<float>(D));
+    a.drop_p = drop_p; a.seed = seed; a.stream = rng_stream;
+    a.out = static_cast<__nv_bfloat16*>(out); a.lse = lse; a.ld_out = static_cast<long long>(H) * D;
+    if (D == 64) return launch_fwd<64, 128>(qkv, a, stream);
+    if (D == 128) return launch_fwd<128, 128>(qkv, a, stream);
+    return launch_fwd<256, 64>(qkv, a, stream);
+}

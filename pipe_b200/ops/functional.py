@@ -204,3 +204,20 @@ def attention_bwd(qkv: Tensor, dout: Tensor, NB: int, S: int, H: int, *, causal:
                                            c_ull(rng_stream), _s(qkv))
     _lib.check(rc, "pb2_attention_bwd")
     return dqkv
+
+
+def flash_attention_fwd(qkv: Tensor, NB: int, S: int, H: int, *, causal: bool, drop_p: float, seed: int,
+                        rng_stream: int, want_lse: bool = True) -> Tuple[Tensor, Optional[Tensor]]:
+    """Blocked (flash) attention on the tcgen05 kernels: any ``S``, head_dim in {64, 128, 256}.  Returns
+    ``(out [T, E] bf16, lse [NB * H, S] fp32 or None)``."""
+    T, E3 = qkv.shape
+    E = E3 // 3
+    assert qkv.dtype == torch.bfloat16 and qkv.is_contiguous() and T == NB * S and E % H == 0
+    out = torch.empty((T, E), dtype=torch.bfloat16, device=qkv.device)
+    lse = torch.empty((NB * H, S), dtype=torch.float32, device=qkv.device) if want_lse else None
+    with _lib.on_device(qkv.device):
+        rc = _lib.load().pb2_flash_attention_fwd(c_p(qkv.data_ptr()), c_p(out.data_ptr()), c_p(ptr(lse)), c_i(NB), c_i(S),
+                                                 c_i(H), c_i(E // H), c_i(int(causal)), c_f(drop_p), c_ull(seed),
+                                                 c_ull(rng_stream), _s(qkv))
+    _lib.check(rc, "pb2_flash_attention_fwd")
+    return out, lse

@@ -1,0 +1,64 @@
+"""Flash attention (tcgen05 / TMEM / TMA, ``csrc/attention_flash.cu``) against fp32 scaled-dot-product attention
+on the packed QKV layout of the encoder layer.  Reference call site: ``nn.MultiheadAttention`` inside
+``nn.TransformerEncoderLayer`` (``main.py:148``), sequence lengths up to ``max_len = 5000`` (``main.py:59``)."""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+dev = "cuda"
+
+
+def rel(got, want):
+    got, want = got.float(), want.float()
+    return ((got - want).norm() / (want.norm() + 1e-12)).item()
+
+
+def _reference(qkv, NB, S, H, causal):
+    T, E3 = qkv.shape
+    E = E3 // 3
+    D = E // H
+    x = qkv.float().view(S, NB, 3, H, D)
+    q, k, v = (x[:, :, i].permute(1, 2, 0, 3) for i in range(3))          # [NB, H, S, D]
+    out = F.scaled_dot_product_attention(q, k, v, is_causal=causal)
+    scores = (q @ k.transpose(-1, -2)) / math.sqrt(D)
+    if causal:
+        scores = scores.masked_fill(torch.ones(S, S, device=qkv.device).triu(1).bool(), float("-inf"))
+    lse = torch.logsumexp(scores, dim=-1)                                   # [NB, H, S]
+    return out.permute(2, 0, 1, 3).reshape(T, E), lse.reshape(NB * H, S)
+
+
+@pytest.mark.parametrize("S,NB,H,D", [(128, 2, 4, 64), (200, 3, 2, 64), (512, 2, 2, 128), (2048, 1, 2, 64),
+                                      (384, 1, 2, 256), (77, 2, 2, 128), (1000, 1, 1, 256)])
+@pytest.mark.parametrize("causal", [False, True])
+def test_flash_forward_matches_sdpa(S, NB, H, D, causal):
+    from pipe_b200.ops import functional as F2
+    torch.manual_seed(S + D)
+    qkv = (torch.randn(S * NB, 3 * H * D, device=dev) * 0.7).bfloat16()
+    out, lse = F2.flash_attention_fwd(qkv, NB, S, H, causal=causal, drop_p=0.0, seed=0, rng_stream=0)
+    torch.cuda.synchronize()
+    want, want_lse = _reference(qkv, NB, S, H, causal)
+    assert rel(out, want) < 1.5e-2, rel(out, want)
+    assert torch.allclose(lse, want_lse, atol=2e-2, rtol=1e-3), (lse - want_lse).abs().max().item()
+
+
+def test_flash_forward_dropout_keeps_expectation_and_is_reproducible():
+    from pipe_b200.ops import functional as F2
+    S, NB, H, D = 256, 2, 2, 64
+    torch.manual_seed(0)
+    qkv = (torch.randn(S * NB, 3 * H * D, device=dev) * 0.5).bfloat16()
+    a, _ = F2.flash_attention_fwd(qkv, NB, S, H, causal=False, drop_p=0.25, seed=11, rng_stream=3)
+    b, _ = F2.flash_attention_fwd(qkv, NB, S, H, causal=False, drop_p=0.25, seed=11, rng_stream=3)
+    c, _ = F2.flash_attention_fwd(qkv, NB, S, H, causal=False, drop_p=0.25, seed=12, rng_stream=3)
+    clean, _ = F2.flash_attention_fwd(qkv, NB, S, H, causal=False, drop_p=0.0, seed=0, rng_stream=0)
+    torch.cuda.synchronize()
+    assert torch.equal(a, b) and not torch.equal(a, c)
+    # dropout on the probabilities is unbiased: averaged over many seeds the output approaches the clean one
+    acc = torch.zeros_like(clean, dtype=torch.float32)
+    n = 24
+    for s in range(n):
+        o, _ = F2.flash_attention_fwd(qkv, NB, S, H, causal=False, drop_p=0.25, seed=100 + s, rng_stream=3)
+        acc += o.float()
+    assert rel(acc / n, clean) < 0.12
