@@ -196,6 +196,18 @@ int pb2_flash_attention_fwd(const void* qkv, void* out, float* lse, int NB, int 
                             float drop_p, unsigned long long seed, unsigned long long rng_stream,
                             cudaStream_t stream);
 
+/* Backward of pb2_flash_attention_fwd (head_dim 64 or 128): recomputes the probabilities block by block from
+ * `lse`, keeps dK / dV of a key block in TMEM while it walks the query blocks, adds dQ into an fp32 accumulator.
+ * `out` is the forward's output, `dout` its gradient ([T, E] bf16), `dqkv` receives the packed gradient [T, 3E].
+ * `scratch` (pb2_flash_attention_bwd_scratch_bytes() bytes, 16-byte aligned, contents irrelevant) holds
+ * delta = rowsum(dO o O) and the dQ accumulator; three small launches around the main kernel (memset, delta,
+ * dQ cast) run on the same stream. */
+size_t pb2_flash_attention_bwd_scratch_bytes(int NB, int S, int H, int D);
+int pb2_flash_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv,
+                            void* scratch, size_t scratch_bytes, int NB, int S, int H, int D, int causal,
+                            float drop_p, unsigned long long seed, unsigned long long rng_stream,
+                            cudaStream_t stream);
+
 /* ---- multi-tensor fused clip + Adam ---------------------------------------------------------
  * `table_dev` is a device array of n_tensors descriptors sorted by tile_start; a tensor of
  * [rows, cols] owns ceil(rows/32) * ceil(cols/64) consecutive tiles.  w/g/m/v are fp32; w16

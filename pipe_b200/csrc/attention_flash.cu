@@ -330,6 +330,318 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_cons
     }
 }
 
+
+// =====================================================================================================
+// Backward.  One CTA per (128 keys, head, sequence) walks the query blocks that attend to them:
+//   S  = Q K^T, dP = dO V^T                       (two MMAs into TMEM, both operands K-major)
+//   P  = exp(S * scale - LSE), dropout, dS = P o (dP - delta) * scale       (softmax warps, one row each,
+//                                                   P and dS to shared memory as bf16)
+//   dV += P^T dO, dK += dS^T Q                    (A and B both MN-major: the tiles are used as they were
+//                                                   loaded / written, nothing is transposed)
+//   dQ  = dS K                                     (A K-major, B MN-major) -> fp32 atomics into a dQ accumulator
+// dK and dV stay in TMEM for the whole walk and are written once.  delta = rowsum(dO o O) comes from a small
+// kernel in front, the bf16 dQ from one behind (the accumulator is fp32 because several key blocks add to it).
+// TMEM: S | dP | dK | dV = 256 + 2 D columns, dQ reuses the S columns once S has been read: D <= 128.
+// =====================================================================================================
+struct FaBwdArgs {
+    int NB, S, H, D;
+    int causal;
+    float scale, scale_log2;
+    float drop_p;
+    unsigned long long seed, stream;
+    const float* lse;        // [NB * H, S]
+    const float* delta;      // [NB * H, S]
+    float* dq_acc;           // [T, E] fp32, zeroed
+    __nv_bfloat16* dqkv;     // [T, 3E]
+    long long ld_dqkv;       // 3E
+};
+
+struct __align__(8) FaBwdCtl {
+    uint64_t kv_full;
+    uint64_t q_full[2];
+    uint64_t q_empty[2];
+    uint64_t sdp_full;
+    uint64_t pds_full;
+    uint64_t dq_full;
+    uint64_t dq_free;
+    uint32_t tmem_base;
+    uint32_t pad;
+};
+
+template <int D, int STAGES>
+__global__ void __launch_bounds__(kFaThreads, 1)
+flash_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_constant__ CUtensorMap tmap_do, const FaBwdArgs a) {
+    constexpr int KB = D / 64;
+    constexpr int BN = 128;                              // keys per CTA
+    constexpr uint32_t kTile = 128 * D * 2;              // one [128, D] bf16 tile
+    constexpr uint32_t kPTile = 128 * 128 * 2;
+    constexpr uint32_t kDkCol = 256, kDvCol = 256 + D;
+    static_assert(256 + 2 * D <= 512, "TMEM budget");
+
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sK = smem;
+    uint8_t* sV = sK + kTile;
+    uint8_t* sQ = sV + kTile;                            // [STAGES]
+    uint8_t* sdO = sQ + STAGES * kTile;                  // [STAGES]
+    uint8_t* sP = sdO + STAGES * kTile;                  // [2 key blocks][128 q rows][128 B]
+    uint8_t* sdS = sP + kPTile;
+    FaBwdCtl* ctl = reinterpret_cast<FaBwdCtl*>(sdS + kPTile);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int k0 = blockIdx.x * BN;
+    const int h = blockIdx.y, n = blockIdx.z;
+    const int E = a.H * D;
+    const int q_blocks = (a.S + kFaBM - 1) / kFaBM;
+    const int first = a.causal ? k0 / kFaBM : 0;         // query blocks before the key block see none of its keys
+    const int n_it = q_blocks - first;
+
+    pdl_launch_dependents();
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmap_qkv);
+        tma_prefetch_desc(&tmap_do);
+        mbar_init(&ctl->kv_full, 1);
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&ctl->q_full[s], 1);
+            mbar_init(&ctl->q_empty[s], 1);
+        }
+        mbar_init(&ctl->sdp_full, 1);
+        mbar_init(&ctl->pds_full, 128);
+        mbar_init(&ctl->dq_full, 1);
+        mbar_init(&ctl->dq_free, 128);
+        fence_mbar_init();
+    }
+    if (warp == 1) {
+        tmem_alloc(&ctl->tmem_base, 512);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = ctl->tmem_base;
+
+    if (warp == 0) {
+        if (elect_one()) {
+            pdl_wait();
+            mbar_expect_tx(&ctl->kv_full, 2 * kTile);
+            for (int kb = 0; kb < KB; ++kb) {
+                tma_load_3d(sK + kb * (BN * 128), &tmap_qkv, &ctl->kv_full, E + h * D + kb * 64, n, k0);
+                tma_load_3d(sV + kb * (BN * 128), &tmap_qkv, &ctl->kv_full, 2 * E + h * D + kb * 64, n, k0);
+            }
+            for (int it = 0; it < n_it; ++it) {
+                const int s = it % STAGES;
+                const int q0 = (first + it) * kFaBM;
+                mbar_wait(&ctl->q_empty[s], ((it / STAGES) & 1) ^ 1);
+                mbar_expect_tx(&ctl->q_full[s], 2 * kTile);
+                for (int kb = 0; kb < KB; ++kb) {
+                    tma_load_3d(sQ + s * kTile + kb * (kFaBM * 128), &tmap_qkv, &ctl->q_full[s], h * D + kb * 64, n, q0);
+                    tma_load_3d(sdO + s * kTile + kb * (kFaBM * 128), &tmap_do, &ctl->q_full[s], h * D + kb * 64, n, q0);
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        const uint32_t idesc_s = umma_idesc_bf16_major(128, 128, 0, 0);      // S, dP: K-major x K-major
+        const uint32_t idesc_kv = umma_idesc_bf16_major(128, D, 1, 1);       // dV, dK: MN-major x MN-major
+        const uint32_t idesc_q = umma_idesc_bf16_major(128, D, 0, 1);        // dQ: K-major x MN-major
+        mbar_wait(&ctl->kv_full, 0);
+        for (int it = 0; it < n_it; ++it) {
+            const int s = it % STAGES;
+            mbar_wait(&ctl->q_full[s], (it / STAGES) & 1);
+            if (it > 0) mbar_wait(&ctl->dq_free, (it - 1) & 1);       // dQ of the previous block was read out of the S columns
+            tc_fence_after();
+            const uint32_t q_base = smem_u32(sQ + s * kTile), do_base = smem_u32(sdO + s * kTile);
+            if (elect_one()) {
+#pragma unroll
+                for (int kb = 0; kb < KB; ++kb) {
+                    const uint64_t dq_ = umma_desc_k_sw128(q_base + kb * (kFaBM * 128));
+                    const uint64_t dk_ = umma_desc_k_sw128(smem_u32(sK + kb * (BN * 128)));
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) umma_bf16(tmem, dq_ + 2 * k, dk_ + 2 * k, idesc_s, (kb | k) ? 1u : 0u);
+                }
+#pragma unroll
+                for (int kb = 0; kb < KB; ++kb) {
+                    const uint64_t ddo = umma_desc_k_sw128(do_base + kb * (kFaBM * 128));
+                    const uint64_t dv_ = umma_desc_k_sw128(smem_u32(sV + kb * (BN * 128)));
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) umma_bf16(tmem + 128, ddo + 2 * k, dv_ + 2 * k, idesc_s, (kb | k) ? 1u : 0u);
+                }
+                umma_commit(&ctl->sdp_full);
+            }
+            __syncwarp();
+            mbar_wait(&ctl->pds_full, it & 1);
+            tc_fence_after();
+            if (elect_one()) {
+                const uint32_t p_base = smem_u32(sP), ds_base = smem_u32(sdS);
+#pragma unroll
+                for (int t = 0; t < 8; ++t) {            // 16 query rows per MMA: K = q
+                    // A = P^T / dS^T: [q rows][keys] tiles read MN-major (keys contiguous), key atoms 16 KB apart
+                    const uint64_t ap = umma_desc_mn_sw128(p_base + t * 2048, kFaBM * 128);
+                    const uint64_t ads = umma_desc_mn_sw128(ds_base + t * 2048, kFaBM * 128);
+                    // B = dO / Q: [q rows][D] tiles read MN-major (d contiguous), d atoms 16 KB apart
+                    const uint64_t bdo = umma_desc_mn_sw128(do_base + t * 2048, kFaBM * 128);
+                    const uint64_t bq = umma_desc_mn_sw128(q_base + t * 2048, kFaBM * 128);
+                    umma_bf16(tmem + kDvCol, ap, bdo, idesc_kv, (it | t) ? 1u : 0u);
+                    umma_bf16(tmem + kDkCol, ads, bq, idesc_kv, (it | t) ? 1u : 0u);
+                }
+#pragma unroll
+                for (int t = 0; t < 8; ++t) {            // 16 keys per MMA: K = keys
+                    const uint64_t ads = umma_desc_k_sw128(ds_base + (t >> 2) * (kFaBM * 128)) + 2 * (t & 3);
+                    const uint64_t bk = umma_desc_mn_sw128(smem_u32(sK) + t * 2048, BN * 128);
+                    umma_bf16(tmem, ads, bk, idesc_q, t ? 1u : 0u);
+                }
+                umma_commit(&ctl->q_empty[s]);
+                umma_commit(&ctl->dq_full);
+            }
+            __syncwarp();
+        }
+    } else {
+        const int quarter = warp & 3;
+        const int row = quarter * 32 + lane;
+        const uint32_t lane_addr = static_cast<uint32_t>(quarter * 32) << 16;
+        const CounterRng rng(a.seed);
+        const uint32_t thr = static_cast<uint32_t>(fminf(a.drop_p, 0.999999f) * 4294967296.0f);
+        const bool drop = a.drop_p > 0.f;
+        const float inv_keep = drop ? 1.f / (1.f - a.drop_p) : 1.f;
+        for (int it = 0; it < n_it; ++it) {
+            const int q = (first + it) * kFaBM + row;
+            const bool q_ok = q < a.S;
+            const size_t stat = static_cast<size_t>(n * a.H + h) * a.S + (q_ok ? q : 0);
+            const float lse2 = q_ok ? a.lse[stat] * 1.4426950408889634f : 0.f;
+            const float delta = q_ok ? a.delta[stat] : 0.f;
+            const uint64_t row_base = (static_cast<uint64_t>(n * a.H + h) * a.S + (q_ok ? q : 0)) * static_cast<uint64_t>(a.S);
+            mbar_wait(&ctl->sdp_full, it & 1);
+            tc_fence_after();
+            if (it > 0) {
+                // P / dS of the previous block are still operands of its dV / dK / dQ MMAs until dq_full
+                // (waited below in the previous iteration), so they may be overwritten now
+            }
+#pragma unroll
+            for (int c = 0; c < BN; c += 16) {
+                uint32_t rs[16], rp[16];
+                tmem_ld_32x16(tmem + lane_addr + c, rs);
+                tmem_ld_32x16(tmem + lane_addr + 128 + c, rp);
+                tmem_ld_wait();
+                uint32_t pk_p[8], pk_ds[8];
+#pragma unroll
+                for (int i = 0; i < 16; i += 2) {
+                    float pp[2], dd[2];
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        const int key = k0 + c + i + e;
+                        const bool ok = q_ok && key < a.S && (!a.causal || key <= q);
+                        const float p = ok ? exp2f(__uint_as_float(rs[i + e]) * a.scale_log2 - lse2) : 0.f;
+                        float keep = 1.f;
+                        if (drop && ok && !dropout_keep(rng, a.stream, row_base + key, thr)) keep = 0.f;
+                        const float dp = __uint_as_float(rp[i + e]) * keep * inv_keep;      // back through the dropout
+                        pp[e] = p * keep * inv_keep;                                          // what multiplied V
+                        dd[e] = p * (dp - delta) * a.scale;
+                    }
+                    __nv_bfloat162 hp = __floats2bfloat162_rn(pp[0], pp[1]);
+                    __nv_bfloat162 hd = __floats2bfloat162_rn(dd[0], dd[1]);
+                    pk_p[i >> 1] = *reinterpret_cast<uint32_t*>(&hp);
+                    pk_ds[i >> 1] = *reinterpret_cast<uint32_t*>(&hd);
+                }
+                const uint32_t tile_off = (c >> 6) * (kFaBM * 128);
+                const uint32_t col = c & 63;
+                *reinterpret_cast<uint4*>(sP + tile_off + sw128_offset(row, col)) = make_uint4(pk_p[0], pk_p[1], pk_p[2], pk_p[3]);
+                *reinterpret_cast<uint4*>(sP + tile_off + sw128_offset(row, col + 8)) = make_uint4(pk_p[4], pk_p[5], pk_p[6], pk_p[7]);
+                *reinterpret_cast<uint4*>(sdS + tile_off + sw128_offset(row, col)) = make_uint4(pk_ds[0], pk_ds[1], pk_ds[2], pk_ds[3]);
+                *reinterpret_cast<uint4*>(sdS + tile_off + sw128_offset(row, col + 8)) = make_uint4(pk_ds[4], pk_ds[5], pk_ds[6], pk_ds[7]);
+            }
+            fence_proxy_async();
+            tc_fence_before();
+            mbar_arrive(&ctl->pds_full);
+            // dQ of this query block: out of TMEM, into the fp32 accumulator other key blocks add to as well
+            mbar_wait(&ctl->dq_full, it & 1);
+            tc_fence_after();
+            float* dq = a.dq_acc + (static_cast<size_t>(q_ok ? q : 0) * a.NB + n) * E + h * D;
+#pragma unroll
+            for (int c = 0; c < D; c += 16) {
+                uint32_t r[16];
+                tmem_ld_32x16(tmem + lane_addr + c, r);
+                tmem_ld_wait();
+                if (q_ok) {
+#pragma unroll
+                    for (int i = 0; i < 16; i += 4)
+                        red_add_f32x4(dq + c + i, __uint_as_float(r[i]), __uint_as_float(r[i + 1]), __uint_as_float(r[i + 2]),
+                                      __uint_as_float(r[i + 3]));
+                }
+            }
+            tc_fence_before();
+            mbar_arrive(&ctl->dq_free);
+        }
+        // dK, dV of this key block: one writer, straight into the packed gradient
+        const int key = k0 + row;
+        if (n_it > 0) {
+            __nv_bfloat16* dk = a.dqkv + (static_cast<size_t>(key < a.S ? key : 0) * a.NB + n) * a.ld_dqkv + E + h * D;
+            __nv_bfloat16* dv = dk + E;
+#pragma unroll
+            for (int c = 0; c < D; c += 16) {
+                uint32_t rk[16], rv[16];
+                tmem_ld_32x16(tmem + lane_addr + kDkCol + c, rk);
+                tmem_ld_32x16(tmem + lane_addr + kDvCol + c, rv);
+                tmem_ld_wait();
+                if (key < a.S) {
+                    uint4 pk[2], pv[2];
+                    __nv_bfloat162* hk = reinterpret_cast<__nv_bfloat162*>(pk);
+                    __nv_bfloat162* hv = reinterpret_cast<__nv_bfloat162*>(pv);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        hk[i] = __floats2bfloat162_rn(__uint_as_float(rk[2 * i]), __uint_as_float(rk[2 * i + 1]));
+                        hv[i] = __floats2bfloat162_rn(__uint_as_float(rv[2 * i]), __uint_as_float(rv[2 * i + 1]));
+                    }
+                    reinterpret_cast<uint4*>(dk + c)[0] = pk[0];
+                    reinterpret_cast<uint4*>(dk + c)[1] = pk[1];
+                    reinterpret_cast<uint4*>(dv + c)[0] = pv[0];
+                    reinterpret_cast<uint4*>(dv + c)[1] = pv[1];
+                }
+            }
+        }
+        tc_fence_before();
+    }
+
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem, 512);
+    }
+}
+
+// delta[(n, h), s] = sum_d dO[s, n, h, d] * O[s, n, h, d]: one warp per (token, head)
+__global__ void flash_delta_kernel(const __nv_bfloat16* __restrict__ out, const __nv_bfloat16* __restrict__ dout,
+                                   float* __restrict__ delta, int NB, int S, int H, int D) {
+    pdl_launch_dependents();
+    pdl_wait();
+    const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    const int total = NB * S * H;
+    if (w >= total) return;
+    const int h = w % H, tok = w / H;                      // tok = s * NB + n
+    const int s = tok / NB, n = tok % NB;
+    const size_t base = static_cast<size_t>(tok) * H * D + static_cast<size_t>(h) * D;
+    float acc = 0.f;
+    for (int d = lane * 2; d < D; d += 64) {
+        const __nv_bfloat162 o = *reinterpret_cast<const __nv_bfloat162*>(out + base + d);
+        const __nv_bfloat162 g = *reinterpret_cast<const __nv_bfloat162*>(dout + base + d);
+        acc += __bfloat162float(o.x) * __bfloat162float(g.x) + __bfloat162float(o.y) * __bfloat162float(g.y);
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) delta[static_cast<size_t>(n * H + h) * S + s] = acc;
+}
+
+// dqkv[:, 0:E] = bf16(dq_acc)
+__global__ void flash_dq_cast_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ dqkv, size_t T, int E) {
+    pdl_launch_dependents();
+    pdl_wait();
+    const size_t i4 = (static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x) * 4;
+    if (i4 >= T * E) return;
+    const size_t t = i4 / E, c = i4 % E;
+    const float4 v = *reinterpret_cast<const float4*>(acc + i4);
+    __nv_bfloat162* o = reinterpret_cast<__nv_bfloat162*>(dqkv + t * 3 * E + c);
+    o[0] = __floats2bfloat162_rn(v.x, v.y);
+    o[1] = __floats2bfloat162_rn(v.z, v.w);
+}
+
 }  // namespace pb2
 
 using namespace pb2;
@@ -397,4 +709,71 @@ extern "C" int pb2_flash_attention_fwd(const void* qkv, void* out, float* lse, i
     if (D == 64) return launch_fwd<64, 128>(qkv, a, stream);
     if (D == 128) return launch_fwd<128, 128>(qkv, a, stream);
     return launch_fwd<256, 64>(qkv, a, stream);
+}
+
+namespace {
+
+template <int D, int STAGES>
+int launch_bwd(const void* qkv, const void* dout, const FaBwdArgs& a, cudaStream_t stream) {
+    CUtensorMap tq, tdo;
+    if (make_tmap_seq3d(&tq, qkv, 3 * a.H * D, a.NB, a.S, 128)) return -1;
+    if (make_tmap_seq3d(&tdo, dout, a.H * D, a.NB, a.S, 128)) return -1;
+    const size_t tile = static_cast<size_t>(128) * D * 2;
+    const size_t smem = 2 * tile + 2 * STAGES * tile + 2 * (128 * 128 * 2) + sizeof(FaBwdCtl) + 1024;
+    if (ensure_max_smem(reinterpret_cast<const void*>(flash_bwd_kernel<D, STAGES>), 227 * 1024)) return -1;
+    dim3 grid((a.S + 127) / 128, a.H, a.NB);
+    PB2_CUDA(launch_pdl(flash_bwd_kernel<D, STAGES>, grid, dim3(kFaThreads), smem, stream, tq, tdo, a));
+    PB2_LAUNCHED("flash_bwd_kernel");
+    return 0;
+}
+
+}  // namespace
+
+extern "C" size_t pb2_flash_attention_bwd_scratch_bytes(int NB, int S, int H, int D) {
+    const size_t T = static_cast<size_t>(NB) * S, E = static_cast<size_t>(H) * D;
+    return ((static_cast<size_t>(NB) * H * S * 4 + 255) / 256) * 256 + T * E * 4;
+}
+
+extern "C" int pb2_flash_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv,
+                                       void* scratch, size_t scratch_bytes, int NB, int S, int H, int D, int causal,
+                                       float drop_p, unsigned long long seed, unsigned long long rng_stream,
+                                       cudaStream_t stream) {
+    if (NB <= 0 || S <= 0 || H <= 0) { set_error("pb2_flash_attention_bwd: empty problem"); return -1; }
+    if (D != 64 && D != 128) { set_error("pb2_flash_attention_bwd: head_dim %d not in {64, 128}", D); return -1; }
+    const size_t need = pb2_flash_attention_bwd_scratch_bytes(NB, S, H, D);
+    if (!scratch || scratch_bytes < need) { set_error("pb2_flash_attention_bwd: scratch of %zu bytes needed, %zu given", need, scratch_bytes); return -1; }
+    if ((reinterpret_cast<uintptr_t>(qkv) | reinterpret_cast<uintptr_t>(dout) | reinterpret_cast<uintptr_t>(scratch)) & 15) {
+        set_error("pb2_flash_attention_bwd: qkv, dout and scratch must be 16-byte aligned");
+        return -1;
+    }
+    const size_t T = static_cast<size_t>(NB) * S;
+    const int E = H * D;
+    float* delta = static_cast<float*>(scratch);
+    float* dq_acc = reinterpret_cast<float*>(static_cast<char*>(scratch) + ((static_cast<size_t>(NB) * H * S * 4 + 255) / 256) * 256);
+    PB2_CUDA(cudaMemsetAsync(dq_acc, 0, T * E * 4, stream));
+    {
+        const int warps = NB * S * H;
+        const int blocks = (warps * 32 + 255) / 256;
+        PB2_CUDA(launch_pdl(flash_delta_kernel, dim3(blocks), dim3(256), 0, stream, static_cast<const __nv_bfloat16*>(out),
+                            static_cast<const __nv_bfloat16*>(dout), delta, NB, S, H, D));
+        PB2_LAUNCHED("flash_delta_kernel");
+    }
+    FaBwdArgs a;
+    memset(&a, 0, sizeof(a));
+    a.NB = NB; a.S = S; a.H = H; a.D = D; a.causal = causal;
+    a.scale = 1.f / sqrtf(static_cast<float>(D));
+    a.scale_log2 = a.scale * 1.4426950408889634f;
+    a.drop_p = drop_p; a.seed = seed; a.stream = rng_stream;
+    a.lse = lse; a.delta = delta; a.dq_acc = dq_acc;
+    a.dqkv = static_cast<__nv_bfloat16*>(dqkv); a.ld_dqkv = 3ll * E;
+    const int rc = D == 64 ? launch_bwd<64, 2>(qkv, dout, a, stream) : launch_bwd<128, 1>(qkv, dout, a, stream);
+    if (rc) return rc;
+    {
+        const size_t n4 = T * E / 4;
+        const unsigned blocks = static_cast<unsigned>((n4 + 255) / 256);
+        PB2_CUDA(launch_pdl(flash_dq_cast_kernel, dim3(blocks), dim3(256), 0, stream, static_cast<const float*>(dq_acc),
+                            static_cast<__nv_bfloat16*>(dqkv), T, E));
+        PB2_LAUNCHED("flash_dq_cast_kernel");
+    }
+    return 0;
 }

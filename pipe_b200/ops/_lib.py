@@ -94,6 +94,7 @@ def load() -> ctypes.CDLL:
         lib.pb2_launch_count.restype = ctypes.c_longlong
         lib.pb2_gemm_workspace_bytes.restype = ctypes.c_size_t
         lib.pb2_encoder_stack_act_elems.restype = ctypes.c_size_t
+        lib.pb2_flash_attention_bwd_scratch_bytes.restype = ctypes.c_size_t
         lib.pb2_encoder_stack_tmp_elems.restype = ctypes.c_size_t
         _lib = lib
     return _lib

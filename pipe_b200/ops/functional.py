@@ -221,3 +221,23 @@ def flash_attention_fwd(qkv: Tensor, NB: int, S: int, H: int, *, causal: bool, d
                                                  c_ull(rng_stream), _s(qkv))
     _lib.check(rc, "pb2_flash_attention_fwd")
     return out, lse
+
+
+def flash_attention_bwd(qkv: Tensor, out: Tensor, dout: Tensor, lse: Tensor, NB: int, S: int, H: int, *, causal: bool,
+                        drop_p: float, seed: int, rng_stream: int) -> Tensor:
+    """Gradient of :func:`flash_attention_fwd` with respect to the packed QKV (head_dim 64 or 128)."""
+    T, E3 = qkv.shape
+    E = E3 // 3
+    assert dout.dtype == torch.bfloat16 and dout.is_contiguous() and dout.shape == (T, E) and out.shape == (T, E)
+    assert lse.dtype == torch.float32 and lse.is_contiguous() and lse.numel() == NB * H * S
+    lib = _lib.load()
+    nbytes = int(lib.pb2_flash_attention_bwd_scratch_bytes(c_i(NB), c_i(S), c_i(H), c_i(E // H)))
+    scratch = torch.empty(nbytes, dtype=torch.uint8, device=qkv.device)
+    dqkv = torch.empty_like(qkv)
+    with _lib.on_device(qkv.device):
+        rc = lib.pb2_flash_attention_bwd(c_p(qkv.data_ptr()), c_p(out.data_ptr()), c_p(dout.data_ptr()), c_p(lse.data_ptr()),
+                                         c_p(dqkv.data_ptr()), c_p(scratch.data_ptr()), ctypes.c_size_t(nbytes), c_i(NB),
+                                         c_i(S), c_i(H), c_i(E // H), c_i(int(causal)), c_f(drop_p), c_ull(seed),
+                                         c_ull(rng_stream), _s(qkv))
+    _lib.check(rc, "pb2_flash_attention_bwd")
+    return dqkv

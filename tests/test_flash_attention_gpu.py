@@ -62,3 +62,47 @@ def test_flash_forward_dropout_keeps_expectation_and_is_reproducible():
         o, _ = F2.flash_attention_fwd(qkv, NB, S, H, causal=False, drop_p=0.25, seed=100 + s, rng_stream=3)
         acc += o.float()
     assert rel(acc / n, clean) < 0.12
+
+
+@pytest.mark.parametrize("S,NB,H,D", [(128, 2, 4, 64), (200, 3, 2, 64), (512, 2, 2, 128), (1024, 1, 2, 64), (77, 2, 2, 128)])
+@pytest.mark.parametrize("causal", [False, True])
+def test_flash_backward_matches_autograd(S, NB, H, D, causal):
+    from pipe_b200.ops import functional as F2
+    torch.manual_seed(S * 3 + D)
+    E = H * D
+    qkv = (torch.randn(S * NB, 3 * E, device=dev) * 0.7).bfloat16()
+    dout = (torch.randn(S * NB, E, device=dev) * 0.5).bfloat16()
+    out, lse = F2.flash_attention_fwd(qkv, NB, S, H, causal=causal, drop_p=0.0, seed=0, rng_stream=0)
+    dqkv = F2.flash_attention_bwd(qkv, out, dout, lse, NB, S, H, causal=causal, drop_p=0.0, seed=0, rng_stream=0)
+    torch.cuda.synchronize()
+    ref_in = qkv.float().requires_grad_()
+    x = ref_in.view(S, NB, 3, H, D)
+    q, k, v = (x[:, :, i].permute(1, 2, 0, 3) for i in range(3))
+    want = F.scaled_dot_product_attention(q, k, v, is_causal=causal).permute(2, 0, 1, 3).reshape(S * NB, E)
+    want.backward(dout.float())
+    g = ref_in.grad.view(S * NB, 3, E)
+    got = dqkv.float().view(S * NB, 3, E)
+    for i, name in enumerate("qkv"):
+        assert rel(got[:, i], g[:, i]) < 3e-2, (name, rel(got[:, i], g[:, i]))
+
+
+def test_flash_backward_dropout_is_consistent_with_forward():
+    """With V = identity-like probes the forward output exposes the dropped probabilities; the backward must
+    have used the same mask: finite-difference of the loss along a random direction matches <grad, direction>."""
+    from pipe_b200.ops import functional as F2
+    S, NB, H, D = 256, 1, 2, 64
+    E = H * D
+    torch.manual_seed(5)
+    qkv = (torch.randn(S * NB, 3 * E, device=dev) * 0.5).bfloat16()
+    dout = (torch.randn(S * NB, E, device=dev) * 0.5).bfloat16()
+    kw = dict(causal=True, drop_p=0.2, seed=77, rng_stream=1)
+    out, lse = F2.flash_attention_fwd(qkv, NB, S, H, **kw)
+    dqkv = F2.flash_attention_bwd(qkv, out, dout, lse, NB, S, H, **kw).float()
+    direction = torch.randn_like(dqkv)
+    direction[:, :2 * E] = 0                                  # move V only: the output is linear in V
+    eps = 0.25
+    plus, _ = F2.flash_attention_fwd((qkv.float() + eps * direction).bfloat16(), NB, S, H, **kw)
+    minus, _ = F2.flash_attention_fwd((qkv.float() - eps * direction).bfloat16(), NB, S, H, **kw)
+    fd = ((plus.float() - minus.float()) * dout.float()).sum().item() / (2 * eps)
+    an = (dqkv * direction).sum().item()
+    assert abs(fd - an) / (abs(an) + 1e-6) < 5e-2, (fd, an)
