@@ -221,3 +221,76 @@ def _mailbox_case(rank, world, mode):
 def test_mailbox_transport_matches_nccl(world, mode):
     _need(world)
     _spawn(_mailbox_case, world, mode)
+
+
+# ---------------------------------------------------------------------------------------------------
+# stress of the cross-GPU flag protocols (stands in for compute-sanitizer's racecheck, which is closed on
+# the pool): many back-to-back collectives of random sizes under concurrent compute, every result checked
+# ---------------------------------------------------------------------------------------------------
+def _allreduce_stress(rank, world):
+    import random
+
+    from pipe_b200.parallel import SymmetricBuffer
+    dev = torch.device("cuda", rank)
+    g = 4 * world
+    buf = SymmetricBuffer(600 * 1000 // g * g, None, dev)
+    rnd = random.Random(1234)                         # same sequence on every rank
+    noise = torch.cuda.Stream(dev)
+    a = torch.randn(2048, 2048, device=dev, dtype=torch.bfloat16)
+    errors = torch.zeros((), dtype=torch.int64, device=dev)
+    base = float(sum(range(1, world + 1)))
+    iters = 1200
+    for it in range(iters):
+        if it % 8 == 0:
+            with torch.cuda.stream(noise):            # tensor-core work competing for SMs and HBM
+                a = (a @ a).clamp_(-1, 1)
+        lo = rnd.randrange(0, buf.numel // g // 2) * g
+        hi = lo + rnd.randrange(1, (buf.numel - lo) // g + 1) * g
+        ctas = rnd.choice([1, 3, 16, 48, 64])
+        use_mm = bool(buf.multicast_ptr) and rnd.random() < 0.5
+        bias = float(it % 7)
+        buf.data[lo:hi].fill_(rank + 1 + bias)
+        buf.all_reduce_(scale=0.5, ctas=ctas, use_multimem=use_mm, lo=lo, hi=hi)
+        errors += (buf.data[lo:hi] != 0.5 * (base + world * bias)).sum()
+    torch.cuda.synchronize()
+    assert int(errors.item()) == 0, f"{int(errors.item())} wrong elements over {iters} collectives"
+    dist.barrier()
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_allreduce_flag_protocol_stress(world):
+    _need(world)
+    _spawn(_allreduce_stress, world)
+
+
+def _mailbox_stress(rank, world):
+    from pipe_b200.parallel.mailbox import PeerMailbox
+    dev = torch.device("cuda", rank)
+    pair = dist.new_group([0, 1])
+    sizes = [16, 4096, 65536 * 3 + 16, 1 << 20]
+    layout = {slot: [((n // 4,), torch.float32)] for slot, n in enumerate(sizes)}
+    box = PeerMailbox(pair, dev, sender_rank=0, layout=layout)
+    noise = torch.cuda.Stream(dev)
+    a = torch.randn(2048, 2048, device=dev, dtype=torch.bfloat16)
+    errors = torch.zeros((), dtype=torch.int64, device=dev)
+    rounds = 300
+    for seq in range(1, rounds + 1):
+        if seq % 8 == 0:
+            with torch.cuda.stream(noise):
+                a = (a @ a).clamp_(-1, 1)
+        for slot, n in enumerate(sizes):                   # 4 x 300 = 1200 messages
+            if rank == 0:
+                src = torch.full((n // 4,), float(seq * 10 + slot), device=dev)
+                box.send(slot, 0, src, seq)
+            else:
+                dst = torch.empty(n // 4, device=dev)
+                box.recv(slot, 0, dst, seq)
+                errors += (dst != float(seq * 10 + slot)).sum()
+    torch.cuda.synchronize()
+    assert int(errors.item()) == 0
+    dist.barrier()
+
+
+def test_mailbox_flag_protocol_stress():
+    _need(2)
+    _spawn(_mailbox_stress, 2)
