@@ -93,6 +93,12 @@ struct __align__(8) FaCtl {
     uint32_t pad;
 };
 
+__device__ __forceinline__ float fast_exp2(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
 // element (row, col) of a [rows][64] bf16 tile with the 128-byte swizzle, as a byte offset
 __device__ __forceinline__ uint32_t sw128_offset(uint32_t row, uint32_t col) {
     return row * 128u + ((((col >> 3) ^ (row & 7u)) << 4) | ((col & 7u) << 1));
@@ -226,24 +232,32 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_cons
             mbar_wait(&ctl->s_full[j & 1], (j >> 1) & 1);
             tc_fence_after();
             const uint32_t s_addr = tmem + lane_addr + (j & 1) * 128;
-            // pass 1: row maximum of this block
-            float m_blk = -INFINITY;
+            // Blocks that lie entirely inside the sequence (and, with a causal mask, entirely below the diagonal)
+            // need no per-element tests: most of a long sequence takes the plain path.
+            const bool need_mask = (j * BN + BN > a.S) || (a.causal && j * BN + BN - 1 > q0);
+            // pass 1: row maximum of this block (raw scores; the scale is positive, so it commutes with max)
+            float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-            for (int c = 0; c < BN; c += 16) {
-                uint32_t r[16];
-                tmem_ld_32x16(s_addr + c, r);
+            for (int c = 0; c < BN; c += 32) {
+                uint32_t r[32];
+                tmem_ld_32x32(s_addr + c, r);
                 tmem_ld_wait();
+                if (need_mask) {
 #pragma unroll
-                for (int i = 0; i < 16; ++i) {
-                    const int key = j * BN + c + i;
-                    const bool ok = key < a.S && (!a.causal || key <= q);
-                    const float v = ok ? __uint_as_float(r[i]) * a.scale_log2 : -INFINITY;
-                    m_blk = fmaxf(m_blk, v);
+                    for (int i = 0; i < 32; ++i) {
+                        const int key = j * BN + c + i;
+                        const bool ok = key < a.S && (!a.causal || key <= q);
+                        mx[i & 3] = fmaxf(mx[i & 3], ok ? __uint_as_float(r[i]) : -INFINITY);
+                    }
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) mx[i & 3] = fmaxf(mx[i & 3], __uint_as_float(r[i]));
                 }
             }
+            const float m_blk = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])) * a.scale_log2;
             const float m_new = fmaxf(m_run, m_blk);
             const float m_use = m_new == -INFINITY ? 0.f : m_new;
-            const float alpha = exp2f(m_run - m_use);          // 0 on the first block (m_run = -inf)
+            const float alpha = fast_exp2(m_run - m_use);          // 0 on the first block (m_run = -inf)
             // the previous block's P V must be complete before P is overwritten and O rescaled
             if (j > 0) {
                 mbar_wait(&ctl->pv_done, (j - 1) & 1);
@@ -263,34 +277,50 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_cons
                 }
             }
             // pass 2: probabilities -> bf16 P tile (dropout applied), row sum before dropout
-            float l_blk = 0.f;
+            float ls[4] = {0.f, 0.f, 0.f, 0.f};
+            const float neg_m = -m_use;
 #pragma unroll
-            for (int c = 0; c < BN; c += 16) {
-                uint32_t r[16];
-                tmem_ld_32x16(s_addr + c, r);
+            for (int c = 0; c < BN; c += 32) {
+                uint32_t r[32];
+                tmem_ld_32x32(s_addr + c, r);
                 tmem_ld_wait();
-                uint32_t packed[8];
+                float p[32];
 #pragma unroll
-                for (int i = 0; i < 16; i += 2) {
-                    float pv[2];
+                for (int i = 0; i < 32; ++i) p[i] = fast_exp2(fmaf(__uint_as_float(r[i]), a.scale_log2, neg_m));
+                if (need_mask) {
 #pragma unroll
-                    for (int e = 0; e < 2; ++e) {
-                        const int key = j * BN + c + i + e;
-                        const bool ok = key < a.S && (!a.causal || key <= q);
-                        float p = ok ? exp2f(__uint_as_float(r[i + e]) * a.scale_log2 - m_use) : 0.f;
-                        l_blk += p;
-                        if (drop && ok && !dropout_keep(rng, a.stream, row_base + key, thr)) p = 0.f;
-                        pv[e] = p;
+                    for (int i = 0; i < 32; ++i) {
+                        const int key = j * BN + c + i;
+                        if (!(key < a.S && (!a.causal || key <= q))) p[i] = 0.f;
                     }
-                    __nv_bfloat162 h2 = __floats2bfloat162_rn(pv[0], pv[1]);
+                }
+#pragma unroll
+                for (int i = 0; i < 32; ++i) ls[i & 3] += p[i];
+                if (drop) {
+#pragma unroll
+                    for (int i = 0; i < 32; i += 4) {
+                        // four consecutive keys share one generator call when the row base is a multiple of 4
+                        const uint64_t idx = row_base + static_cast<uint64_t>(j * BN + c + i);
+#pragma unroll
+                        for (int e = 0; e < 4; ++e)
+                            if (!dropout_keep(rng, a.stream, idx + e, thr)) p[i + e] = 0.f;
+                    }
+                }
+                uint32_t packed[16];
+#pragma unroll
+                for (int i = 0; i < 32; i += 2) {
+                    __nv_bfloat162 h2 = __floats2bfloat162_rn(p[i], p[i + 1]);
                     packed[i >> 1] = *reinterpret_cast<uint32_t*>(&h2);
                 }
-                // 16 keys = two 16-byte chunks of this row in the 64-key block c / 64
+                // 32 keys = four 16-byte chunks of this row in the 64-key block c / 64
                 uint8_t* tile = sP + (c >> 6) * (kFaBM * 128);
                 const uint32_t col = c & 63;
-                *reinterpret_cast<uint4*>(tile + sw128_offset(row, col)) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
-                *reinterpret_cast<uint4*>(tile + sw128_offset(row, col + 8)) = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+#pragma unroll
+                for (int v4 = 0; v4 < 4; ++v4)
+                    *reinterpret_cast<uint4*>(tile + sw128_offset(row, col + 8 * v4)) =
+                        make_uint4(packed[4 * v4], packed[4 * v4 + 1], packed[4 * v4 + 2], packed[4 * v4 + 3]);
             }
+            const float l_blk = (ls[0] + ls[1]) + (ls[2] + ls[3]);
             l_run = l_run * alpha + l_blk;
             m_run = m_new;
             fence_proxy_async();            // P was written by the generic proxy, the tensor core reads it through the async proxy
@@ -516,29 +546,46 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_cons
                 // P / dS of the previous block are still operands of its dV / dK / dQ MMAs until dq_full
                 // (waited below in the previous iteration), so they may be overwritten now
             }
+            const int q_first = (first + it) * kFaBM;
+            const bool need_mask = (q_first + kFaBM > a.S) || (k0 + BN > a.S) || (a.causal && k0 + BN - 1 > q_first);
+            const float neg_lse = -lse2;
+            const float ds_scale = a.scale;
 #pragma unroll
             for (int c = 0; c < BN; c += 16) {
                 uint32_t rs[16], rp[16];
                 tmem_ld_32x16(tmem + lane_addr + c, rs);
                 tmem_ld_32x16(tmem + lane_addr + 128 + c, rp);
                 tmem_ld_wait();
+                float p[16], dp[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    p[i] = fast_exp2(fmaf(__uint_as_float(rs[i]), a.scale_log2, neg_lse));
+                    dp[i] = __uint_as_float(rp[i]);
+                }
+                if (need_mask) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        const int key = k0 + c + i;
+                        if (!(q_ok && key < a.S && (!a.causal || key <= q))) p[i] = 0.f;
+                    }
+                }
+                float pd[16];                                    // what multiplied V in the forward
+                if (drop) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        const bool keep = dropout_keep(rng, a.stream, row_base + static_cast<uint64_t>(k0 + c + i), thr);
+                        pd[i] = keep ? p[i] * inv_keep : 0.f;
+                        dp[i] = keep ? dp[i] * inv_keep : 0.f;       // back through the dropout
+                    }
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) pd[i] = p[i];
+                }
                 uint32_t pk_p[8], pk_ds[8];
 #pragma unroll
                 for (int i = 0; i < 16; i += 2) {
-                    float pp[2], dd[2];
-#pragma unroll
-                    for (int e = 0; e < 2; ++e) {
-                        const int key = k0 + c + i + e;
-                        const bool ok = q_ok && key < a.S && (!a.causal || key <= q);
-                        const float p = ok ? exp2f(__uint_as_float(rs[i + e]) * a.scale_log2 - lse2) : 0.f;
-                        float keep = 1.f;
-                        if (drop && ok && !dropout_keep(rng, a.stream, row_base + key, thr)) keep = 0.f;
-                        const float dp = __uint_as_float(rp[i + e]) * keep * inv_keep;      // back through the dropout
-                        pp[e] = p * keep * inv_keep;                                          // what multiplied V
-                        dd[e] = p * (dp - delta) * a.scale;
-                    }
-                    __nv_bfloat162 hp = __floats2bfloat162_rn(pp[0], pp[1]);
-                    __nv_bfloat162 hd = __floats2bfloat162_rn(dd[0], dd[1]);
+                    __nv_bfloat162 hp = __floats2bfloat162_rn(pd[i], pd[i + 1]);
+                    __nv_bfloat162 hd = __floats2bfloat162_rn(p[i] * (dp[i] - delta) * ds_scale, p[i + 1] * (dp[i + 1] - delta) * ds_scale);
                     pk_p[i >> 1] = *reinterpret_cast<uint32_t*>(&hp);
                     pk_ds[i >> 1] = *reinterpret_cast<uint32_t*>(&hd);
                 }

@@ -14,10 +14,18 @@ import torch.nn.functional as F
 from pipe_b200.ops import functional as F2
 
 
-def timed(fn, iters=20):
+def timed(fn, iters=20, graph=True):
     for _ in range(3):
         fn()
     torch.cuda.synchronize()
+    if not graph:
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0.record()
+        for _ in range(iters):
+            fn()
+        t1.record()
+        torch.cuda.synchronize()
+        return t0.elapsed_time(t1) * 1e3 / iters
     g = torch.cuda.CUDAGraph()
     with torch.cuda.graph(g):
         for _ in range(iters):
@@ -57,7 +65,7 @@ def main():
             ts = timed(lambda: F.scaled_dot_product_attention(q, k, v, is_causal=causal))
             o = F.scaled_dot_product_attention(q, k, v, is_causal=causal)
             go = torch.randn_like(o)
-            tsb = timed(lambda: torch.autograd.grad(o, (q, k, v), go, retain_graph=True))
+            tsb = timed(lambda: torch.autograd.grad(o, (q, k, v), go, retain_graph=True), iters=50, graph=False)   # the engine cannot be captured
             print(f"{S} {NB} {H} {D} {int(causal)} | {t_f:.1f} ({flops / t_f / 1e6:.0f}) | {t_b:.1f} ({2.5 * flops / t_b / 1e6:.0f}) | "
                   f"{tile} | {ts:.1f} / {tsb:.1f}  {note}")
 
