@@ -178,9 +178,13 @@ int pb2_l2_prefetch(const void* ptr, size_t bytes, cudaStream_t stream);
 int pb2_sumsq(const float* x, size_t n, float* out, cudaStream_t stream);
 
 /* ---- attention core on packed QKV [T, 3E] (row = s*NB + n), out [T, E] ----------------------
- * softmax(QK^T/sqrt(D)) V with probability dropout and optional causal mask.  S <= 128, D <= 256.
+ * softmax(QK^T/sqrt(D)) V with probability dropout and optional causal mask.  Single-tile kernels: S <= 128,
+ * D <= 256 (the path for BASELINE's 25-token sequences); longer sequences use pb2_flash_attention_*.
  * Backward recomputes the probabilities and the dropout mask.
  * Reference counterpart: nn.MultiheadAttention core (main.py:148); SURVEY.md K3. */
+/* 1 when the layer executor routes this shape to the flash kernels below (head_dim 64 / 128 and S >= 64): the
+ * caller then provides attn_lse / attn_scratch in pb2_encoder_layer. */
+int pb2_attention_uses_flash(int S, int D);
 int pb2_attention_fwd(const void* qkv, void* out, int NB, int S, int H, int D, int causal, float drop_p,
                       unsigned long long seed, unsigned long long rng_stream, cudaStream_t stream);
 int pb2_attention_bwd(const void* qkv, const void* dout, void* dqkv, int NB, int S, int H, int D, int causal,
@@ -310,6 +314,12 @@ typedef struct pb2_encoder_layer {
      * (same meaning as in pb2_transpose_jobs) */
     int n_peers;
     long long peer_delta[PB2_MAX_PEERS];
+    /* needed when pb2_attention_uses_flash(S, E / heads): log-sum-exp of the attention rows, fp32 [NB * heads * S]
+     * (written by the forward, read by the backward), and for the backward a scratch buffer of
+     * pb2_flash_attention_bwd_scratch_bytes() bytes */
+    float* attn_lse;
+    void* attn_scratch;
+    size_t attn_scratch_bytes;
 } pb2_encoder_layer;
 
 int pb2_encoder_layer_fwd(const pb2_encoder_layer* L, cudaStream_t stream);
@@ -345,10 +355,16 @@ typedef struct pb2_encoder_stack {
     void* workspace;
     size_t workspace_bytes;
     void* side_stream;
+    /* flash-attention shapes only (pb2_attention_uses_flash): `stats` then holds n x (4T + heads * T) floats — each
+     * layer's LayerNorm statistics followed by its attention log-sum-exp — and the backward needs one scratch buffer
+     * of pb2_flash_attention_bwd_scratch_bytes() bytes, shared by the layers of the run */
+    void* attn_scratch;
+    size_t attn_scratch_bytes;
 } pb2_encoder_stack;
 
 size_t pb2_encoder_stack_act_elems(const pb2_encoder_layer* layers, int n, int T);
 size_t pb2_encoder_stack_tmp_elems(const pb2_encoder_layer* layers, int n, int T);
+size_t pb2_encoder_stack_stats_floats(const pb2_encoder_layer* layers, int n, int S, int T);
 int pb2_encoder_stack_fwd(const pb2_encoder_stack* s, cudaStream_t stream);
 int pb2_encoder_stack_bwd(const pb2_encoder_stack* s, cudaStream_t stream);
 

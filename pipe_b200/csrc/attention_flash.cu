@@ -22,6 +22,7 @@
 // attention_tc.cu stay the path for BASELINE's 25-token sequences (a UMMA pipeline costs more than it saves
 // there); this file is the path beyond.
 #include <math.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "pipe_b200.h"
@@ -740,6 +741,20 @@ int launch_fwd(const void* qkv, const FaArgs& a, cudaStream_t stream) {
 }
 
 }  // namespace
+
+extern "C" int pb2_attention_uses_flash(int S, int D) {
+    // Measured on B200 (profiles/attention_bench_r2.txt): at S = 128, D = 64 the flash pair takes 10 + 28 us against
+    // 28 + 84 us for the single-tile kernels; below one 64-key block the single-tile kernels win (one small tile per
+    // head, no TMEM pipeline to fill).  PB2_ATTN_FLASH=0 keeps the single-tile kernels wherever they apply.
+    static int off = -1;
+    if (off < 0) {
+        const char* e = getenv("PB2_ATTN_FLASH");
+        off = (e && e[0] == '0') ? 1 : 0;
+    }
+    if (D != 64 && D != 128) return 0;
+    if (S > 128) return 1;
+    return (S >= 64 && !off) ? 1 : 0;
+}
 
 extern "C" int pb2_flash_attention_fwd(const void* qkv, void* out, float* lse, int NB, int S, int H, int D, int causal,
                                        float drop_p, unsigned long long seed, unsigned long long rng_stream,

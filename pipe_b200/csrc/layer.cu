@@ -51,7 +51,12 @@ extern "C" int pb2_encoder_layer_fwd(const pb2_encoder_layer* L, cudaStream_t st
     if (pf && pb2_l2_prefetch(L->w_o, w_ee, stream)) return -1;
     if (linear(L, Lin{L->w_qkv, E, 3 * E, E}, L->x, T, L->qkv, L->b_qkv, 0, 0.f, 0, nullptr, 0.f, nullptr, stream)) return -1;
     if (pf && pb2_l2_prefetch(L->w_1, w_ef, stream)) return -1;
-    if (pb2_attention_fwd(L->qkv, L->a, L->NB, L->S, L->heads, E / L->heads, L->causal, p, L->seed, 0, stream)) return -1;
+    if (pb2_attention_uses_flash(L->S, E / L->heads)) {
+        if (!L->attn_lse) { pb2::set_error("pb2_encoder_layer_fwd: this shape uses flash attention: attn_lse is required"); return -1; }
+        if (pb2_flash_attention_fwd(L->qkv, L->a, L->attn_lse, L->NB, L->S, L->heads, E / L->heads, L->causal, p, L->seed, 0, stream)) return -1;
+    } else if (pb2_attention_fwd(L->qkv, L->a, L->NB, L->S, L->heads, E / L->heads, L->causal, p, L->seed, 0, stream)) {
+        return -1;
+    }
     if (linear(L, Lin{L->w_o, E, E, E}, L->a, T, L->o, L->b_o, 0, p, 1, nullptr, 0.f, nullptr, stream)) return -1;
     if (pb2_add_layernorm_fwd(L->x, L->o, L->g1, L->be1, L->x1, L->mean1, L->rstd1, T, E, L->eps, stream)) return -1;
     if (pf && pb2_l2_prefetch(L->w_2, w_ef, stream)) return -1;
@@ -85,7 +90,13 @@ extern "C" int pb2_encoder_layer_bwd(const pb2_encoder_layer* L, cudaStream_t st
                               L->seed, 1, stream)) return -1;
     if (pf && pb2_l2_prefetch(L->wt_qkv, w_qt, stream)) return -1;
     if (linear(L, Lin{L->wt_o, L->ldt_o, E, E}, L->do_, T, L->da, nullptr, 0, 0.f, 0, nullptr, 0.f, nullptr, stream)) return -1;
-    if (pb2_attention_bwd(L->qkv, L->da, L->dqkv, L->NB, L->S, L->heads, E / L->heads, L->causal, p, L->seed, 0, stream)) return -1;
+    if (pb2_attention_uses_flash(L->S, E / L->heads)) {
+        if (!L->attn_lse || !L->attn_scratch) { pb2::set_error("pb2_encoder_layer_bwd: this shape uses flash attention: attn_lse / attn_scratch are required"); return -1; }
+        if (pb2_flash_attention_bwd(L->qkv, L->a, L->da, L->attn_lse, L->dqkv, L->attn_scratch, L->attn_scratch_bytes, L->NB, L->S,
+                                    L->heads, E / L->heads, L->causal, p, L->seed, 0, stream)) return -1;
+    } else if (pb2_attention_bwd(L->qkv, L->da, L->dqkv, L->NB, L->S, L->heads, E / L->heads, L->causal, p, L->seed, 0, stream)) {
+        return -1;
+    }
     // every source of the wgrad-operand transposes exists once the attention backward is done: from here
     // on they can run on the side stream, next to the QKV dgrad and the next layer's kernels
     cudaStream_t tstream = stream;
@@ -143,6 +154,11 @@ void carve_act(pb2_encoder_layer& d, char* base, int T) {
     d.f = base;
 }
 
+// floats of `stats` per layer: LayerNorm statistics, plus the attention log-sum-exp on flash shapes
+inline size_t stats_stride(const pb2_encoder_layer& L, int S, int T) {
+    return static_cast<size_t>(4) * T + (pb2_attention_uses_flash(S, L.E / L.heads) ? static_cast<size_t>(L.heads) * T : 0);
+}
+
 int check_stack(const pb2_encoder_stack* s, const char* who) {
     if (!s || !s->layers || s->n_layers <= 0) { pb2::set_error("%s: empty stack", who); return -1; }
     if (s->T != s->S * s->NB) { pb2::set_error("%s: T != S * NB", who); return -1; }
@@ -157,6 +173,10 @@ extern "C" size_t pb2_encoder_stack_act_elems(const pb2_encoder_layer* layers, i
     size_t total = 0;
     for (int l = 0; l < n; ++l) total += act_elems(layers[l], T);
     return total;
+}
+
+extern "C" size_t pb2_encoder_stack_stats_floats(const pb2_encoder_layer* layers, int n, int S, int T) {
+    return n > 0 ? static_cast<size_t>(n) * stats_stride(layers[0], S, T) : 0;
 }
 
 extern "C" size_t pb2_encoder_stack_tmp_elems(const pb2_encoder_layer* layers, int n, int T) {
@@ -180,8 +200,9 @@ extern "C" int pb2_encoder_stack_fwd(const pb2_encoder_stack* s, cudaStream_t st
         d.y = y + static_cast<size_t>(l) * T * E * 2;
         carve_act(d, act, T);
         act += act_elems(d, T) * 2;
-        float* st = s->stats + static_cast<size_t>(l) * 4 * T;
+        float* st = s->stats + static_cast<size_t>(l) * stats_stride(s->layers[0], s->S, T);
         d.mean1 = st; d.rstd1 = st + T; d.mean2 = st + 2 * T; d.rstd2 = st + 3 * T;
+        d.attn_lse = st + 4 * T;
         d.workspace = s->workspace; d.workspace_bytes = s->workspace_bytes;
         d.prefetch = 0; d.next_weight = nullptr; d.next_weight_bytes = 0;
         if (pb2_encoder_layer_fwd(&d, stream)) return -1;
@@ -211,8 +232,10 @@ extern "C" int pb2_encoder_stack_bwd(const pb2_encoder_stack* s, cudaStream_t st
         d.x = l == 0 ? s->x : y + static_cast<size_t>(l - 1) * T * E * 2;
         d.y = y + static_cast<size_t>(l) * T * E * 2;
         carve_act(d, static_cast<char*>(s->act) + act_off[l], T);
-        float* st = s->stats + static_cast<size_t>(l) * 4 * T;
+        float* st = s->stats + static_cast<size_t>(l) * stats_stride(s->layers[0], s->S, T);
         d.mean1 = st; d.rstd1 = st + T; d.mean2 = st + 2 * T; d.rstd2 = st + 3 * T;
+        d.attn_lse = st + 4 * T;
+        d.attn_scratch = s->attn_scratch; d.attn_scratch_bytes = s->attn_scratch_bytes;
         // scratch of this layer: dr2 | df | dz1 | dx1 | dr1 | do | da | dqkv | dx
         char* b = static_cast<char*>(s->tmp) + tmp_off[l];
         const size_t FF = d.FF, tt = T;

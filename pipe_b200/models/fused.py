@@ -161,6 +161,16 @@ def _side_stream(device: torch.device) -> "torch.cuda.Stream":
             st = _side_streams[device.index] = torch.cuda.Stream(device)
         return st
 
+def _uses_flash(S: int, D: int) -> bool:
+    """The layer executor routes this (sequence length, head_dim) to the flash-attention kernels: extra buffers needed."""
+    return bool(_lib.load().pb2_attention_uses_flash(ctypes.c_int(S), ctypes.c_int(D)))
+
+
+def _flash_scratch(NB: int, S: int, H: int, D: int, device: torch.device) -> Tensor:
+    n = int(_lib.load().pb2_flash_attention_bwd_scratch_bytes(ctypes.c_int(NB), ctypes.c_int(S), ctypes.c_int(H), ctypes.c_int(D)))
+    return torch.empty(n, dtype=torch.uint8, device=device)
+
+
 class _EncoderLayerFn(torch.autograd.Function):
     """Forward and backward of the whole layer, each one call into the C++ layer executor
     (``csrc/layer.cu``): 7 and 8 kernel launches respectively, no Python between them."""
@@ -180,7 +190,8 @@ class _EncoderLayerFn(torch.autograd.Function):
         # one allocation for every saved activation: qkv | a | o | x1 | hmid | f
         widths = (3 * E, E, E, E, FF, E)
         act = torch.empty(T * sum(widths), dtype=torch.bfloat16, device=dev)
-        stats = torch.empty(4 * T, dtype=torch.float32, device=dev)
+        flash = _uses_flash(S, E // layer.nhead)
+        stats = torch.empty(4 * T + (layer.nhead * T if flash else 0), dtype=torch.float32, device=dev)
         y = torch.empty((S, NB, E), dtype=torch.bfloat16, device=dev)
 
         d = layer._desc(dev)
@@ -193,6 +204,8 @@ class _EncoderLayerFn(torch.autograd.Function):
             at += T * w
         sb = stats.data_ptr()
         d.mean1, d.rstd1, d.mean2, d.rstd2 = sb, sb + 4 * T, sb + 8 * T, sb + 12 * T
+        if flash:
+            d.attn_lse = sb + 16 * T
         stream = _lib.raw_stream(dev)
         ws = workspace(dev, stream)
         d.workspace, d.workspace_bytes = ws.data_ptr(), ws.numel()
@@ -233,6 +246,10 @@ class _EncoderLayerFn(torch.autograd.Function):
             at += T * w
         sb = stats.data_ptr()
         d.mean1, d.rstd1, d.mean2, d.rstd2 = sb, sb + 4 * T, sb + 8 * T, sb + 12 * T
+        scratch = None
+        if _uses_flash(S, E // layer.nhead):
+            scratch = _flash_scratch(NB, S, layer.nhead, E // layer.nhead, dev)
+            d.attn_lse, d.attn_scratch, d.attn_scratch_bytes = sb + 16 * T, scratch.data_ptr(), scratch.numel()
         base, at = tmp.data_ptr(), 0
         for name, w in zip(("dr2", "df", "dz1", "dx1", "dr1", "do_", "da", "dqkv"), widths):
             setattr(d, name, base + at * 2)
@@ -378,8 +395,8 @@ class EncoderStack:
         self.layers = list(layers)
         self.n = len(self.layers)
         first = self.layers[0]
-        if any(l.d_model != first.d_model for l in self.layers):
-            raise ValueError("layers of a stack must share d_model")
+        if any(l.d_model != first.d_model or l.nhead != first.nhead for l in self.layers):
+            raise ValueError("layers of a stack must share d_model and nhead")
         self.E = first.d_model
         self.anchor = first.self_attn.in_proj_weight
         self.stash = StackStash([l._lg(k) for l in self.layers for k in ("qkv", "o", "l1", "l2")])
@@ -486,7 +503,8 @@ class _StackFn(torch.autograd.Function):
         arr = stack.static(dev, with_grads=False)
         act_elems, _ = stack.sizes(arr, T)
         act = torch.empty(act_elems, dtype=torch.bfloat16, device=dev)
-        stats = torch.empty(4 * T * n, dtype=torch.float32, device=dev)
+        n_stats = int(_lib.load().pb2_encoder_stack_stats_floats(arr, ctypes.c_int(n), ctypes.c_int(S), ctypes.c_int(T)))
+        stats = torch.empty(n_stats, dtype=torch.float32, device=dev)
         ys = torch.empty((n, S, NB, E), dtype=torch.bfloat16, device=dev)
         stream = _lib.raw_stream(dev)
         ws = workspace(dev, stream)
@@ -530,6 +548,11 @@ class _StackFn(torch.autograd.Function):
         c.seeds = ctypes.addressof(seeds) if seeds is not None else None
         c.x, c.y, c.act, c.stats = x2.data_ptr(), ys.data_ptr(), act.data_ptr(), stats.data_ptr()
         c.dy, c.dx, c.tmp, c.stash_off = dy2.data_ptr(), dx.data_ptr(), tmp.data_ptr(), off
+        first = stack.layers[0]
+        scratch = None
+        if _uses_flash(S, E // first.nhead):
+            scratch = _flash_scratch(NB, S, first.nhead, E // first.nhead, dev)
+            c.attn_scratch, c.attn_scratch_bytes = scratch.data_ptr(), scratch.numel()
         c.workspace, c.workspace_bytes = ws.data_ptr(), ws.numel()
         c.side_stream = side.cuda_stream if side is not None else None
         with _lib.on_device(dev):

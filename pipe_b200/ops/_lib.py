@@ -63,6 +63,7 @@ class EncoderLayerDesc(ctypes.Structure):
         + [("workspace", _vp), ("workspace_bytes", ctypes.c_size_t)]
         + [("next_weight", _vp), ("next_weight_bytes", ctypes.c_size_t), ("prefetch", _ci), ("side_stream", _vp)]
         + [("n_peers", _ci), ("peer_delta", _ll * 7)]
+        + [("attn_lse", _vp), ("attn_scratch", _vp), ("attn_scratch_bytes", ctypes.c_size_t)]
     )
 
 
@@ -72,7 +73,7 @@ class EncoderStackDesc(ctypes.Structure):
         ("n_layers", _ci), ("layers", _vp), ("T", _ci), ("NB", _ci), ("S", _ci), ("drop_p", _cf),
         ("seeds", _vp), ("x", _vp), ("y", _vp), ("act", _vp), ("stats", _vp), ("dy", _vp), ("dx", _vp),
         ("tmp", _vp), ("stash_off", _ci), ("workspace", _vp), ("workspace_bytes", ctypes.c_size_t),
-        ("side_stream", _vp),
+        ("side_stream", _vp), ("attn_scratch", _vp), ("attn_scratch_bytes", ctypes.c_size_t),
     ]
 
 
@@ -96,6 +97,7 @@ def load() -> ctypes.CDLL:
         lib.pb2_encoder_stack_act_elems.restype = ctypes.c_size_t
         lib.pb2_flash_attention_bwd_scratch_bytes.restype = ctypes.c_size_t
         lib.pb2_encoder_stack_tmp_elems.restype = ctypes.c_size_t
+        lib.pb2_encoder_stack_stats_floats.restype = ctypes.c_size_t
         _lib = lib
     return _lib
 

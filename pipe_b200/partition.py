@@ -71,8 +71,14 @@ class PipeSequential(nn.Sequential):
         run: List[nn.Module] = []
 
         def close() -> None:
+            chain = None
             if len(run) >= 2:
-                plan.append((type(run[0]).pb2_make_chain(list(run)), tuple(run)))
+                try:
+                    chain = type(run[0]).pb2_make_chain(list(run))
+                except ValueError:
+                    chain = None               # layers of different widths: run them one by one
+            if chain is not None:
+                plan.append((chain, tuple(run)))
             else:
                 plan.extend(run)
             run.clear()

@@ -36,7 +36,7 @@ def test_ctypes_struct_layouts_match_the_header():
             printf("%zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(pb2_gemm_desc), offsetof(pb2_gemm_desc, persistent),
                    sizeof(pb2_encoder_layer), offsetof(pb2_encoder_layer, side_stream),
                    offsetof(pb2_encoder_layer, peer_delta), sizeof(pb2_encoder_stack),
-                   offsetof(pb2_encoder_stack, side_stream), sizeof(pb2_transpose_jobs));
+                   offsetof(pb2_encoder_stack, attn_scratch_bytes), sizeof(pb2_transpose_jobs));
             return 0;
         }
     """)
@@ -52,7 +52,7 @@ def test_ctypes_struct_layouts_match_the_header():
     from pipe_b200.ops import functional as F2
     assert _lib.EncoderLayerDesc.peer_delta.offset == peer_off
     assert ctypes.sizeof(_lib.EncoderStackDesc) == stack_size
-    assert _lib.EncoderStackDesc.side_stream.offset == stack_off
+    assert _lib.EncoderStackDesc.attn_scratch_bytes.offset == stack_off
     assert ctypes.sizeof(F2._TransposeJobs) == jobs_size
     assert ctypes.sizeof(_lib.GemmDesc) == gemm_size
     assert _lib.GemmDesc.persistent.offset == gemm_off

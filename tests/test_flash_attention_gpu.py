@@ -106,3 +106,41 @@ def test_flash_backward_dropout_is_consistent_with_forward():
     fd = ((plus.float() - minus.float()) * dout.float()).sum().item() / (2 * eps)
     an = (dqkv * direction).sum().item()
     assert abs(fd - an) / (abs(an) + 1e-6) < 5e-2, (fd, an)
+
+
+@pytest.mark.parametrize("S,E,H", [(128, 256, 4), (200, 256, 2), (640, 256, 4)])
+def test_fused_layers_use_flash_attention_beyond_one_tile(S, E, H):
+    """The encoder layer (per-layer call and the stage-level stack call) routes S >= 64 with head_dim 64 / 128 to
+    the flash kernels — including sequences the single-tile kernels refuse (S > 128) — and matches
+    nn.TransformerEncoderLayer."""
+    from torch import nn
+
+    from pipe_b200.models.fused import FusedEncoderLayer, _uses_flash
+    from pipe_b200.ops import wgrad
+    from pipe_b200.partition import PipeSequential
+    assert _uses_flash(S, E // H)
+    torch.manual_seed(0)
+    NB, FF = 2, 512
+    refs = [nn.TransformerEncoderLayer(E, H, FF, 0.0).to(dev) for _ in range(2)]
+    fused = [FusedEncoderLayer(E, H, FF, 0.0).to(dev) for _ in range(2)]
+    for f, r in zip(fused, refs):
+        f.load_state_dict(r.state_dict())
+    x = torch.randn(S, NB, E, device=dev)
+    g = torch.randn(S, NB, E, device=dev)
+    xr = x.clone().requires_grad_()
+    yr = refs[1](refs[0](xr))
+    yr.backward(g)
+    for runner in ("stack", "single"):
+        xf = x.bfloat16().requires_grad_()
+        if runner == "stack":
+            yf = PipeSequential(*fused)(xf)
+        else:
+            yf = fused[1](fused[0](xf))
+        assert rel(yf, yr) < 3e-2, (runner, rel(yf, yr))
+        yf.backward(g.bfloat16())
+        wgrad.flush_pending()
+        assert rel(xf.grad, xr.grad) < 6e-2, (runner, rel(xf.grad, xr.grad))
+        for f, r in zip(fused, refs):
+            for (name, pf), pr in zip(f.named_parameters(), r.parameters()):
+                assert rel(pf.grad, pr.grad) < 6e-2, (runner, name, rel(pf.grad, pr.grad))
+                pf.grad = None
