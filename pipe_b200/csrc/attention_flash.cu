@@ -100,6 +100,27 @@ __device__ __forceinline__ float fast_exp2(float x) {
     return y;
 }
 
+// Dropout decisions of eight consecutive keys of one attention row from ONE generator call: 16 random bits per
+// element (p is quantised to 1/65536; the kernels scale by the exact keep probability of the quantised value).
+// counter = row * ceil(S / 8) + key / 8, so forward, backward and recompute agree for any S.
+__device__ __forceinline__ uint32_t drop_keep8(const CounterRng& rng, uint64_t stream, uint64_t counter, uint32_t thr16) {
+    const uint4 r = rng(counter, stream);
+    uint32_t bits = 0;
+    bits |= ((r.x & 0xFFFFu) >= thr16) << 0;
+    bits |= ((r.x >> 16) >= thr16) << 1;
+    bits |= ((r.y & 0xFFFFu) >= thr16) << 2;
+    bits |= ((r.y >> 16) >= thr16) << 3;
+    bits |= ((r.z & 0xFFFFu) >= thr16) << 4;
+    bits |= ((r.z >> 16) >= thr16) << 5;
+    bits |= ((r.w & 0xFFFFu) >= thr16) << 6;
+    bits |= ((r.w >> 16) >= thr16) << 7;
+    return bits;
+}
+__host__ __device__ __forceinline__ uint32_t drop_thr16(float p) {
+    const float t = p * 65536.f + 0.5f;
+    return t < 0.f ? 0u : (t > 65535.f ? 65535u : static_cast<uint32_t>(t));
+}
+
 // element (row, col) of a [rows][64] bf16 tile with the 128-byte swizzle, as a byte offset
 __device__ __forceinline__ uint32_t sw128_offset(uint32_t row, uint32_t col) {
     return row * 128u + ((((col >> 3) ^ (row & 7u)) << 4) | ((col & 7u) << 1));
@@ -225,9 +246,9 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_cons
         const int q = q0 + row;
         const uint32_t lane_addr = static_cast<uint32_t>(quarter * 32) << 16;
         const CounterRng rng(a.seed);
-        const uint32_t thr = static_cast<uint32_t>(fminf(a.drop_p, 0.999999f) * 4294967296.0f);
+        const uint32_t thr16 = drop_thr16(a.drop_p);
         const bool drop = a.drop_p > 0.f;
-        const uint64_t row_base = (static_cast<uint64_t>(n * a.H + h) * a.S + (q < a.S ? q : 0)) * static_cast<uint64_t>(a.S);
+        const uint64_t row_base = (static_cast<uint64_t>(n * a.H + h) * a.S + (q < a.S ? q : 0)) * static_cast<uint64_t>((a.S + 7) >> 3);
         float m_run = -INFINITY, l_run = 0.f;
         for (int j = 0; j < n_blocks; ++j) {
             mbar_wait(&ctl->s_full[j & 1], (j >> 1) & 1);
@@ -299,12 +320,11 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_cons
                 for (int i = 0; i < 32; ++i) ls[i & 3] += p[i];
                 if (drop) {
 #pragma unroll
-                    for (int i = 0; i < 32; i += 4) {
-                        // four consecutive keys share one generator call when the row base is a multiple of 4
-                        const uint64_t idx = row_base + static_cast<uint64_t>(j * BN + c + i);
+                    for (int i = 0; i < 32; i += 8) {
+                        const uint32_t keep = drop_keep8(rng, a.stream, row_base + static_cast<uint64_t>((j * BN + c + i) >> 3), thr16);
 #pragma unroll
-                        for (int e = 0; e < 4; ++e)
-                            if (!dropout_keep(rng, a.stream, idx + e, thr)) p[i + e] = 0.f;
+                        for (int e = 0; e < 8; ++e)
+                            if (!((keep >> e) & 1u)) p[i + e] = 0.f;
                     }
                 }
                 uint32_t packed[16];
@@ -331,7 +351,7 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_cons
         // epilogue: O / l (and the dropout rescale), bf16, straight to [T, E]
         mbar_wait(&ctl->pv_done, (n_blocks - 1) & 1);
         tc_fence_after();
-        const float inv = (l_run > 0.f ? 1.f / l_run : 0.f) * (drop ? 1.f / (1.f - a.drop_p) : 1.f);
+        const float inv = (l_run > 0.f ? 1.f / l_run : 0.f) * (drop ? 65536.f / (65536.f - static_cast<float>(thr16)) : 1.f);
         const uint32_t o_addr = tmem + lane_addr + kOCol;
         __nv_bfloat16* dst = a.out + (static_cast<size_t>(q) * a.NB + n) * a.ld_out + h * D;
 #pragma unroll
@@ -531,16 +551,16 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_cons
         const int row = quarter * 32 + lane;
         const uint32_t lane_addr = static_cast<uint32_t>(quarter * 32) << 16;
         const CounterRng rng(a.seed);
-        const uint32_t thr = static_cast<uint32_t>(fminf(a.drop_p, 0.999999f) * 4294967296.0f);
+        const uint32_t thr16 = drop_thr16(a.drop_p);
         const bool drop = a.drop_p > 0.f;
-        const float inv_keep = drop ? 1.f / (1.f - a.drop_p) : 1.f;
+        const float inv_keep = drop ? 65536.f / (65536.f - static_cast<float>(thr16)) : 1.f;
         for (int it = 0; it < n_it; ++it) {
             const int q = (first + it) * kFaBM + row;
             const bool q_ok = q < a.S;
             const size_t stat = static_cast<size_t>(n * a.H + h) * a.S + (q_ok ? q : 0);
             const float lse2 = q_ok ? a.lse[stat] * 1.4426950408889634f : 0.f;
             const float delta = q_ok ? a.delta[stat] : 0.f;
-            const uint64_t row_base = (static_cast<uint64_t>(n * a.H + h) * a.S + (q_ok ? q : 0)) * static_cast<uint64_t>(a.S);
+            const uint64_t row_base = (static_cast<uint64_t>(n * a.H + h) * a.S + (q_ok ? q : 0)) * static_cast<uint64_t>((a.S + 7) >> 3);
             mbar_wait(&ctl->sdp_full, it & 1);
             tc_fence_after();
             if (it > 0) {
@@ -573,10 +593,14 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_cons
                 float pd[16];                                    // what multiplied V in the forward
                 if (drop) {
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) {
-                        const bool keep = dropout_keep(rng, a.stream, row_base + static_cast<uint64_t>(k0 + c + i), thr);
-                        pd[i] = keep ? p[i] * inv_keep : 0.f;
-                        dp[i] = keep ? dp[i] * inv_keep : 0.f;       // back through the dropout
+                    for (int i = 0; i < 16; i += 8) {
+                        const uint32_t keep = drop_keep8(rng, a.stream, row_base + static_cast<uint64_t>((k0 + c + i) >> 3), thr16);
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) {
+                            const bool k1 = (keep >> e) & 1u;
+                            pd[i + e] = k1 ? p[i + e] * inv_keep : 0.f;
+                            dp[i + e] = k1 ? dp[i + e] * inv_keep : 0.f;       // back through the dropout
+                        }
                     }
                 } else {
 #pragma unroll
