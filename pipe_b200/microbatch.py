@@ -12,12 +12,14 @@ Parity: reference ``pipe.py:446-464,476-477,484,490``, ``pipeline.py:44-54,229``
 """
 from __future__ import annotations
 
+import threading
+
 from typing import Any, Callable, Iterator, List, Optional, Sequence, Tuple, Union
 
 import torch
 from torch import Tensor
 
-__all__ = ["NoChunk", "Batch", "check", "scatter", "gather", "GatherBuffer"]
+__all__ = ["NoChunk", "Batch", "check", "scatter", "gather", "GatherBuffer", "CellContext", "use_cell", "current_cell"]
 
 Tensors = Sequence[Tensor]
 TensorOrTensors = Union[Tensor, Tensors]
@@ -164,27 +166,27 @@ def scatter(*inputs: Any, chunks: int) -> List[Batch]:
 
 
 def _adjacent_base(tensors: Sequence[Tensor]) -> Optional[Tensor]:
-    """If ``tensors`` are consecutive dim-0 slices of one contiguous buffer (a last stage that wrote
-    its micro-batch outputs straight into a :class:`GatherBuffer`), return the zero-copy view that
-    spans them; else ``None``."""
+    """If ``tensors`` are consecutive dim-0 slices of one buffer with identical strides (a last stage that
+    wrote its micro-batch outputs straight into a :class:`GatherBuffer`; rows may be padded, i.e. the
+    slices need not be contiguous), return the zero-copy view that spans them; else ``None``."""
     first = tensors[0]
-    if not first.is_contiguous() or first.dim() == 0:
+    if first.dim() == 0 or first.stride(-1) != 1 and first.numel() > 0:
         return None
     storage = first.untyped_storage()
-    item = first.element_size()
+    strides = first.stride()
     at = first.storage_offset()
     rows = 0
     for t in tensors:
         if (t.dtype != first.dtype or t.device != first.device or t.shape[1:] != first.shape[1:]
-                or not t.is_contiguous() or t.untyped_storage().data_ptr() != storage.data_ptr()
+                or t.stride() != strides or t.untyped_storage().data_ptr() != storage.data_ptr()
                 or t.storage_offset() != at):
             return None
-        at += t.numel()
+        at += t.size(0) * strides[0]
         rows += t.size(0)
-    if (first.storage_offset() + (at - first.storage_offset())) * item > storage.nbytes():
+    if at * first.element_size() > storage.nbytes():
         return None
     return torch.empty(0, dtype=first.dtype, device=first.device).set_(
-        storage, first.storage_offset(), (rows, *first.shape[1:]))
+        storage, first.storage_offset(), (rows, *first.shape[1:]), strides)
 
 
 class _AdjacentCat(torch.autograd.Function):
@@ -238,8 +240,9 @@ class GatherBuffer:
     ``gather`` costs one extra read+write of the whole output (450 MiB for the
     tutorial logits).  A last-stage module that knows its slice
     can instead write straight into ``buffer[offset:offset+rows]``; ``cat`` then
-    has nothing left to do.  Used by the fused LM head; plain ``gather`` remains
-    the default path.
+    has nothing left to do.  The fused vocabulary projection does that for the logits it
+    returns (``models/fused.py`` ``_DecoderFn``; it learns its slice from
+    :func:`current_cell`); plain ``gather`` remains the path for everything else.
     """
 
     def __init__(self, rows: int, tail_shape: Sequence[int], *, dtype: torch.dtype, device: torch.device):
@@ -261,3 +264,41 @@ class GatherBuffer:
         row = b[0].numel() if b.size(0) else 0
         return torch.empty(0, dtype=b.dtype, device=b.device).set_(
             b.untyped_storage(), b.storage_offset() + lo * row, (hi - lo, *b.shape[1:]))
+
+
+# ---------------------------------------------------------------------------------------
+# which micro-batch is running: lets a last-stage module write into its slice of the mini-batch output
+# ---------------------------------------------------------------------------------------
+class CellContext:
+    """Set by the pipeline executor around every stage call: micro-batch ``index``, the dim-0 row count of
+    every micro-batch of this forward pass (``sizes``) and a dict shared by all cells of the pass."""
+
+    __slots__ = ("index", "sizes", "shared")
+
+    def __init__(self, index: int, sizes: Sequence[int], shared: dict) -> None:
+        self.index = index
+        self.sizes = list(sizes)
+        self.shared = shared
+
+
+_cell_local = threading.local()
+
+
+class use_cell:
+    def __init__(self, cell: Optional[CellContext]) -> None:
+        self.cell = cell
+        self.prev: Optional[CellContext] = None
+
+    def __enter__(self):
+        self.prev = getattr(_cell_local, "cell", None)
+        _cell_local.cell = self.cell
+        return self.cell
+
+    def __exit__(self, *exc):
+        _cell_local.cell = self.prev
+        return False
+
+
+def current_cell() -> Optional[CellContext]:
+    """The running cell's context, or ``None`` outside a pipeline."""
+    return getattr(_cell_local, "cell", None)

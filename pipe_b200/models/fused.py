@@ -637,39 +637,57 @@ class FusedEncoder(nn.Module):
 # vocabulary projection (+ fused cross-entropy)
 # ======================================================================================
 class _DecoderFn(torch.autograd.Function):
-    """logits = x W^T + b, returned batch-first like the reference's Decoder."""
+    """logits = x W^T + b, returned batch-first like the reference's Decoder.
+
+    The GEMM runs on batch-first rows, so its output *is* the ``(N, S, V)`` tensor (row pitch padded to 64
+    columns).  Inside a pipeline every micro-batch writes into its slice of ONE mini-batch-wide buffer
+    (``microbatch.GatherBuffer``, found through ``microbatch.current_cell()``), which makes the final
+    ``gather`` a view instead of a 2 x 59 MB copy per micro-batch at the reference's shape
+    (reference ``pipe.py:490``, ``README.md:382``)."""
 
     @staticmethod
     def forward(ctx, x: Tensor, module: "FusedDecoder", *params: Tensor) -> Tensor:  # type: ignore[override]
+        from .. import microbatch
         S, NB, E = x.shape
         T = S * NB
-        x2 = x.contiguous().view(T, E)
-        if x2.dtype != torch.bfloat16:
-            x2 = x2.to(torch.bfloat16)
+        xb = x.transpose(0, 1).contiguous().view(T, E)              # batch-first rows: n * S + s
+        if xb.dtype != torch.bfloat16:
+            xb = xb.to(torch.bfloat16)
         V = module.ntoken
         ld = _round_up(V, 64)
         w16, _ = module._sh("dec")
-        buf = torch.empty((T, ld), dtype=torch.bfloat16, device=x.device)
-        gemm_nt(w16, x2, out=buf[:, :V], transpose_out=True, bias=module.decoder.bias, bias_along_m=True)
+        cell = microbatch.current_cell()
+        buf = None
+        if cell is not None and cell.index < len(cell.sizes) and cell.sizes[cell.index] == NB:
+            key = ("logits", id(module), S, ld)
+            gb = cell.shared.get(key)
+            if gb is None:
+                gb = microbatch.GatherBuffer(sum(cell.sizes), (S, ld), dtype=torch.bfloat16, device=x.device)
+                gb.plan(cell.sizes)
+                cell.shared[key] = gb
+            buf = gb.slot(cell.index)                               # [NB, S, ld] alias of the shared buffer
+        if buf is None:
+            buf = torch.empty((NB, S, ld), dtype=torch.bfloat16, device=x.device)
+        gemm_nt(w16, xb, out=buf.view(T, ld)[:, :V], transpose_out=True, bias=module.decoder.bias, bias_along_m=True)
         ctx.module = module
         ctx.meta = (S, NB, E, V, ld)
-        ctx.save_for_backward(x2)
-        return buf[:, :V].view(S, NB, V).permute(1, 0, 2)
+        ctx.save_for_backward(xb)
+        return buf[:, :, :V]
 
     @staticmethod
     def backward(ctx, dlogits: Tensor):  # type: ignore[override]
         module: FusedDecoder = ctx.module
         S, NB, E, V, ld = ctx.meta
         T = S * NB
-        (x2,) = ctx.saved_tensors
-        buf = torch.zeros((T, ld), dtype=torch.bfloat16, device=x2.device)
-        buf[:, :V].view(S, NB, V).copy_(dlogits.permute(1, 0, 2))
+        (xb,) = ctx.saved_tensors
+        buf = torch.zeros((T, ld), dtype=torch.bfloat16, device=xb.device)
+        buf[:, :V].view(NB, S, V).copy_(dlogits)
         dl = buf[:, :V]
         _, w16t = module._sh("dec")
-        dx = gemm_nt(w16t[:, :V], dl, transpose_out=True)
+        dx = gemm_nt(w16t[:, :V], dl, transpose_out=True)           # batch-first rows
         lg = module._lg("dec")
-        F2.transpose_multi(lg.jobs(x2, dl), lg.peer_deltas)
-        return (dx.view(S, NB, E), None) + (None,) * (len(ctx.needs_input_grad) - 2)
+        F2.transpose_multi(lg.jobs(xb, dl), lg.peer_deltas)
+        return (dx.view(NB, S, E).transpose(0, 1), None) + (None,) * (len(ctx.needs_input_grad) - 2)
 
 
 class _DecoderLossFn(torch.autograd.Function):

@@ -41,7 +41,7 @@ from ..autograd.copy import Copy, Wait
 from ..autograd.dependency import fork, join
 from ..autograd.seeds import SeedBase, seed_scope
 from ..autograd.stream import AbstractStream, current_stream, use_device
-from ..microbatch import Batch
+from ..microbatch import Batch, CellContext, use_cell
 from ..skip.layout import SkipLayout
 from ..skip.tracker import SkipTrackerThroughPotals, use_skip_tracker
 from .schedule import Cell, clock_cycles
@@ -136,6 +136,11 @@ class Pipeline:
     def run(self, batches: List[Batch]) -> None:
         m, n = len(batches), len(self.partitions)
         trackers = [SkipTrackerThroughPotals(self.skip_layout) for _ in batches]
+        # row counts of the micro-batches + a dict shared by the cells of this pass: a last-stage module may
+        # write its output straight into its slice of a mini-batch-wide buffer (microbatch.GatherBuffer)
+        sizes = [b[b.find_tensor_idx()].size(0) if b[b.find_tensor_idx()].dim() else 1 for b in batches]
+        shared: dict = {}
+        self._cells = [CellContext(i, sizes, shared) for i in range(m)]
         for tick in clock_cycles(m, n):
             self.fence(batches, tick, trackers)
             self.compute(batches, tick, trackers)
@@ -239,8 +244,10 @@ class Pipeline:
         timeline = self.timeline
         device = self.devices[j]
 
+        cell = self._cells[i] if i < len(getattr(self, "_cells", ())) else None
+
         def stage(*inputs):
-            with use_skip_tracker(tracker), _cell_range(label, device):
+            with use_skip_tracker(tracker), _cell_range(label, device), use_cell(cell):
                 return partition(*inputs)
 
         if checkpointed:

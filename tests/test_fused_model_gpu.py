@@ -330,3 +330,28 @@ def test_autograd_grad_does_not_see_weight_gradients():
     gx, gw = torch.autograd.grad(y.float().sum(), [x, layer.linear1.weight], allow_unused=True)
     wgrad.flush_pending()
     assert gx is not None and gw is None
+
+
+def test_logits_path_writes_into_one_buffer_and_gather_is_a_view():
+    """Without targets the fused decoder returns logits (reference main.py:55).  Inside Pipe every micro-batch
+    writes its logits into its slice of one mini-batch-wide buffer, so the gathered output aliases the first
+    micro-batch's memory (no cat), matches the eager model, and gradients still flow."""
+    from pipe_b200 import Pipe
+    from pipe_b200.models import build_stages
+    cfg = _tiny_cfg(0.0)
+    eager = build_stages(cfg, [0], impl="eager")
+    fused = build_stages(cfg, [0], impl="fused")
+    fused.load_state_dict(eager.state_dict())
+    tokens = torch.randint(0, cfg.ntokens, (cfg.batch, cfg.bptt), device=dev)
+    pipe = Pipe(fused, chunks=4, checkpoint="never")
+    out = pipe(tokens).local_value()
+    want = eager(tokens)
+    assert out.shape == want.shape == (cfg.batch, cfg.bptt, cfg.ntokens)
+    assert rel(out, want) < 3e-2
+    ld = (cfg.ntokens + 63) // 64 * 64
+    assert out.stride() == (cfg.bptt * ld, ld, 1)                 # rows of the padded shared buffer: a view, not a copy
+    out.float().sum().backward()
+    want.sum().backward()
+    for (name, pf), pr in zip(pipe.named_parameters(), eager.parameters()):
+        assert rel(pf.grad, pr.grad) < 8e-2, (name, rel(pf.grad, pr.grad))
+    pipe.close()
