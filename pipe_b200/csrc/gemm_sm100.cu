@@ -833,9 +833,35 @@ static int gemm_launch(const pb2_gemm_desc* d, float* partials, unsigned int* co
         bn = ((d->N + 15) / 16) * 16;
         if (bn > 256) bn = 256;
         if (d->N > 256) {
-            // balance the N tiles
-            int tiles = (d->N + 255) / 256;
-            bn = (((d->N + tiles - 1) / tiles) + 15) / 16 * 16;
+            // Pick the number of N tiles.  Widest tiles (256) are the most efficient per tile, but with one
+            // persistent CTA per SM the last round of tiles can leave most SMs idle: 48 x 4 = 192 tiles are two
+            // rounds on 148 SMs for the work of 1.3.  Cost model fitted to the 1024-token shapes of the
+            // reference-as-shipped configuration (scripts/bench_gemm.py, SWEEP=shipped): rounds x (tile width + 96);
+            // a narrower tile must promise > 8 % before it is taken (QKV forward 6144 x 1024 x 2048: 4 -> 6 N tiles,
+            // 29.1 -> 25.8 us; every other measured shape keeps 256).  Small problems with a short reduction
+            // (K <= 2048) that would otherwise run as <= 74 tiles x split-K take enough N tiles to fill the SMs
+            // instead (2048 x 1024 x 2048: 16.3 -> 14.7 us).
+            const int m_t = (d->M + kBlockM - 1) / kBlockM;
+            const int sms = sm_count();
+            const int nt_min = (d->N + 255) / 256, nt_max = (d->N + 127) / 128;
+            auto width = [&](int nt) { return (((d->N + nt - 1) / nt) + 15) / 16 * 16; };
+            int best_nt = nt_min;
+            if (static_cast<long long>(m_t) * nt_min > sms) {
+                auto cost = [&](int nt) {
+                    const long long tiles = static_cast<long long>(m_t) * nt;
+                    return static_cast<double>((tiles + sms - 1) / sms) * (width(nt) + 96);
+                };
+                const double base = cost(nt_min);
+                double best = base;
+                for (int nt = nt_min + 1; nt <= nt_max; ++nt) {
+                    if (width(nt) % 16) continue;
+                    const double c = cost(nt);
+                    if (c < best && c < 0.92 * base) { best = c; best_nt = nt; }
+                }
+            } else if (d->K <= 2048 && static_cast<long long>(m_t) * nt_min * 2 <= sms && d->splits <= 0) {
+                while (best_nt < nt_max && static_cast<long long>(m_t) * (best_nt + 1) <= sms) ++best_nt;
+            }
+            bn = width(best_nt);
         }
     }
     if (bn % 16 || bn < 16 || bn > 256) {

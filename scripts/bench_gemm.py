@@ -109,6 +109,14 @@ elif args.sweep and os.environ.get("SWEEP") == "persist":
         for pers in (2, 1):
             for stages in ((0, 3) if pers == 1 else (0, 4)):
                 case(nm, M, N, K, out_f32=f32, transpose=tr, persistent=pers, stages=stages)
+elif args.sweep and os.environ.get("SWEEP") == "shipped":
+    # reference-as-shipped shapes (E = 2048, 1024-token micro-batches, 4096-token mini-batch): N-tile width vs wave quantisation
+    E2, T2, TB = 2048, 1024, 4096
+    for (nm, M, N, K, f32, tr) in (("qkv fwd", 3 * E2, T2, E2, False, True), ("out-proj / ffn fwd", E2, T2, E2, False, True),
+                                   ("qkv dgrad", E2, T2, 3 * E2, False, True), ("wgrad 3ExE", 3 * E2, E2, TB, True, False),
+                                   ("wgrad ExE", E2, E2, TB, True, False), ("vocab fwd", V, T2, E2, False, True)):
+        for bn in (tuple(int(x) for x in os.environ['BNS'].split(',')) if os.environ.get('BNS') else (0, 256, 192, 128, 64)):
+            case(nm, M, N, K, out_f32=f32, transpose=tr, block_n=bn)
 elif args.sweep and os.environ.get("SWEEP") == "wgrad":
     for bn in (256, 128, 64):
         for stages in (0, 2, 4):
