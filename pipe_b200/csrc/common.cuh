@@ -69,6 +69,10 @@ EncodeTiledFn get_encode_tiled();
 int make_tmap_bf16_2d(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld_elems,
                       uint32_t box_rows, uint32_t box_cols);
 
+// 2-D fp32 row-major [rows, cols] tensor map with a [box_rows, box_cols <= 32] box and 128-byte swizzle (TMA stores).
+int make_tmap_f32_2d(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld_elems,
+                     uint32_t box_rows, uint32_t box_cols);
+
 // Raise a kernel's dynamic shared-memory limit once per (kernel, device, host thread).
 int ensure_max_smem(const void* func, int bytes);
 

@@ -80,6 +80,7 @@ struct GemmArgs {
     int cluster_reduce;              // splits CTAs of a tile form a cluster and reduce through DSMEM
     int local_chunks;                // 16-column chunks each cluster rank owns (ceil(n_chunks / splits))
     unsigned long long* debug_ts;    // optional: per-CTA phase timestamps (globaltimer ns), 8 per CTA
+    int tma_store;                   // persistent kernel: plain fp32 row-major result leaves through TMA stores
 };
 
 __device__ __forceinline__ unsigned long long gtime() {
@@ -608,6 +609,20 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
 // Tiles are walked M-fastest, so CTAs that run side by side share the same B tile in L2.
 //   acc_full[b]  : MMA warp -> epilogue   (tcgen05.commit)
 //   acc_empty[b] : epilogue -> MMA warp   (one arrival per epilogue warp)
+// ---- TMA store (shared -> global through a tensor map), bulk-group completion ----
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, const void* smem_src, int32_t c0, int32_t c1) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                 ::"l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1)
+                 : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
+constexpr int kStoreBufBytes = 32 * 128;            // one 32-row x 32-column fp32 block, 128-byte swizzled
+constexpr int kStoreBytes = kEpilogueWarps * 2 * kStoreBufBytes;     // two blocks per epilogue warp
+
 struct __align__(8) SmemCtlP {
     uint64_t full[kMaxStages];
     uint64_t empty[kMaxStages];
@@ -619,15 +634,19 @@ struct __align__(8) SmemCtlP {
 
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_bf16_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-                            const GemmArgs g, const int m_tiles, const int n_tiles) {
+                            const __grid_constant__ CUtensorMap tmap_out, const GemmArgs g, const int m_tiles,
+                            const int n_tiles) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     // carve: [stages][A 16 KB][B block_n*128 B], then 20 KB of epilogue staging, then the control block
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     const uint32_t a_bytes = kBlockM * kBlockK * 2;
     const uint32_t b_bytes = g.block_n * kBlockK * 2;
     const uint32_t stage_bytes = a_bytes + b_bytes;
+    // after the ring: the epilogue's staging area — 20 KB of padded rows for the register-store paths, or (tma_store)
+    // 64 KB of swizzled blocks that TMA reads; ring_bytes is a multiple of 1024, so the blocks are 1024-aligned
     float* staging = reinterpret_cast<float*>(smem + g.ring_bytes);
-    SmemCtlP* ctl = reinterpret_cast<SmemCtlP*>(smem + g.ring_bytes + kEpilogueWarps * 32 * kStagePitch * 4);
+    const uint32_t staging_bytes = g.tma_store ? kStoreBytes : kEpilogueWarps * 32 * kStagePitch * 4;
+    SmemCtlP* ctl = reinterpret_cast<SmemCtlP*>(smem + g.ring_bytes + staging_bytes);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -734,6 +753,7 @@ gemm_bf16_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
         const bool staged = !g.transpose_out && !g.relu && g.drop_p <= 0.f && !g.mask_src && !g.addend;
         float* st = staging + (warp - 2) * (32 * kStagePitch);
         float ss = 0.f;
+        int nb = 0;              // TMA-store blocks issued by this warp so far (alternates its two buffers across tiles too)
         for (int t = 0; t < my_tiles; ++t) {
             const int tile = blockIdx.x + t * gridDim.x;
             const int m0 = (tile % m_tiles) * kBlockM;
@@ -746,6 +766,45 @@ gemm_bf16_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
             mbar_wait(&ctl->acc_full[acc], (t >> 1) & 1);
             tc_fence_after();
             const uint32_t t_lane = tmem_base + acc * acc_stride + (static_cast<uint32_t>(quarter * 32) << 16);
+            if (g.tma_store) {
+                // Plain fp32 row-major result (the weight gradients: 128 KB per tile, the kernel's main cost): the warp
+                // parks a 32-row x 32-column block in shared memory (128-byte rows, TMA's swizzle) and one lane hands it
+                // to the TMA unit, which writes whole lines and clips at the matrix edge; two blocks per warp in flight.
+                // ~10x fewer instructions than register stores: the epilogue no longer sets the pace of the tile.
+                uint8_t* bufs = reinterpret_cast<uint8_t*>(staging) + (warp - 2) * (2 * kStoreBufBytes);
+                for (int c = half * 32; c < g.block_n; c += 64, ++nb) {
+                    uint32_t r[32];
+                    tmem_ld_32x32(t_lane + c, r);
+                    tmem_ld_wait();
+                    uint8_t* buf = bufs + (nb & 1) * kStoreBufBytes;
+                    if (lane == 0) tma_store_wait_read<1>();        // the block stored two rounds ago has been read
+                    __syncwarp();
+                    if (n0 + c < g.N) {
+                        float v[32];
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * g.alpha;
+                        if (g.sumsq && m_glob < g.M) {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j)
+                                if (n0 + c + j < g.N) ss += v[j] * v[j];
+                        }
+#pragma unroll
+                        for (int j = 0; j < 8; ++j)
+                            *reinterpret_cast<float4*>(buf + lane * 128 + ((j ^ (lane & 7)) << 4)) =
+                                make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+                        fence_proxy_async();
+                        __syncwarp();
+                        if (lane == 0) {
+                            tma_store_2d(&tmap_out, buf, n0 + c, m0 + quarter * 32);
+                            tma_store_commit();
+                        }
+                    }
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&ctl->acc_empty[acc]);
+                continue;
+            }
             for (int c = half * 16; c < g.block_n; c += 32) {
                 uint32_t r[16];
                 tmem_ld_32x16(t_lane + c, r);
@@ -768,6 +827,7 @@ gemm_bf16_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
             ss = warp_sum(ss);
             if (lane == 0) atomicAdd(g.sumsq, ss);
         }
+        if (g.tma_store && lane == 0) tma_store_wait_all();          // the bulk stores must land before the CTA exits
         tc_fence_before();
     }
 
@@ -968,11 +1028,32 @@ static int gemm_launch(const pb2_gemm_desc* d, float* partials, unsigned int* co
         // a 3-stage ring than with 4 (27.3 vs 28.7 us, 67.2 vs 70.4 us); long ones want the deepest ring
         if (d->stages <= 0 && g.k_blocks_total <= 8 && pst > 3) pst = 3;
         if (pst >= 2 && 2 * bn <= 512) {
+            // plain fp32 row-major results (the weight gradients) leave through TMA stores
+            static int tma_store_off = -1;
+            if (tma_store_off < 0) {
+                const char* e = getenv("PB2_GEMM_TMA_STORE");
+                tma_store_off = (e && e[0] == '0') ? 1 : 0;
+            }
+            CUtensorMap tout = ta;          // placeholder when unused
+            g.tma_store = (!tma_store_off && d->out_f32 && !d->transpose_out && !d->accumulate && !d->relu && d->drop_p <= 0.f &&
+                           !d->mask_src && !d->addend && !d->bias && (d->ld_out % 4) == 0 && bn % 32 == 0 &&
+                           (reinterpret_cast<uintptr_t>(d->out) & 15) == 0) ? 1 : 0;
+            size_t staging_bytes = kEpilogueWarps * 32 * kStagePitch * 4;
+            if (g.tma_store) {
+                staging_bytes = kStoreBytes;
+                while (pst > 2 && static_cast<size_t>(pst) * stage_bytes + staging_bytes + sizeof(SmemCtlP) + 1024 > 227 * 1024) --pst;
+                if (static_cast<size_t>(pst) * stage_bytes + staging_bytes + sizeof(SmemCtlP) + 1024 > 227 * 1024) g.tma_store = 0;
+            }
+            if (g.tma_store) {
+                if (make_tmap_f32_2d(&tout, d->out, d->M, d->N, d->ld_out, 32, 32)) return -1;
+            } else {
+                staging_bytes = kEpilogueWarps * 32 * kStagePitch * 4;
+            }
             g.stages = pst;
             g.ring_bytes = pst * stage_bytes;
             g.tmem_cols = next_pow2_cols(2 * bn);
             g.debug_ts = nullptr;
-            const size_t smem_p = static_cast<size_t>(g.ring_bytes) + kEpilogueWarps * 32 * kStagePitch * 4 + sizeof(SmemCtlP) + 1024;
+            const size_t smem_p = static_cast<size_t>(g.ring_bytes) + staging_bytes + sizeof(SmemCtlP) + 1024;
             if (ensure_max_smem(reinterpret_cast<const void*>(gemm_bf16_persistent_kernel), 227 * 1024)) return -1;
             cudaLaunchConfig_t pc;
             memset(&pc, 0, sizeof(pc));
@@ -985,7 +1066,7 @@ static int gemm_launch(const pb2_gemm_desc* d, float* partials, unsigned int* co
             pa[0].val.programmaticStreamSerializationAllowed = 1;
             pc.attrs = pa;
             pc.numAttrs = 1;
-            PB2_CUDA(cudaLaunchKernelEx(&pc, gemm_bf16_persistent_kernel, ta, tb, g, m_tiles, n_tiles));
+            PB2_CUDA(cudaLaunchKernelEx(&pc, gemm_bf16_persistent_kernel, ta, tb, tout, g, m_tiles, n_tiles));
             PB2_LAUNCHED("gemm_bf16_persistent_kernel");
             return 0;
         }

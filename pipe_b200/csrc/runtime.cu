@@ -96,6 +96,36 @@ int make_tmap_bf16_2d(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t
     return 0;
 }
 
+int make_tmap_f32_2d(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld_elems,
+                     uint32_t box_rows, uint32_t box_cols) {
+    // same direct-mapped cache as the bf16 maps; the element size is folded into the key through ld (in bytes) | 1
+    if (!t_tmap_cache) t_tmap_cache = new TmapSlot[kTmapSlots]();
+    const TmapKey key{ptr, rows, cols, (ld_elems * 4) | 1, box_rows, box_cols};
+    TmapSlot& slot = t_tmap_cache[tmap_hash(key)];
+    if (slot.valid && slot.key == key) {
+        *out = slot.map;
+        return 0;
+    }
+    EncodeTiledFn enc = get_encode_tiled();
+    if (!enc) return -1;
+    cuuint64_t dims[2] = {cols, rows};
+    cuuint64_t strides[1] = {ld_elems * 4};
+    cuuint32_t box[2] = {box_cols, box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled (fp32) failed (%d) for [%llu x %llu] ld %llu box [%u x %u]", static_cast<int>(r),
+                  (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)ld_elems, box_rows, box_cols);
+        return -1;
+    }
+    slot.key = key;
+    slot.map = *out;
+    slot.valid = true;
+    return 0;
+}
+
 // cudaFuncSetAttribute(max dynamic smem) once per (kernel, device) instead of once per launch.
 // One timing-less event per device is enough for record-then-wait pairs: cudaStreamWaitEvent captures the
 // work recorded by the most recent cudaEventRecord at the time of the call, later records do not disturb it.
