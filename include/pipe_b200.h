@@ -113,6 +113,18 @@ int pb2_embed_fwd(const long long* tokens, const float* weight, const float* pe,
 int pb2_embed_bwd(const long long* tokens, const void* dout, float* dweight, int N, int S, int E, float scale,
                   float drop_p, unsigned long long seed, unsigned long long rng_stream, cudaStream_t stream);
 
+/* Embedding gradient of a data-parallel hybrid, exchanged as operands instead of all-reduced as a dense V x E matrix.
+ * pb2_embed_pack: row r of a micro-batch = dout[r] * scale * dropout mask (the mask of pb2_embed_fwd for the same seed /
+ * stream) as fp32 into rows[r], its token id into toks[r], and the same values at the same addresses + peer_delta[q]
+ * (this replica's region of the stash in every replica's memory).  pb2_embed_scatter: over R stash slots (toks < 0 =
+ * unused), dweight[token] += alpha * (sum of all rows with that token, in slot order), one writer per token — the same
+ * bits on every replica.  Reference counterpart: nn.Embedding's backward (main.py:28) under DDP (pipe.py:290-293). */
+int pb2_embed_pack(const long long* tokens, const void* dout, float* rows, long long* toks, int N, int S, int E,
+                   float scale, float drop_p, unsigned long long seed, unsigned long long rng_stream, int n_peers,
+                   const long long* peer_delta, cudaStream_t stream);
+int pb2_embed_scatter(const long long* toks, const float* rows, float* dweight, int R, int E, float alpha,
+                      cudaStream_t stream);
+
 /* ---- softmax cross-entropy over bf16 logits [rows, ld] with V valid columns ----------------
  * loss_rows[r] = logsumexp - logit[target] (loss_rows may be NULL); with write_grad the logits are
  * overwritten by (softmax - onehot) * row_scale[r] (row_scale may be NULL = 1; pad columns zeroed),

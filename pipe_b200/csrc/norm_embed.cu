@@ -279,6 +279,93 @@ embed_bwd_kernel(const long long* __restrict__ tokens, const __nv_bfloat16* __re
 }
 
 // ---------------------------------------------------------------------------------
+// Embedding gradient of a data-parallel hybrid, exchanged as operands.  The dense gradient is V x E fp32 (472 MB
+// at V = 28782, E = 4096) of which at most `tokens` rows are non-zero, so the replicas do not all-reduce it:
+//   embed_pack:    row r of this micro-batch = dout[r] * scale * dropout mask, as fp32, plus its token id, stored into
+//                  this replica's region of a stash in EVERY replica's memory (peer-mapped stores, like the wgrad stash)
+//   embed_scatter: after the group barrier every replica holds all replicas' rows at the same slots; one CTA per slot
+//                  that is the FIRST occurrence of its token adds up all slots with that token in slot order and writes
+//                  alpha * sum into dweight[token].  One writer per token, fixed order: no atomics, and every replica
+//                  computes bit-identical gradients.
+// ---------------------------------------------------------------------------------
+struct EmbedPackArgs {
+    const long long* tokens;       // [N, S]
+    const __nv_bfloat16* dout;     // [S * N, E]
+    float* rows;                   // stash rows of this micro-batch: [S * N, E] fp32 (local address)
+    long long* toks;               // stash token ids of this micro-batch (local address)
+    int N, S, E;
+    float scale, drop_p;
+    unsigned long long seed, rng_stream;
+    int n_peers;
+    long long peer_delta[PB2_MAX_PEERS];
+};
+
+__global__ void __launch_bounds__(256)
+embed_pack_kernel(const EmbedPackArgs a) {
+    pdl_launch_dependents();
+    pdl_wait();
+    const int row = blockIdx.x;
+    const int s = row / a.N, n = row % a.N;
+    const long long tok = a.tokens[static_cast<size_t>(n) * a.S + s];
+    const CounterRng ph(a.seed);
+    const uint32_t thr = static_cast<uint32_t>(fminf(a.drop_p, 0.999999f) * 4294967296.0f);
+    const float k = a.scale * (a.drop_p > 0.f ? 1.f / (1.f - a.drop_p) : 1.f);
+    if (threadIdx.x == 0) {
+        a.toks[row] = tok;
+        for (int q = 0; q < a.n_peers; ++q)
+            *reinterpret_cast<long long*>(reinterpret_cast<char*>(a.toks + row) + a.peer_delta[q]) = tok;
+    }
+    for (int c = threadIdx.x * 4; c < a.E; c += blockDim.x * 4) {
+        const __nv_bfloat162* d = reinterpret_cast<const __nv_bfloat162*>(a.dout + static_cast<size_t>(row) * a.E + c);
+        const float2 d0 = __bfloat1622float2(d[0]), d1 = __bfloat1622float2(d[1]);
+        float v[4] = {d0.x * k, d0.y * k, d1.x * k, d1.y * k};
+        if (a.drop_p > 0.f) {
+            const uint64_t idx = static_cast<uint64_t>(row) * a.E + c;
+            const uint4 r = ph(idx >> 2, a.rng_stream);
+            if (r.x < thr) v[0] = 0.f;
+            if (r.y < thr) v[1] = 0.f;
+            if (r.z < thr) v[2] = 0.f;
+            if (r.w < thr) v[3] = 0.f;
+        }
+        float* dst = a.rows + static_cast<size_t>(row) * a.E + c;
+        const float4 out = make_float4(v[0], v[1], v[2], v[3]);
+        *reinterpret_cast<float4*>(dst) = out;
+        for (int q = 0; q < a.n_peers; ++q)
+            *reinterpret_cast<float4*>(reinterpret_cast<char*>(dst) + a.peer_delta[q]) = out;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+embed_scatter_kernel(const long long* __restrict__ toks, const float* __restrict__ rows, float* __restrict__ dweight,
+                     int R, int E, float alpha) {
+    pdl_launch_dependents();
+    pdl_wait();
+    const int r = blockIdx.x;
+    const long long tok = toks[r];
+    if (tok < 0) return;                                   // unused slot
+    // not the first slot with this token: an earlier CTA owns the sum
+    __shared__ int earlier;
+    if (threadIdx.x == 0) earlier = 0;
+    __syncthreads();
+    for (int i = threadIdx.x; i < r; i += blockDim.x)
+        if (toks[i] == tok) earlier = 1;
+    __syncthreads();
+    if (earlier) return;
+    for (int c = threadIdx.x * 4; c < E; c += blockDim.x * 4) {
+        float4 acc = *reinterpret_cast<const float4*>(rows + static_cast<size_t>(r) * E + c);
+        for (int i = r + 1; i < R; ++i) {
+            if (toks[i] != tok) continue;                  // uniform across the CTA
+            const float4 v = *reinterpret_cast<const float4*>(rows + static_cast<size_t>(i) * E + c);
+            acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+        }
+        float4* dw = reinterpret_cast<float4*>(dweight + static_cast<size_t>(tok) * E + c);
+        float4 old = *dw;
+        old.x += acc.x * alpha; old.y += acc.y * alpha; old.z += acc.z * alpha; old.w += acc.w * alpha;
+        *dw = old;
+    }
+}
+
+// ---------------------------------------------------------------------------------
 // softmax cross-entropy over bf16 logits [T, ld] (V valid columns).  One CTA per row:
 //   loss[row] = logsumexp(l) - l[target];   logits <- softmax(l) - onehot(target)   (in place)
 // ---------------------------------------------------------------------------------
@@ -564,6 +651,32 @@ extern "C" int pb2_embed_bwd(const long long* tokens, const void* dout, float* d
     PB2_CUDA(launch_pdl(embed_bwd_kernel, dim3(N * S), dim3(256), 0, stream, tokens, static_cast<const __nv_bfloat16*>(dout), dweight, N, S, E,
                                                 scale, drop_p, seed, rng_stream));
     PB2_LAUNCHED("embed_bwd_kernel");
+    return 0;
+}
+
+extern "C" int pb2_embed_pack(const long long* tokens, const void* dout, float* rows, long long* toks, int N, int S, int E,
+                              float scale, float drop_p, unsigned long long seed, unsigned long long rng_stream, int n_peers,
+                              const long long* peer_delta, cudaStream_t stream) {
+    if (E % 4) { set_error("pb2_embed_pack: E must be a multiple of 4"); return -1; }
+    if (n_peers < 0 || n_peers > PB2_MAX_PEERS) { set_error("pb2_embed_pack: n_peers %d out of range", n_peers); return -1; }
+    if (N * S <= 0) return 0;
+    EmbedPackArgs a;
+    memset(&a, 0, sizeof(a));
+    a.tokens = tokens; a.dout = static_cast<const __nv_bfloat16*>(dout); a.rows = rows; a.toks = toks;
+    a.N = N; a.S = S; a.E = E; a.scale = scale; a.drop_p = drop_p; a.seed = seed; a.rng_stream = rng_stream;
+    a.n_peers = n_peers;
+    for (int q = 0; q < n_peers; ++q) a.peer_delta[q] = peer_delta[q];
+    PB2_CUDA(launch_pdl(embed_pack_kernel, dim3(N * S), dim3(256), 0, stream, a));
+    PB2_LAUNCHED("embed_pack_kernel");
+    return 0;
+}
+
+extern "C" int pb2_embed_scatter(const long long* toks, const float* rows, float* dweight, int R, int E, float alpha,
+                                 cudaStream_t stream) {
+    if (E % 4) { set_error("pb2_embed_scatter: E must be a multiple of 4"); return -1; }
+    if (R <= 0) return 0;
+    PB2_CUDA(launch_pdl(embed_scatter_kernel, dim3(R), dim3(256), 0, stream, toks, rows, dweight, R, E, alpha));
+    PB2_LAUNCHED("embed_scatter_kernel");
     return 0;
 }
 

@@ -589,7 +589,12 @@ class _EmbedFn(torch.autograd.Function):
         d = dout.contiguous()
         if d.dtype != torch.bfloat16:
             d = d.to(torch.bfloat16)
-        F2.embed_bwd(tokens, d, ensure_grad(module.encoder.weight), math.sqrt(module.ninp), p, seed, 0)
+        stash = module.__dict__.get("_pb2_embed_stash")
+        if stash is not None:
+            # data-parallel hybrid: the rows go to every replica's stash; the table gradient is formed at flush time
+            stash.pack(tokens, d, math.sqrt(module.ninp), p, seed, 0)
+        else:
+            F2.embed_bwd(tokens, d, ensure_grad(module.encoder.weight), math.sqrt(module.ninp), p, seed, 0)
         return None, None, None
 
 
@@ -616,6 +621,10 @@ class FusedEncoder(nn.Module):
         self.ninp = ninp
         self.dropout = float(dropout)
         nn.init.uniform_(self.encoder.weight, -0.1, 0.1)
+
+    def pb2_embed_weight(self) -> nn.Parameter:
+        """The table whose gradient a data-parallel hybrid may exchange row-wise (parallel/replica_stash.py)."""
+        return self.encoder.weight
 
     def forward(self, src: Tensor, *extra: Any):
         if src.size(1) > self.pos_encoder.pe.size(0):

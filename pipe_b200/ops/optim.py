@@ -129,12 +129,26 @@ class FusedClipAdam:
         hybrid = self.replicas > 1
         if hybrid and len(self.devs) != 1:
             raise ValueError("replicated (hybrid) mode expects one stage = one device per rank")
+        # gather backend: embedding tables exchange their gradient rows instead of all-reducing V x E floats
+        embed_mods = [sub for sub in module.modules() if hasattr(sub, "pb2_embed_weight")] \
+            if hybrid and self.reduce_backend == "gather" else []
+        exchanged = {id(m.pb2_embed_weight()) for m in embed_mods}
         # dense: every gradient of the stage in one flat buffer [matrices | small], reduced bucket by bucket
         dense = hybrid and self.reduce_backend in ("allreduce", "nccl")
         pad = 32                       # bucket granularity: a multiple of 4 * world for every world <= 8
         for st in self.devs.values():
-            small = [p for p in st.params if id(p) not in gemm_written]
+            small = [p for p in st.params if id(p) not in gemm_written and id(p) not in exchanged]
+            local = [p for p in st.params if id(p) in exchanged]
             big = [p for p in st.params if id(p) in gemm_written]
+            st.flat_local = None
+            if local:
+                # gradients this rank forms itself, already averaged (EmbedStash.scatter adds into them): zeroed per step
+                st.flat_local = torch.zeros(sum((p.numel() + pad - 1) // pad * pad for p in local), dtype=torch.float32,
+                                            device=st.device)
+                at = 0
+                for p in local:
+                    p.grad = st.flat_local[at:at + p.numel()].view_as(p)
+                    at += (p.numel() + pad - 1) // pad * pad
             n_small = max(sum((p.numel() + pad - 1) // pad * pad for p in small), pad)
             n_big = sum((p.numel() + pad - 1) // pad * pad for p in big) if dense else 0
             st.symm = None
@@ -197,7 +211,7 @@ class FusedClipAdam:
                 if max_tokens <= 0:
                     raise ValueError("reduce_backend='gather' needs max_tokens (tokens a replica stacks per step)")
                 from ..parallel.replica_stash import ReplicaStash
-                self._stash = ReplicaStash(lgs, self.replica_group, st.device, max_tokens)
+                self._stash = ReplicaStash(lgs, self.replica_group, st.device, max_tokens, embeddings=embed_mods)
             else:
                 for lg in lgs:
                     lg.on_flushed = self._bucket_ready
@@ -213,6 +227,8 @@ class FusedClipAdam:
             return
         for st in self.devs.values():
             st.flat_small.zero_()
+            if getattr(st, "flat_local", None) is not None:
+                st.flat_local.zero_()
             st.normsq.zero_()
             for p in st.params:
                 if id(p) in self._gemm_written:
@@ -270,6 +286,8 @@ class FusedClipAdam:
         if self.reduce_backend == "gather":
             # matrices: summed into st.normsq by the wgrad epilogues (identical on every replica)
             F2.sumsq(st.flat_small, st.normsq)
+            if st.flat_local is not None:
+                F2.sumsq(st.flat_local, st.normsq)
             for p in st.params:
                 if id(p) in self._gemm_written and not getattr(p, "_pb2_sumsq_done", False):
                     F2.sumsq(p.grad.view(-1), st.normsq)

@@ -34,11 +34,75 @@ from ..ops import wgrad
 from ..ops.wgrad import LinearGrad
 from .symmetric import SymmetricBuffer
 
-__all__ = ["ReplicaStash"]
+__all__ = ["ReplicaStash", "EmbedStash"]
 
 
 def _round_up(x: int, m: int) -> int:
     return (x + m - 1) // m * m
+
+
+class EmbedStash:
+    """The same idea for an embedding table: its dense gradient is ``V x E`` fp32 of which at most ``tokens`` rows are
+    non-zero, so the replicas exchange the rows (already scaled and dropout-masked, fp32) and their token ids; after the
+    barrier every replica sums them per token in a fixed order (``pb2_embed_scatter``: one writer per token, no
+    atomics), which keeps the replicas bit-identical.  472 MB of all-reduce become ``2 x tokens x E x 4`` bytes."""
+
+    def __init__(self, weight: torch.nn.Parameter, group: dist.ProcessGroup, device: torch.device, max_tokens: int) -> None:
+        self.weight = weight
+        self.replicas = dist.get_world_size(group)
+        self.replica = dist.get_rank(group)
+        self.cap = _round_up(max(int(max_tokens), 8), 8)
+        self.E = weight.size(1)
+        slots = self.replicas * self.cap
+        self.buf = SymmetricBuffer(slots * self.E + 2 * slots, group, torch.device(device))
+        if self.buf.mode == "torch":
+            raise RuntimeError("peer-mapped memory is not available for this replica group")
+        self.rows = self.buf.data[: slots * self.E].view(slots, self.E)
+        self.toks = self.buf.data[slots * self.E: slots * self.E + 2 * slots].view(torch.int64)
+        self.toks.fill_(-1)
+        me = self.buf.peer_data[self.replica]
+        self.deltas = [p - me for q, p in enumerate(self.buf.peer_data) if q != self.replica]
+        self.used = 0
+        torch.cuda.synchronize(device)
+        dist.barrier(group=group)
+
+    def pack(self, tokens: torch.Tensor, dout: torch.Tensor, scale: float, drop_p: float, seed: int, rng_stream: int) -> None:
+        """Called by the embedding's backward for one micro-batch (``tokens [N, S]``, ``dout [S, N, E]`` bf16)."""
+        import ctypes
+
+        from ..ops import _lib
+        N, S = tokens.shape
+        T = N * S
+        if self.used + T > self.cap:
+            raise RuntimeError(f"embedding stash holds {self.cap} tokens per step and replica: raise max_tokens")
+        off = self.replica * self.cap + self.used
+        self.used += T
+        arr = (ctypes.c_longlong * max(len(self.deltas), 1))(*self.deltas)
+        with _lib.on_device(dout.device):
+            rc = _lib.load().pb2_embed_pack(
+                ctypes.c_void_p(tokens.data_ptr()), ctypes.c_void_p(dout.data_ptr()),
+                ctypes.c_void_p(self.rows[off].data_ptr()), ctypes.c_void_p(self.toks[off:].data_ptr()),
+                ctypes.c_int(N), ctypes.c_int(S), ctypes.c_int(self.E), ctypes.c_float(scale), ctypes.c_float(drop_p),
+                ctypes.c_ulonglong(seed), ctypes.c_ulonglong(rng_stream), ctypes.c_int(len(self.deltas)), arr,
+                _lib.stream_ptr(dout.device))
+        _lib.check(rc, "pb2_embed_pack")
+
+    def scatter(self, stream: int) -> None:
+        """After the group barrier: every replica's rows are here; add them up into ``weight.grad`` (mean over replicas)."""
+        import ctypes
+
+        from ..ops import _lib
+        from ..ops.wgrad import ensure_grad
+        grad = ensure_grad(self.weight)
+        dev = self.rows.device
+        with _lib.on_device(dev):
+            rc = _lib.load().pb2_embed_scatter(ctypes.c_void_p(self.toks.data_ptr()), ctypes.c_void_p(self.rows.data_ptr()),
+                                               ctypes.c_void_p(grad.data_ptr()), ctypes.c_int(self.toks.numel()),
+                                               ctypes.c_int(self.E), ctypes.c_float(1.0 / self.replicas), ctypes.c_void_p(stream))
+        _lib.check(rc, "pb2_embed_scatter")
+        with torch.cuda.stream(torch.cuda.ExternalStream(stream, device=dev)):
+            self.toks.fill_(-1)            # slots a shorter next step leaves unused must read "empty"
+        self.used = 0
 
 
 class ReplicaStash:
@@ -52,7 +116,9 @@ class ReplicaStash:
     """
 
     def __init__(self, lgs: Sequence[LinearGrad], group: dist.ProcessGroup, device: torch.device,
-                 max_tokens: int) -> None:
+                 max_tokens: int, embeddings: Sequence[torch.nn.Module] = ()) -> None:
+        """``embeddings``: modules with ``pb2_embed_weight()`` (the fused encoder) whose table gradient is exchanged
+        row-wise (:class:`EmbedStash`) instead of all-reduced."""
         self.lgs: List[LinearGrad] = list(lgs)
         self.group = group
         self.device = torch.device(device)
@@ -78,6 +144,12 @@ class ReplicaStash:
         self.bytes_pushed_per_token = sum((lg.weight.size(0) + lg.weight.size(1)) * 2 for lg in self.lgs) \
             * (self.replicas - 1)
         self._mine = {id(lg) for lg in self.lgs}
+        self.embed_stashes: List[EmbedStash] = []
+        for mod in embeddings:
+            es = EmbedStash(mod.pb2_embed_weight(), group, self.device, max_tokens)
+            mod.__dict__["_pb2_embed_stash"] = es
+            self.embed_stashes.append(es)
+        self._embed_modules = list(embeddings)
         wgrad.pre_flush_hooks.append(self._before_gemms)
         wgrad.post_flush_hooks.append(self._after_gemms)
 
@@ -91,7 +163,10 @@ class ReplicaStash:
     def _before_gemms(self, todo) -> None:
         """All replicas' operand stores have landed before any wgrad GEMM reads them."""
         if any(id(lg) in self._mine for lg in todo):
-            self.buf.barrier(phase=0, stream=self._stream_of(todo))
+            stream = self._stream_of(todo)
+            self.buf.barrier(phase=0, stream=stream)
+            for es in self.embed_stashes:
+                es.scatter(stream)
 
     def _after_gemms(self, todo) -> None:
         """Nobody starts overwriting the stash (next step's backward) while a peer's GEMMs still read it."""
@@ -99,6 +174,8 @@ class ReplicaStash:
             self.buf.barrier(phase=1, stream=self._stream_of(todo))
 
     def close(self) -> None:
+        for mod in self._embed_modules:
+            mod.__dict__.pop("_pb2_embed_stash", None)
         for hooks, fn in ((wgrad.pre_flush_hooks, self._before_gemms), (wgrad.post_flush_hooks, self._after_gemms)):
             if fn in hooks:
                 hooks.remove(fn)
