@@ -118,12 +118,12 @@ int pb2_embed_bwd(const long long* tokens, const void* dout, float* dweight, int
  * stream) as fp32 into rows[r], its token id into toks[r], and the same values at the same addresses + peer_delta[q]
  * (this replica's region of the stash in every replica's memory).  pb2_embed_scatter: over R stash slots (toks < 0 =
  * unused), dweight[token] += alpha * (sum of all rows with that token, in slot order), one writer per token — the same
- * bits on every replica.  Reference counterpart: nn.Embedding's backward (main.py:28) under DDP (pipe.py:290-293). */
+ * bits on every replica; reset_slots = 1 marks every slot unused again afterwards (on `stream`).  Reference counterpart: nn.Embedding's backward (main.py:28) under DDP (pipe.py:290-293). */
 int pb2_embed_pack(const long long* tokens, const void* dout, float* rows, long long* toks, int N, int S, int E,
                    float scale, float drop_p, unsigned long long seed, unsigned long long rng_stream, int n_peers,
                    const long long* peer_delta, cudaStream_t stream);
-int pb2_embed_scatter(const long long* toks, const float* rows, float* dweight, int R, int E, float alpha,
-                      cudaStream_t stream);
+int pb2_embed_scatter(long long* toks, const float* rows, float* dweight, int R, int E, float alpha,
+                      int reset_slots, cudaStream_t stream);
 
 /* ---- softmax cross-entropy over bf16 logits [rows, ld] with V valid columns ----------------
  * loss_rows[r] = logsumexp - logit[target] (loss_rows may be NULL); with write_grad the logits are
@@ -379,6 +379,9 @@ size_t pb2_encoder_stack_tmp_elems(const pb2_encoder_layer* layers, int n, int T
 size_t pb2_encoder_stack_stats_floats(const pb2_encoder_layer* layers, int n, int S, int T);
 int pb2_encoder_stack_fwd(const pb2_encoder_stack* s, cudaStream_t stream);
 int pb2_encoder_stack_bwd(const pb2_encoder_stack* s, cudaStream_t stream);
+
+/* cudaMemset2DAsync on `stream`: `height` rows of `width` bytes, `pitch` bytes apart, set to `value`. */
+int pb2_memset2d(void* ptr, size_t pitch, int value, size_t width, size_t height, cudaStream_t stream);
 
 /* `waiter` waits (on the device) for everything enqueued on `waited` so far; both on the current device. */
 int pb2_stream_wait_stream(cudaStream_t waiter, cudaStream_t waited);

@@ -12,6 +12,8 @@
 // Reference counterparts: ATen dropout + add + native_layer_norm (nn.TransformerEncoderLayer,
 // main.py:148), nn.Embedding + PositionalEncoding (main.py:24-40,57-73), nn.CrossEntropyLoss
 // (main.py:182,217).  SURVEY.md K1, K5, K9.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "pipe_b200.h"
 
@@ -333,29 +335,42 @@ embed_pack_kernel(const EmbedPackArgs a) {
         for (int q = 0; q < a.n_peers; ++q)
             *reinterpret_cast<float4*>(reinterpret_cast<char*>(dst) + a.peer_delta[q]) = out;
     }
+    // see transpose_multi_kernel: the peer stores must have been performed when this grid retires
+    if (a.n_peers > 0) __threadfence_system();
+}
+
+// system-scope loads: the stash was written by other GPUs; these reads must observe what the flag exchange ordered
+__device__ __forceinline__ long long ld_sys_s64(const long long* p) {
+    long long v;
+    asm volatile("ld.relaxed.sys.global.s64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ float4 ld_sys_f32x4(const float* p) {
+    float4 v;
+    asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+    return v;
 }
 
 __global__ void __launch_bounds__(256)
-embed_scatter_kernel(const long long* __restrict__ toks, const float* __restrict__ rows, float* __restrict__ dweight,
-                     int R, int E, float alpha) {
+embed_scatter_kernel(const long long* toks, const float* rows, float* __restrict__ dweight, int R, int E, float alpha) {
     pdl_launch_dependents();
     pdl_wait();
     const int r = blockIdx.x;
-    const long long tok = toks[r];
+    const long long tok = ld_sys_s64(toks + r);
     if (tok < 0) return;                                   // unused slot
     // not the first slot with this token: an earlier CTA owns the sum
     __shared__ int earlier;
     if (threadIdx.x == 0) earlier = 0;
     __syncthreads();
     for (int i = threadIdx.x; i < r; i += blockDim.x)
-        if (toks[i] == tok) earlier = 1;
+        if (ld_sys_s64(toks + i) == tok) earlier = 1;
     __syncthreads();
     if (earlier) return;
     for (int c = threadIdx.x * 4; c < E; c += blockDim.x * 4) {
-        float4 acc = *reinterpret_cast<const float4*>(rows + static_cast<size_t>(r) * E + c);
+        float4 acc = ld_sys_f32x4(rows + static_cast<size_t>(r) * E + c);
         for (int i = r + 1; i < R; ++i) {
-            if (toks[i] != tok) continue;                  // uniform across the CTA
-            const float4 v = *reinterpret_cast<const float4*>(rows + static_cast<size_t>(i) * E + c);
+            if (ld_sys_s64(toks + i) != tok) continue;     // uniform across the CTA
+            const float4 v = ld_sys_f32x4(rows + static_cast<size_t>(i) * E + c);
             acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
         }
         float4* dw = reinterpret_cast<float4*>(dweight + static_cast<size_t>(tok) * E + c);
@@ -556,6 +571,10 @@ transpose_multi_kernel(const pb2_transpose_jobs jobs) {
             atomicAdd(j.colsum + c0 + tx, t * j.scale);
         }
     }
+    // Stores into a peer's memory are posted: the grid can retire while they are still on their way, and a flag raised
+    // by a LATER kernel (pb2_group_barrier) may then overtake them on another NVLink lane.  A system-scope fence by the
+    // storing thread itself makes "this kernel has completed" imply "its peer stores have been performed".
+    if (jobs.n_peers > 0) __threadfence_system();
 }
 
 // Fire-and-forget L2 prefetch of a byte range: each thread asks the memory system for one 16 KB
@@ -671,12 +690,13 @@ extern "C" int pb2_embed_pack(const long long* tokens, const void* dout, float* 
     return 0;
 }
 
-extern "C" int pb2_embed_scatter(const long long* toks, const float* rows, float* dweight, int R, int E, float alpha,
-                                 cudaStream_t stream) {
+extern "C" int pb2_embed_scatter(long long* toks, const float* rows, float* dweight, int R, int E, float alpha,
+                                 int reset_slots, cudaStream_t stream) {
     if (E % 4) { set_error("pb2_embed_scatter: E must be a multiple of 4"); return -1; }
     if (R <= 0) return 0;
     PB2_CUDA(launch_pdl(embed_scatter_kernel, dim3(R), dim3(256), 0, stream, toks, rows, dweight, R, E, alpha));
     PB2_LAUNCHED("embed_scatter_kernel");
+    if (reset_slots) PB2_CUDA(cudaMemsetAsync(toks, 0xFF, static_cast<size_t>(R) * sizeof(long long), stream));   // all slots "empty" (-1)
     return 0;
 }
 

@@ -177,3 +177,12 @@ extern "C" int pb2_version(void) { return 1; }
 extern "C" int pb2_stream_wait_stream(cudaStream_t waiter, cudaStream_t waited) {
     return pb2::record_and_wait(waited, waiter);
 }
+
+// Strided fill on a raw stream (rows of `width` bytes, `pitch` bytes apart): the Python layer uses it where a region has
+// to be cleared on exactly the stream a kernel was launched on (a torch op under an ExternalStream wrapper of the legacy
+// default stream is NOT ordered with torch's own default stream).
+extern "C" int pb2_memset2d(void* ptr, size_t pitch, int value, size_t width, size_t height, cudaStream_t stream) {
+    if (!ptr || width == 0 || height == 0) return 0;
+    PB2_CUDA(cudaMemset2DAsync(ptr, pitch, value, width, height, stream));
+    return 0;
+}

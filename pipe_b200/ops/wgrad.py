@@ -194,10 +194,15 @@ class LinearGrad:
             cap, k = self.rep
             if self.used < self.high:
                 # a shorter step than before: stale columns of every replica's region would be summed in
-                with torch.cuda.stream(torch.cuda.ExternalStream(self.stream, device=self.xt.device)):
-                    for r in range(k):
-                        self.xt[:, r * cap + self.used: r * cap + self.high].zero_()
-                        self.dyt[:, r * cap + self.used: r * cap + self.high].zero_()
+                lib = _lib.load()
+                with _lib.on_device(self.xt.device):
+                    for t in (self.xt, self.dyt):
+                        for r in range(k):
+                            part = t[:, r * cap + self.used: r * cap + self.high]
+                            rc = lib.pb2_memset2d(ctypes.c_void_p(part.data_ptr()), ctypes.c_size_t(t.stride(0) * 2), ctypes.c_int(0),
+                                                  ctypes.c_size_t(part.size(1) * 2), ctypes.c_size_t(part.size(0)),
+                                                  ctypes.c_void_p(self.stream))
+                            _lib.check(rc, "pb2_memset2d")
             self.high = self.used
             gemm_nt(self.dyt, self.xt, out=grad, accumulate=not fresh, alpha=1.0 / k, sumsq=normsq, stream=self.stream)
         if fresh:

@@ -96,12 +96,13 @@ class EmbedStash:
         grad = ensure_grad(self.weight)
         dev = self.rows.device
         with _lib.on_device(dev):
+            # reset_slots: slots a shorter next step leaves unused must read "empty"; done by the library on the same
+            # stream, right behind the kernel
             rc = _lib.load().pb2_embed_scatter(ctypes.c_void_p(self.toks.data_ptr()), ctypes.c_void_p(self.rows.data_ptr()),
                                                ctypes.c_void_p(grad.data_ptr()), ctypes.c_int(self.toks.numel()),
-                                               ctypes.c_int(self.E), ctypes.c_float(1.0 / self.replicas), ctypes.c_void_p(stream))
+                                               ctypes.c_int(self.E), ctypes.c_float(1.0 / self.replicas), ctypes.c_int(1),
+                                               ctypes.c_void_p(stream))
         _lib.check(rc, "pb2_embed_scatter")
-        with torch.cuda.stream(torch.cuda.ExternalStream(stream, device=dev)):
-            self.toks.fill_(-1)            # slots a shorter next step leaves unused must read "empty"
         self.used = 0
 
 

@@ -294,3 +294,73 @@ def _mailbox_stress(rank, world):
 def test_mailbox_flag_protocol_stress():
     _need(2)
     _spawn(_mailbox_stress, 2)
+
+
+def _peer_store_barrier_case(rank, world):
+    """The ordering the replicated stashes rely on: kernel A stores into every peer's memory, a LATER kernel (the
+    group barrier) exchanges flags, a kernel after that reads what the peers stored — no host synchronisation in
+    between, many rounds back to back."""
+    from pipe_b200.ops import functional as F2
+    from pipe_b200.parallel import SymmetricBuffer
+    dev = torch.device("cuda", rank)
+    R, C = 64, 256                                  # each rank contributes a [C, R] block (transposed [R, C] source)
+    buf = SymmetricBuffer(world * C * R // 2, None, dev)     # bf16 [C, world * R]
+    slab = buf.data.view(torch.bfloat16)[: C * world * R].view(C, world * R)
+    me = buf.peer_data[rank]
+    deltas = [p - me for q, p in enumerate(buf.peer_data) if q != rank]
+    errors = torch.zeros((), dtype=torch.int64, device=dev)
+    for it in range(300):
+        src = torch.full((R, C), float((it % 50) + rank * 64), device=dev).bfloat16()
+        F2.transpose_multi([(src, slab, rank * R, None, 1.0)], deltas)
+        buf.barrier(phase=0)
+        for q in range(world):
+            errors += (slab[:, q * R:(q + 1) * R].float() != float((it % 50) + q * 64)).sum()
+        buf.barrier(phase=1)                        # nobody overwrites before everybody has read
+    torch.cuda.synchronize()
+    assert int(errors.item()) == 0, int(errors.item())
+    dist.barrier()
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_peer_stores_are_visible_after_group_barrier(world):
+    _need(world)
+    _spawn(_peer_store_barrier_case, world)
+
+
+def _embed_stash_case(rank, world):
+    """EmbedStash alone: every replica packs its own rows, after the group barrier every replica must hold the same,
+    complete gradient (= dense scatter-add of all replicas' rows / world), round after round without host syncs."""
+    from pipe_b200.ops import functional as F2
+    from pipe_b200.parallel import SymmetricBuffer
+    from pipe_b200.parallel.replica_stash import EmbedStash
+    dev = torch.device("cuda", rank)
+    V, E, N, S = 300, 256, 4, 16
+    weight = torch.nn.Parameter(torch.zeros(V, E, device=dev))
+    weight.grad = torch.zeros(V, E, device=dev)
+    sync = SymmetricBuffer(8, None, dev)                    # its pad carries the barriers
+    stash = EmbedStash(weight, dist.group.WORLD, dev, max_tokens=2 * N * S)
+    bad = torch.zeros((), dtype=torch.int64, device=dev)
+    for it in range(40):
+        g = torch.Generator().manual_seed(1000 + it)
+        all_tok = torch.randint(0, V, (world, 2, N, S), generator=g).to(dev)
+        all_dout = torch.randn(world, 2, S, N, E, generator=g).to(dev).bfloat16()
+        weight.grad.zero_()
+        for mb in range(2):
+            stash.pack(all_tok[rank, mb].contiguous(), all_dout[rank, mb].contiguous(), 2.0, 0.0, 0, 0)
+        sync.barrier(phase=0)
+        stash.scatter(torch.cuda.current_stream(dev).cuda_stream)
+        sync.barrier(phase=1)
+        want = torch.zeros(V, E, device=dev)
+        for q in range(world):
+            for mb in range(2):
+                F2.embed_bwd(all_tok[q, mb].contiguous(), all_dout[q, mb].contiguous(), want, 2.0, 0.0, 0, 0)
+        bad += (~torch.isclose(weight.grad, want / world, rtol=1e-4, atol=1e-4)).sum()
+    torch.cuda.synchronize()
+    assert int(bad.item()) == 0, int(bad.item())
+    dist.barrier()
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_embedding_rows_exchange_gives_every_replica_the_full_gradient(world):
+    _need(world)
+    _spawn(_embed_stash_case, world)

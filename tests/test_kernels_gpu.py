@@ -227,3 +227,36 @@ def test_fused_clip_adam_matches_torch():
     for sh in layer.pb2_shadows():
         assert torch.equal(sh.w16, sh.param.detach().bfloat16())
         assert torch.equal(sh.w16t[:, : sh.param.size(0)], sh.param.detach().t().bfloat16())
+
+
+@pytest.mark.parametrize("drop_p", [0.0, 0.3])
+def test_embed_pack_scatter_matches_dense_embedding_backward(drop_p):
+    """The row-exchange form of the embedding gradient (pb2_embed_pack + pb2_embed_scatter, used by the data-parallel
+    hybrid) against the dense scatter-add kernel: two "replicas" packed into two regions of one stash, mean over both."""
+    import ctypes
+
+    from pipe_b200.ops import _lib
+    from pipe_b200.ops import functional as F2
+    torch.manual_seed(0)
+    N, S, E, V, cap = 3, 7, 256, 50, 24
+    lib = _lib.load()
+    slots = 2 * cap
+    rows = torch.zeros(slots, E, device="cuda")
+    toks = torch.full((slots,), -1, dtype=torch.int64, device="cuda")
+    want = torch.zeros(V, E, device="cuda")
+    for r in range(2):
+        tokens = torch.randint(0, V, (N, S), device="cuda")
+        dout = torch.randn(S, N, E, device="cuda").bfloat16()
+        F2.embed_bwd(tokens, dout, want, 4.0, drop_p, 123 + r, 0)
+        off = r * cap
+        rc = lib.pb2_embed_pack(ctypes.c_void_p(tokens.data_ptr()), ctypes.c_void_p(dout.data_ptr()),
+                                ctypes.c_void_p(rows[off].data_ptr()), ctypes.c_void_p(toks[off:].data_ptr()),
+                                ctypes.c_int(N), ctypes.c_int(S), ctypes.c_int(E), ctypes.c_float(4.0), ctypes.c_float(drop_p),
+                                ctypes.c_ulonglong(123 + r), ctypes.c_ulonglong(0), ctypes.c_int(0), None, _lib.stream_ptr())
+        _lib.check(rc, "pb2_embed_pack")
+    got = torch.zeros(V, E, device="cuda")
+    rc = lib.pb2_embed_scatter(ctypes.c_void_p(toks.data_ptr()), ctypes.c_void_p(rows.data_ptr()), ctypes.c_void_p(got.data_ptr()),
+                               ctypes.c_int(slots), ctypes.c_int(E), ctypes.c_float(0.5), ctypes.c_int(0), _lib.stream_ptr())
+    _lib.check(rc, "pb2_embed_scatter")
+    torch.cuda.synchronize()
+    assert torch.allclose(got, want * 0.5, rtol=1e-5, atol=1e-5), (got - want * 0.5).abs().max().item()
