@@ -336,41 +336,37 @@ embed_pack_kernel(const EmbedPackArgs a) {
             *reinterpret_cast<float4*>(reinterpret_cast<char*>(dst) + a.peer_delta[q]) = out;
     }
     // see transpose_multi_kernel: the peer stores must have been performed when this grid retires
-    if (a.n_peers > 0) __threadfence_system();
+    if (a.n_peers > 0) {
+        __syncthreads();
+        if (threadIdx.x == 0) __threadfence_system();
+    }
 }
 
-// system-scope loads: the stash was written by other GPUs; these reads must observe what the flag exchange ordered
-__device__ __forceinline__ long long ld_sys_s64(const long long* p) {
-    long long v;
-    asm volatile("ld.relaxed.sys.global.s64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ float4 ld_sys_f32x4(const float* p) {
-    float4 v;
-    asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
-    return v;
-}
+constexpr int kScatterMaxSlots = 4096;           // token ids of the whole stash are staged in shared memory (32 KB)
 
 __global__ void __launch_bounds__(256)
-embed_scatter_kernel(const long long* toks, const float* rows, float* __restrict__ dweight, int R, int E, float alpha) {
+embed_scatter_kernel(const long long* __restrict__ toks, const float* __restrict__ rows, float* __restrict__ dweight,
+                     int R, int E, float alpha) {
     pdl_launch_dependents();
     pdl_wait();
-    const int r = blockIdx.x;
-    const long long tok = ld_sys_s64(toks + r);
-    if (tok < 0) return;                                   // unused slot
-    // not the first slot with this token: an earlier CTA owns the sum
+    __shared__ long long s_tok[kScatterMaxSlots];
     __shared__ int earlier;
+    const int r = blockIdx.x;
+    const long long tok = toks[r];
+    if (tok < 0) return;                                   // unused slot (uniform for the CTA)
     if (threadIdx.x == 0) earlier = 0;
+    for (int i = threadIdx.x; i < R; i += blockDim.x) s_tok[i] = toks[i];
     __syncthreads();
+    // not the first slot with this token: an earlier CTA owns the sum
     for (int i = threadIdx.x; i < r; i += blockDim.x)
-        if (ld_sys_s64(toks + i) == tok) earlier = 1;
+        if (s_tok[i] == tok) earlier = 1;
     __syncthreads();
     if (earlier) return;
     for (int c = threadIdx.x * 4; c < E; c += blockDim.x * 4) {
-        float4 acc = ld_sys_f32x4(rows + static_cast<size_t>(r) * E + c);
+        float4 acc = *reinterpret_cast<const float4*>(rows + static_cast<size_t>(r) * E + c);
         for (int i = r + 1; i < R; ++i) {
-            if (ld_sys_s64(toks + i) != tok) continue;     // uniform across the CTA
-            const float4 v = ld_sys_f32x4(rows + static_cast<size_t>(i) * E + c);
+            if (s_tok[i] != tok) continue;                 // uniform across the CTA, broadcast read
+            const float4 v = *reinterpret_cast<const float4*>(rows + static_cast<size_t>(i) * E + c);
             acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
         }
         float4* dw = reinterpret_cast<float4*>(dweight + static_cast<size_t>(tok) * E + c);
@@ -574,7 +570,11 @@ transpose_multi_kernel(const pb2_transpose_jobs jobs) {
     // Stores into a peer's memory are posted: the grid can retire while they are still on their way, and a flag raised
     // by a LATER kernel (pb2_group_barrier) may then overtake them on another NVLink lane.  A system-scope fence by the
     // storing thread itself makes "this kernel has completed" imply "its peer stores have been performed".
-    if (jobs.n_peers > 0) __threadfence_system();
+    // One fence per CTA is enough: the barrier orders the other threads' stores before thread 0's fence, which is cumulative.
+    if (jobs.n_peers > 0) {
+        __syncthreads();
+        if (threadIdx.x == 0) __threadfence_system();
+    }
 }
 
 // Fire-and-forget L2 prefetch of a byte range: each thread asks the memory system for one 16 KB
@@ -693,6 +693,7 @@ extern "C" int pb2_embed_pack(const long long* tokens, const void* dout, float* 
 extern "C" int pb2_embed_scatter(long long* toks, const float* rows, float* dweight, int R, int E, float alpha,
                                  int reset_slots, cudaStream_t stream) {
     if (E % 4) { set_error("pb2_embed_scatter: E must be a multiple of 4"); return -1; }
+    if (R > kScatterMaxSlots) { set_error("pb2_embed_scatter: at most %d stash slots (replicas x tokens per step), got %d", kScatterMaxSlots, R); return -1; }
     if (R <= 0) return 0;
     PB2_CUDA(launch_pdl(embed_scatter_kernel, dim3(R), dim3(256), 0, stream, toks, rows, dweight, R, E, alpha));
     PB2_LAUNCHED("embed_scatter_kernel");
