@@ -364,3 +364,79 @@ def _embed_stash_case(rank, world):
 def test_embedding_rows_exchange_gives_every_replica_the_full_gradient(world):
     _need(world)
     _spawn(_embed_stash_case, world)
+
+
+def _nccl_skip_case(rank, world):
+    """DistPipe over NCCL: a @skippable stash on the first rank popped on the last one (direct route over the
+    pipeline group), in all three checkpoint modes, a short last batch, and an eval pass after training."""
+    from torch import nn
+
+    from pipe_b200.parallel import DistPipe
+    from pipe_b200.skip import Namespace, pop, skippable, stash
+    dev = torch.device("cuda", rank)
+
+    @skippable(stash=["res"])
+    class Stash(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.lin = nn.Linear(16, 16)
+
+        def forward(self, x):
+            y = self.lin(x)
+            yield stash("res", y)
+            return torch.tanh(y)
+
+    @skippable(pop=["res"])
+    class Pop(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.lin = nn.Linear(16, 16)
+
+        def forward(self, x):
+            res = yield pop("res")
+            return self.lin(x) + 2.0 * res
+
+    def build():
+        torch.manual_seed(1)
+        ns = Namespace(key="blk")
+        layers = [Stash().isolate(ns)] + [nn.Sequential(nn.Linear(16, 16), nn.Tanh()) for _ in range(world - 2)] + \
+                 [nn.Sequential(Pop().isolate(ns), nn.Linear(16, 4))]
+        if world == 2:
+            layers = [nn.Sequential(layers[0]), layers[-1]]
+        else:
+            layers = [nn.Sequential(layers[0])] + layers[1:]
+        return layers
+
+    for mode in ("never", "always", "except_last"):
+        stages = build()
+        mine = stages[rank].to(dev)
+        pipe = DistPipe(mine, chunks=3, checkpoint=mode, device=dev)
+        full = nn.Sequential(*[l for st in build() for l in st]).to(dev)
+        torch.manual_seed(7)
+        for rows in (6, 6, 4):                               # the last batch is shorter
+            x = torch.rand(rows, 16, device=dev)
+            for p in mine.parameters():
+                p.grad = None
+            out = pipe(x) if pipe.is_first else pipe()
+            pipe.backward(out.local_value().pow(2).sum() if pipe.is_last else None)
+        full.zero_grad()
+        ref = full(x)
+        ref.pow(2).sum().backward()
+        if pipe.is_last:
+            assert torch.allclose(out.local_value(), ref, atol=1e-5), mode
+        ref_params = dict(full.named_parameters())
+        n_before = sum(len(list(s.parameters())) for s in stages[:rank])
+        for a, b in zip(mine.parameters(), list(full.parameters())[n_before:]):
+            assert torch.allclose(a.grad, b.grad, atol=1e-4), (mode, rank)
+        pipe.eval()
+        with torch.no_grad():
+            out = pipe(x) if pipe.is_first else pipe()
+        if pipe.is_last:
+            assert torch.allclose(out.local_value(), full(x), atol=1e-5)
+        dist.barrier()
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_dist_pipe_skip_and_changing_batches_over_nccl(world):
+    _need(world)
+    _spawn(_nccl_skip_case, world)
