@@ -65,6 +65,9 @@ typedef struct pb2_gemm_desc {
     int persistent;       /* tile scheduling when there is no split-K: 0 = choose (persistent CTAs with a
                              double-buffered TMEM accumulator when there are more tiles than SMs),
                              1 = always persistent, 2 = one CTA per tile */
+    int a_mn_major;       /* 1: `a` points to the TRANSPOSE, a bf16 [K, M] matrix with M contiguous and row stride lda — the
+                             tensor core reads it as an MN-major operand.  This is how a dgrad GEMM consumes the forward
+                             weight [out, in] as it is (M = in, K = out) instead of a transposed copy. */
 } pb2_gemm_desc;
 
 size_t pb2_gemm_workspace_bytes(void);
@@ -288,7 +291,8 @@ typedef struct pb2_encoder_layer {
     int causal;
     float drop_p, eps;
     unsigned long long seed;
-    /* bf16 weight shadows [out, in] and transposed shadows [in, ld >= out] */
+    /* bf16 weight shadows [out, in] and — optional — transposed shadows [in, ld >= out]: with wt_* = NULL the dgrad GEMMs
+     * read w_* as MN-major operands (no transposed copy exists) */
     const void *w_qkv, *w_o, *w_1, *w_2;
     const void *wt_qkv, *wt_o, *wt_1, *wt_2;
     long long ldt_qkv, ldt_o, ldt_1, ldt_2;

@@ -284,6 +284,25 @@ __host__ __device__ __forceinline__ uint32_t umma_idesc_bf16(uint32_t m, uint32_
     return d;
 }
 
+// Shared-memory descriptor of an MN-major bf16 operand stored as rows of 64 MN-elements (128 bytes, the row
+// index is K) with the 128-byte swizzle: 8-row K groups are 1024 bytes apart (SBO); further 64-element MN
+// atoms start `lbo_bytes` apart (LBO).  This is what a TMA box of [rows, 64 columns] of a row-major matrix
+// whose *rows* are the reduction dimension gives (V for P V, dO for P^T dO, ...).
+__device__ __forceinline__ uint64_t umma_desc_mn_sw128(uint32_t smem_addr, uint32_t lbo_bytes) {
+    uint64_t d = 0;
+    d |= static_cast<uint64_t>((smem_addr & 0x3FFFF) >> 4);
+    d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFF) << 16;
+    d |= static_cast<uint64_t>(1024 >> 4) << 32;
+    d |= static_cast<uint64_t>(1) << 46;
+    d |= static_cast<uint64_t>(2) << 61;
+    return d;
+}
+
+// bf16 x bf16 -> fp32 instruction descriptor with explicit operand majors (0 = K-major, 1 = MN-major)
+__host__ __device__ __forceinline__ uint32_t umma_idesc_bf16_major(uint32_t m, uint32_t n, uint32_t a_mn, uint32_t b_mn) {
+    return umma_idesc_bf16(m, n) | (a_mn << 15) | (b_mn << 16);
+}
+
 // ---- counter-based random bits -------------------------------------------------------
 // Stateless generator: 128 random bits as a pure function of (seed, stream, counter), built from
 // two SplitMix64 finalisers (2 x 64-bit multiply-xorshift).  Dropout needs reproducibility — the

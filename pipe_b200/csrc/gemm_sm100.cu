@@ -81,7 +81,24 @@ struct GemmArgs {
     int local_chunks;                // 16-column chunks each cluster rank owns (ceil(n_chunks / splits))
     unsigned long long* debug_ts;    // optional: per-CTA phase timestamps (globaltimer ns), 8 per CTA
     int tma_store;                   // persistent kernel: plain fp32 row-major result leaves through TMA stores
+    int a_mn;                        // A is stored [K, M] (M contiguous): MN-major operand, two 64-column boxes per stage
 };
+
+// One stage of A.  K-major: one [128 rows, 64 k] box.  MN-major (A given as [K, M]): two [64 k-rows, 64 m-columns] boxes,
+// 8 KB apart — the two 64-element MN atoms of the 128-row tile.
+__device__ __forceinline__ void load_a_stage(uint8_t* sa, const CUtensorMap* tmap, uint64_t* bar, int k_elem, int m0,
+                                             uint64_t hint, int a_mn) {
+    if (a_mn) {
+        tma_load_2d(sa, tmap, bar, m0, k_elem, hint);
+        tma_load_2d(sa + 8192, tmap, bar, m0 + 64, k_elem, hint);
+    } else {
+        tma_load_2d(sa, tmap, bar, k_elem, m0, hint);
+    }
+}
+__device__ __forceinline__ uint64_t a_desc(uint32_t sa, int a_mn) {
+    return a_mn ? umma_desc_mn_sw128(sa, 8192) : umma_desc_k_sw128(sa);
+}
+
 
 __device__ __forceinline__ unsigned long long gtime() {
     unsigned long long t;
@@ -386,7 +403,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                 for (int it = 0; it < pre; ++it) {
                     uint8_t* sa = smem + static_cast<size_t>(it) * stage_bytes;
                     mbar_expect_tx(&ctl->full[it], stage_bytes);
-                    tma_load_2d(sa, &tmap_a, &ctl->full[it], (kb_begin + it) * kBlockK, m0, kEvictFirst);
+                    load_a_stage(sa, &tmap_a, &ctl->full[it], (kb_begin + it) * kBlockK, m0, kEvictFirst, g.a_mn);
                 }
             }
             pdl_wait();
@@ -403,14 +420,15 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                 mbar_expect_tx(&ctl->full[s], stage_bytes);
                 const int k_elem = (kb_begin + it) * kBlockK;
                 // weights (A) are streamed once: evict-first; tokens (B) are re-read by every M tile: evict-last
-                tma_load_2d(sa, &tmap_a, &ctl->full[s], k_elem, m0, kEvictFirst);
+                load_a_stage(sa, &tmap_a, &ctl->full[s], k_elem, m0, kEvictFirst, g.a_mn);
                 tma_load_2d(sb, &tmap_b, &ctl->full[s], k_elem, n0, kEvictLast);
             }
         }
         __syncwarp();       // reconverge before any warp-aligned barrier below
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
-        const uint32_t idesc = umma_idesc_bf16(kBlockM, g.block_n);
+        const uint32_t idesc = umma_idesc_bf16_major(kBlockM, g.block_n, g.a_mn ? 1u : 0u, 0u);
+        const uint64_t a_step = g.a_mn ? 128 : 2;       // 16 k: two 8-row groups (2048 B) MN-major, 32 bytes K-major
         for (int it = 0; it < kb_count; ++it) {
             const int s = it % g.stages;
             const uint32_t round = it / g.stages;
@@ -419,12 +437,12 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
             if (it == 0 && lane == 0) PB2_TS(2);
             if (elect_one()) {
                 const uint32_t sa = smem_u32(smem + static_cast<size_t>(s) * stage_bytes);
-                const uint64_t da = umma_desc_k_sw128(sa);
+                const uint64_t da = a_desc(sa, g.a_mn);
                 const uint64_t db = umma_desc_k_sw128(sa + a_bytes);
 #pragma unroll
                 for (int k = 0; k < kBlockK / kUmmaK; ++k) {
                     // advance 16 elements = 32 bytes along K inside the swizzle row: +2 in 16-byte units
-                    umma_bf16(tmem_base, da + 2 * k, db + 2 * k, idesc, (it > 0 || k > 0) ? 1u : 0u);
+                    umma_bf16(tmem_base, da + a_step * k, db + 2 * k, idesc, (it > 0 || k > 0) ? 1u : 0u);
                 }
                 umma_commit(&ctl->empty[s]);                      // frees the smem stage when the MMAs retire
                 if (it == kb_count - 1) { umma_commit(&ctl->tmem_full); PB2_TS(3); }
@@ -693,8 +711,8 @@ gemm_bf16_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
                 for (int it = 0; it < pre; ++it) {
                     const int tile = blockIdx.x + (it / kbt) * gridDim.x;
                     mbar_expect_tx(&ctl->full[it], stage_bytes);
-                    tma_load_2d(smem + static_cast<size_t>(it) * stage_bytes, &tmap_a, &ctl->full[it],
-                                (it % kbt) * kBlockK, (tile % m_tiles) * kBlockM, a_hint);
+                    load_a_stage(smem + static_cast<size_t>(it) * stage_bytes, &tmap_a, &ctl->full[it],
+                                 (it % kbt) * kBlockK, (tile % m_tiles) * kBlockM, a_hint, g.a_mn);
                 }
             }
             pdl_wait();
@@ -711,7 +729,7 @@ gemm_bf16_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
                 mbar_wait(&ctl->empty[s], (round & 1) ^ 1);
                 uint8_t* sa = smem + static_cast<size_t>(s) * stage_bytes;
                 mbar_expect_tx(&ctl->full[s], stage_bytes);
-                tma_load_2d(sa, &tmap_a, &ctl->full[s], kb * kBlockK, (tile % m_tiles) * kBlockM, a_hint);
+                load_a_stage(sa, &tmap_a, &ctl->full[s], kb * kBlockK, (tile % m_tiles) * kBlockM, a_hint, g.a_mn);
                 tma_load_2d(sa + a_bytes, &tmap_b, &ctl->full[s], kb * kBlockK, (tile / m_tiles) * g.block_n, b_hint);
                 if (++s == g.stages) { s = 0; ++round; }
                 if (++kb == kbt) { kb = 0; tile += gridDim.x; }
@@ -720,7 +738,8 @@ gemm_bf16_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
         __syncwarp();
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
-        const uint32_t idesc = umma_idesc_bf16(kBlockM, g.block_n);
+        const uint32_t idesc = umma_idesc_bf16_major(kBlockM, g.block_n, g.a_mn ? 1u : 0u, 0u);
+        const uint64_t a_step = g.a_mn ? 128 : 2;
         int s = 0;
         uint32_t round = 0;
         for (int t = 0; t < my_tiles; ++t) {
@@ -733,11 +752,11 @@ gemm_bf16_persistent_kernel(const __grid_constant__ CUtensorMap tmap_a, const __
                 tc_fence_after();
                 if (elect_one()) {
                     const uint32_t sa = smem_u32(smem + static_cast<size_t>(s) * stage_bytes);
-                    const uint64_t da = umma_desc_k_sw128(sa);
+                    const uint64_t da = a_desc(sa, g.a_mn);
                     const uint64_t db = umma_desc_k_sw128(sa + a_bytes);
 #pragma unroll
                     for (int k = 0; k < kBlockK / kUmmaK; ++k)
-                        umma_bf16(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+                        umma_bf16(d_tmem, da + a_step * k, db + 2 * k, idesc, (kb > 0 || k > 0) ? 1u : 0u);
                     umma_commit(&ctl->empty[s]);
                     if (kb == kbt - 1) umma_commit(&ctl->acc_full[acc]);
                 }
@@ -1013,10 +1032,14 @@ static int gemm_launch(const pb2_gemm_desc* d, float* partials, unsigned int* co
     g.accumulate = d->accumulate; g.alpha = d->alpha == 0.f ? 1.f : d->alpha;
     g.sumsq = d->sumsq;
     g.a_static = d->a_static;
+    g.a_mn = d->a_mn_major ? 1 : 0;
     g.debug_ts = g_debug_ts;
 
     CUtensorMap ta, tb;
-    if (make_tmap_bf16_2d(&ta, d->a, d->M, d->K, d->lda, kBlockM, kBlockK)) return -1;
+    if (g.a_mn) {
+        // A is [K, M] with M contiguous: boxes of 64 k-rows x 64 m-columns
+        if (make_tmap_bf16_2d(&ta, d->a, d->K, d->M, d->lda, kBlockK, 64)) return -1;
+    } else if (make_tmap_bf16_2d(&ta, d->a, d->M, d->K, d->lda, kBlockM, kBlockK)) return -1;
     if (make_tmap_bf16_2d(&tb, d->b, d->N, d->K, d->ldb, bn, kBlockK)) return -1;
 
     // more tiles than SMs and no split-K: one persistent CTA per SM, epilogue overlapped with the next tile

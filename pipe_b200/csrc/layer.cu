@@ -13,10 +13,18 @@
 namespace {
 
 struct Lin {
-    const void* w;        // A operand: [M rows, K], row stride lda
+    const void* w;        // A operand: [M rows, K], row stride lda — or, with a_mn, its transpose [K, M] (row stride lda)
     long long lda;
     int M, K;
+    int a_mn = 0;
 };
+
+// dgrad through a Linear with forward weight W [out, in]: dX[T, in] = dY[T, out] W.  With a transposed shadow (wt) that is
+// the usual K-major GEMM; without one the forward shadow itself is read as an MN-major operand (M = in, K = out).
+Lin dgrad_weight(const void* wt, long long ldt, const void* w, int in_f, int out_f) {
+    if (wt) return Lin{wt, ldt, in_f, out_f, 0};
+    return Lin{w, in_f, in_f, out_f, 1};
+}
 
 int linear(const pb2_encoder_layer* L, const Lin& w, const void* act, int T, void* out, const float* bias, int relu,
            float drop_p, unsigned long long rng_stream, const void* mask_src, float mask_scale, const void* addend,
@@ -31,6 +39,7 @@ int linear(const pb2_encoder_layer* L, const Lin& w, const void* act, int T, voi
     d.drop_p = drop_p; d.seed = L->seed; d.rng_stream = rng_stream;
     d.mask_src = mask_src; d.mask_scale = mask_scale; d.addend = addend;
     d.alpha = 1.f;
+    d.a_mn_major = w.a_mn;
     d.a_static = 1;       // weight shadows are only written by the optimizer kernel, never by a layer kernel
     return pb2_gemm_bf16(&d, L->workspace, L->workspace_bytes, stream);
 }
@@ -81,15 +90,15 @@ extern "C" int pb2_encoder_layer_bwd(const pb2_encoder_layer* L, cudaStream_t st
     if (pb2_add_layernorm_bwd(L->dy, L->x1, L->f, L->g2, L->mean2, L->rstd2, L->dr2, L->df, L->dg2, L->dbe2, T, E, p,
                               L->seed, 3, stream)) return -1;
     // through linear2, then ReLU + dropout (mask recovered from the saved activation)
-    if (linear(L, Lin{L->wt_2, L->ldt_2, FF, E}, L->df, T, L->dz1, nullptr, 0, 0.f, 0, L->hmid, inv_keep, nullptr, stream)) return -1;
+    if (linear(L, dgrad_weight(L->wt_2, L->ldt_2, L->w_2, FF, E), L->df, T, L->dz1, nullptr, 0, 0.f, 0, L->hmid, inv_keep, nullptr, stream)) return -1;
     if (pf && pb2_l2_prefetch(L->wt_o, w_ee, stream)) return -1;
     // through linear1, plus the residual branch
-    if (linear(L, Lin{L->wt_1, L->ldt_1, E, FF}, L->dz1, T, L->dx1, nullptr, 0, 0.f, 0, nullptr, 0.f, L->dr2, stream)) return -1;
+    if (linear(L, dgrad_weight(L->wt_1, L->ldt_1, L->w_1, E, FF), L->dz1, T, L->dx1, nullptr, 0, 0.f, 0, nullptr, 0.f, L->dr2, stream)) return -1;
     // x1 = LN1(x + drop(o))
     if (pb2_add_layernorm_bwd(L->dx1, L->x, L->o, L->g1, L->mean1, L->rstd1, L->dr1, L->do_, L->dg1, L->dbe1, T, E, p,
                               L->seed, 1, stream)) return -1;
     if (pf && pb2_l2_prefetch(L->wt_qkv, w_qt, stream)) return -1;
-    if (linear(L, Lin{L->wt_o, L->ldt_o, E, E}, L->do_, T, L->da, nullptr, 0, 0.f, 0, nullptr, 0.f, nullptr, stream)) return -1;
+    if (linear(L, dgrad_weight(L->wt_o, L->ldt_o, L->w_o, E, E), L->do_, T, L->da, nullptr, 0, 0.f, 0, nullptr, 0.f, nullptr, stream)) return -1;
     if (pb2_attention_uses_flash(L->S, E / L->heads)) {
         if (!L->attn_lse || !L->attn_scratch) { pb2::set_error("pb2_encoder_layer_bwd: this shape uses flash attention: attn_lse / attn_scratch are required"); return -1; }
         if (pb2_flash_attention_bwd(L->qkv, L->a, L->da, L->attn_lse, L->dqkv, L->attn_scratch, L->attn_scratch_bytes, L->NB, L->S,
@@ -105,7 +114,7 @@ extern "C" int pb2_encoder_layer_bwd(const pb2_encoder_layer* L, cudaStream_t st
         if (pb2::record_and_wait(stream, tstream)) return -1;
     }
     if (pf && L->next_weight && pb2_l2_prefetch(L->next_weight, L->next_weight_bytes, stream)) return -1;
-    if (linear(L, Lin{L->wt_qkv, L->ldt_qkv, E, 3 * E}, L->dqkv, T, L->dx, nullptr, 0, 0.f, 0, nullptr, 0.f, L->dr1, stream)) return -1;
+    if (linear(L, dgrad_weight(L->wt_qkv, L->ldt_qkv, L->w_qkv, E, 3 * E), L->dqkv, T, L->dx, nullptr, 0, 0.f, 0, nullptr, 0.f, L->dr1, stream)) return -1;
 
     // stack every wgrad operand (and column-sum the bias gradients) in one launch
     pb2_transpose_jobs jobs;

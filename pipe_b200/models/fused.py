@@ -48,9 +48,15 @@ def _round_up(x: int, m: int) -> int:
     return (x + m - 1) // m * m
 
 
+# The dgrad GEMMs read the forward shadow [out, in] as an MN-major tcgen05 operand, so no transposed copy is kept
+# (2 of the optimizer's 32 bytes per parameter and step, and 2 bytes per parameter of memory).  PB2_DGRAD_SHADOW=1
+# brings the transposed bf16 shadow back (the round-1 layout, both operands K-major).
+_TRANSPOSED_SHADOW = os.environ.get("PB2_DGRAD_SHADOW", "0") == "1"
+
+
 class Shadow:
-    """bf16 copy ``w16 [out, in]`` and transposed copy ``w16t [in, ld_t]`` of an
-    fp32 master weight, kept in sync lazily."""
+    """bf16 copy ``w16 [out, in]`` of an fp32 master weight (and, with ``PB2_DGRAD_SHADOW=1``, a transposed copy
+    ``w16t [in, ld_t]``), kept in sync lazily."""
 
     def __init__(self, param: nn.Parameter) -> None:
         self.param = param
@@ -63,16 +69,18 @@ class Shadow:
         if self.w16 is None or self.w16.device != p.device:
             rows, cols = p.shape
             self.w16 = torch.empty((rows, cols), dtype=torch.bfloat16, device=p.device)
-            self.w16t = torch.zeros((cols, _round_up(rows, 8)), dtype=torch.bfloat16, device=p.device)
+            self.w16t = (torch.zeros((cols, _round_up(rows, 8)), dtype=torch.bfloat16, device=p.device)
+                         if _TRANSPOSED_SHADOW else None)
             self.version = -1
 
-    def ensure(self) -> Tuple[Tensor, Tensor]:
+    def ensure(self) -> Tuple[Tensor, Optional[Tensor]]:
         p = self.param
         self.allocate()
         if p._version != self.version:
             with torch.no_grad():
                 self.w16.copy_(p)
-                self.w16t[:, : p.size(0)].copy_(p.t())
+                if self.w16t is not None:
+                    self.w16t[:, : p.size(0)].copy_(p.t())
             self.version = p._version
         return self.w16, self.w16t
 
@@ -317,7 +325,7 @@ class FusedEncoderLayer(_FusedBase):
         """A fresh launch descriptor with everything that does not change between calls
         (shapes, weight shadows, biases, LayerNorm parameters) filled in."""
         sh = {k: self._sh(k) for k in ("qkv", "o", "l1", "l2")}
-        key = tuple(t.data_ptr() for pair in sh.values() for t in pair)
+        key = tuple(t.data_ptr() for pair in sh.values() for t in pair if t is not None)
         cached = self.__dict__.get("_pb2_desc")
         if cached is None or cached[0] != key:
             d = _lib.EncoderLayerDesc()
@@ -326,8 +334,9 @@ class FusedEncoderLayer(_FusedBase):
             for name, k in (("qkv", "qkv"), ("o", "o"), ("1", "l1"), ("2", "l2")):
                 w16, w16t = sh[k]
                 setattr(d, "w_" + name, w16.data_ptr())
-                setattr(d, "wt_" + name, w16t.data_ptr())
-                setattr(d, "ldt_" + name, w16t.stride(0))
+                if w16t is not None:
+                    setattr(d, "wt_" + name, w16t.data_ptr())
+                    setattr(d, "ldt_" + name, w16t.stride(0))
             at = self.self_attn
             d.b_qkv, d.b_o = at.in_proj_bias.data_ptr(), at.out_proj.bias.data_ptr()
             d.b_1, d.b_2 = self.linear1.bias.data_ptr(), self.linear2.bias.data_ptr()
@@ -645,6 +654,14 @@ class FusedEncoder(nn.Module):
 # ======================================================================================
 # vocabulary projection (+ fused cross-entropy)
 # ======================================================================================
+def _decoder_dgrad(module: "FusedDecoder", dl: Tensor, V: int) -> Tensor:
+    """dX[T, E] = dlogits[T, V] W[V, E]: the forward shadow read as an MN-major operand (or the transposed shadow)."""
+    w16, w16t = module._sh("dec")
+    if w16t is not None:
+        return gemm_nt(w16t[:, :V], dl, transpose_out=True)
+    return gemm_nt(w16, dl, a_mn=True, transpose_out=True, a_static=True)
+
+
 class _DecoderFn(torch.autograd.Function):
     """logits = x W^T + b, returned batch-first like the reference's Decoder.
 
@@ -692,8 +709,7 @@ class _DecoderFn(torch.autograd.Function):
         buf = torch.zeros((T, ld), dtype=torch.bfloat16, device=xb.device)
         buf[:, :V].view(NB, S, V).copy_(dlogits)
         dl = buf[:, :V]
-        _, w16t = module._sh("dec")
-        dx = gemm_nt(w16t[:, :V], dl, transpose_out=True)           # batch-first rows
+        dx = _decoder_dgrad(module, dl, V)                           # batch-first rows
         lg = module._lg("dec")
         F2.transpose_multi(lg.jobs(xb, dl), lg.peer_deltas)
         return (dx.view(NB, S, E).transpose(0, 1), None) + (None,) * (len(ctx.needs_input_grad) - 2)
@@ -731,8 +747,7 @@ class _DecoderLossFn(torch.autograd.Function):
         row_scale = g.float().contiguous().repeat(S)
         F2.cross_entropy(buf, tgt_rows, V, write_grad=True, row_scale=row_scale, want_loss=False)
         dl = buf[:, :V]
-        _, w16t = module._sh("dec")
-        dx = gemm_nt(w16t[:, :V], dl, transpose_out=True)
+        dx = _decoder_dgrad(module, dl, V)
         lg = module._lg("dec")
         F2.transpose_multi(lg.jobs(x2, dl), lg.peer_deltas)
         return (dx.view(S, NB, E), None, None) + (None,) * (len(ctx.needs_input_grad) - 3)

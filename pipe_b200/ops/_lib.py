@@ -40,6 +40,7 @@ class GemmDesc(ctypes.Structure):
         ("reduce_mode", ctypes.c_int),
         ("a_static", ctypes.c_int),
         ("persistent", ctypes.c_int),
+        ("a_mn_major", ctypes.c_int),
     ]
 
 

@@ -48,12 +48,17 @@ def gemm_nt(a: Tensor, b: Tensor, *, out: Optional[Tensor] = None, out_dtype: to
             mask_src: Optional[Tensor] = None, mask_scale: float = 1.0, addend: Optional[Tensor] = None,
             accumulate: bool = False, alpha: float = 1.0, sumsq: Optional[Tensor] = None,
             block_n: int = 0, splits: int = 0, stages: int = 0, reduce_mode: int = 0, a_static: bool = False, persistent: int = 0,
-            stream: Optional[int] = None) -> Tensor:
+            a_mn: bool = False, stream: Optional[int] = None) -> Tensor:
+    """``a_mn=True``: ``a`` is given transposed, ``[K, M]`` with M contiguous (computes ``a.T @ b.T``): the tensor core
+    reads it as an MN-major operand — a dgrad GEMM passes the forward weight ``[out, in]`` as it is."""
     lib = _lib.load()
     assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16, "gemm_nt takes bf16 operands"
-    assert a.dim() == 2 and b.dim() == 2 and a.size(1) == b.size(1)
-    assert a.stride(1) == 1 and b.stride(1) == 1, "operands must be K-contiguous"
-    M, K = a.shape
+    assert a.dim() == 2 and b.dim() == 2 and (a.size(0) if a_mn else a.size(1)) == b.size(1)
+    assert a.stride(1) == 1 and b.stride(1) == 1, "operands must be contiguous along their last dimension"
+    if a_mn:
+        K, M = a.shape
+    else:
+        M, K = a.shape
     N = b.size(0)
     if out is None:
         shape = (N, M) if transpose_out else (M, N)
@@ -87,6 +92,7 @@ def gemm_nt(a: Tensor, b: Tensor, *, out: Optional[Tensor] = None, out_dtype: to
     d.block_n, d.splits, d.stages, d.reduce_mode = block_n, splits, stages, reduce_mode
     d.a_static = int(a_static)
     d.persistent = persistent
+    d.a_mn_major = int(a_mn)
 
     if stream is None:
         stream = _lib.raw_stream(a.device)

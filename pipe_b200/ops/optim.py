@@ -196,7 +196,9 @@ class FusedClipAdam:
                 sh = shadows.get(id(p))
                 if sh is not None:
                     sh.ensure()
-                    d["w16"], d["w16t"], d["ld_t"] = sh.w16.data_ptr(), sh.w16t.data_ptr(), sh.w16t.stride(0)
+                    d["w16"] = sh.w16.data_ptr()
+                    if sh.w16t is not None:
+                        d["w16t"], d["ld_t"] = sh.w16t.data_ptr(), sh.w16t.stride(0)
                 d["rows"], d["cols"], d["tile_start"] = rows, cols, tile
                 tile += ((rows + 31) // 32) * ((cols + 63) // 64)
             st.table = torch.from_numpy(rows_desc.view(np.uint8).copy()).to(st.device)

@@ -144,3 +144,26 @@ def test_persistent_schedule_is_bit_identical(M, N, K, bn):
     gemm_nt(a, b, out=acc2, accumulate=True, sumsq=s2, block_n=bn, persistent=1, splits=1)
     assert torch.equal(acc1, acc2)
     assert abs(s1.item() - s2.item()) <= 1e-4 * abs(s1.item())
+
+
+@pytest.mark.parametrize("M,N,K", [(4096, 75, 4096), (512, 48, 1000), (4096, 75, 28782), (2048, 1024, 6144), (300, 20, 192)])
+def test_mn_major_a_operand_matches_transposed_copy(M, N, K):
+    """``a_mn=True`` reads A from its transpose ``[K, M]`` (M contiguous) as an MN-major UMMA operand: bit-identical to the
+    same GEMM on a materialised ``[M, K]`` copy (same products, same accumulation order), on every scheduling path."""
+    from pipe_b200.ops.gemm import gemm_nt
+    torch.manual_seed(2)
+    Mp = (M + 7) // 8 * 8
+    at = torch.randn(K, Mp, device="cuda").bfloat16()[:, :M]          # [K, M], row stride multiple of 8
+    Kp = (K + 7) // 8 * 8
+    a = torch.zeros(M, Kp, device="cuda", dtype=torch.bfloat16)[:, :K]
+    a.copy_(at.t())
+    b = torch.randn(N, Kp, device="cuda").bfloat16()[:, :K]
+    bias = torch.randn(M, device="cuda")
+    for kw in (dict(transpose_out=True), dict(transpose_out=True, bias=bias, bias_along_m=True, relu=True),
+               dict(out_dtype=torch.float32), dict(transpose_out=True, splits=1, persistent=1)):
+        want = gemm_nt(a, b, **kw)
+        got = gemm_nt(at, b, a_mn=True, **kw)
+        assert torch.equal(got, want), kw
+    ref = (a.float() @ b.float().t())
+    got = gemm_nt(at, b, a_mn=True, out_dtype=torch.float32)
+    assert ((got - ref).abs().max() / ref.abs().max()).item() < 1e-2

@@ -226,7 +226,8 @@ def test_fused_clip_adam_matches_torch():
     # shadows follow the masters
     for sh in layer.pb2_shadows():
         assert torch.equal(sh.w16, sh.param.detach().bfloat16())
-        assert torch.equal(sh.w16t[:, : sh.param.size(0)], sh.param.detach().t().bfloat16())
+        if sh.w16t is not None:              # only with PB2_DGRAD_SHADOW=1: dgrad reads w16 as an MN-major operand otherwise
+            assert torch.equal(sh.w16t[:, : sh.param.size(0)], sh.param.detach().t().bfloat16())
 
 
 @pytest.mark.parametrize("drop_p", [0.0, 0.3])
