@@ -284,6 +284,25 @@ def extras(args, cfg, trainer, out, step_resident, dev, world, rank, local_rank,
     n_host = len(host_tok)
     tokens = cfg.tokens_per_step
 
+    # ---- per-step spread: one CUDA-event pair per step on every rank, max over ranks per step -------------------
+    n_spread = max(steps, 10)
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n_spread)]
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    for k, (a, b) in enumerate(evs):
+        a.record(torch.cuda.current_stream(dev))
+        step_resident(k)
+        b.record(torch.cuda.current_stream(dev))
+    torch.cuda.synchronize()
+    per_step = torch.tensor([a.elapsed_time(b) for a, b in evs], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(per_step, op=dist.ReduceOp.MAX)
+    q = torch.quantile(per_step.cpu(), torch.tensor([0.1, 0.5, 0.9], dtype=torch.float64))
+    out["step_ms_percentiles"] = {"p10": round(float(q[0]), 4), "p50": round(float(q[1]), 4), "p90": round(float(q[2]), 4),
+                                  "steps": n_spread, "how": "CUDA events around each step on every rank, max over ranks per step "
+                                  "(a rank's events also see its wait for neighbours, so the median sits near ms_per_step)"}
+
     # ---- measured bubble ---------------------------------------------------------------------
     if world > 1:
         trainer.pipe.timeline = True
