@@ -92,6 +92,34 @@ int pb2_gemm_bf16(const pb2_gemm_desc* desc, void* workspace, size_t workspace_b
 size_t pb2_gemm_noalloc_max_scratch_bytes(void);
 int pb2_gemm_bf16_noalloc(const pb2_gemm_desc* desc, cudaStream_t stream);
 
+/* ---- op chain: dependent skinny GEMMs and the LayerNorms between them as one persistent kernel ----
+ * Every GEMM is described exactly as for pb2_gemm_bf16 (same fused epilogue; not available: accumulate, sumsq,
+ * bias along n) and must see the same N <= 128 tokens; op i may read what any op j < i wrote.  The weights (`a`) of
+ * ALL ops must not be written by the kernel launched before this one: they are fetched ahead of everything else.
+ * `workspace` is the GEMM workspace; its last PB2_CHAIN_BARRIER_BYTES (inside the counter block, zero like the rest)
+ * hold the grid-barrier counters, which the kernel leaves at zero.  pb2_chain_supported: 1 if the ops can run as a
+ * chain, else run them one by one.  No counterpart in the reference (separate cuBLAS / ATen calls, main.py:148). */
+#define PB2_CHAIN_MAX_OPS 8
+#define PB2_CHAIN_BARRIER_BYTES 256u
+typedef struct pb2_chain_ln {
+    const void* x;
+    const void* h;        /* may be NULL */
+    const float* gamma;
+    const float* beta;
+    void* y;
+    float* mean;
+    float* rstd;
+    int rows, E;
+    float eps;
+} pb2_chain_ln;
+typedef struct pb2_chain_op {
+    int kind;             /* 0: GEMM (`gemm`), 1: y = LayerNorm(x + h) (`ln`) */
+    pb2_gemm_desc gemm;
+    pb2_chain_ln ln;
+} pb2_chain_op;
+int pb2_chain_supported(const pb2_chain_op* ops, int n_ops);
+int pb2_chain_run(const pb2_chain_op* ops, int n_ops, void* workspace, size_t workspace_bytes, cudaStream_t stream);
+
 /* ---- residual add + LayerNorm: y = LN(x + h) (h may be NULL) ------------------------------
  * bf16 rows of width E (multiple of 8, <= 8192), fp32 gamma/beta/statistics.
  * Backward also returns dh = dres * dropout_mask / (1 - p): the gradient of the sub-layer output

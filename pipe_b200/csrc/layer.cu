@@ -5,6 +5,7 @@
 //
 // Reference counterpart: the Python-level op sequence of nn.TransformerEncoderLayer
 // (main.py:148) as driven by the autograd engine; SURVEY.md §3.2 "GPU hot path", §7.4 item 2.
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -26,9 +27,9 @@ Lin dgrad_weight(const void* wt, long long ldt, const void* w, int in_f, int out
     return Lin{w, in_f, in_f, out_f, 1};
 }
 
-int linear(const pb2_encoder_layer* L, const Lin& w, const void* act, int T, void* out, const float* bias, int relu,
-           float drop_p, unsigned long long rng_stream, const void* mask_src, float mask_scale, const void* addend,
-           cudaStream_t stream) {
+pb2_gemm_desc linear_desc(const pb2_encoder_layer* L, const Lin& w, const void* act, int T, void* out, const float* bias,
+                          int relu, float drop_p, unsigned long long rng_stream, const void* mask_src, float mask_scale,
+                          const void* addend) {
     // out[T, M] = act[T, K] * w[M, K]^T  (weights on the UMMA M axis, transposed store)
     pb2_gemm_desc d;
     memset(&d, 0, sizeof(d));
@@ -41,7 +42,70 @@ int linear(const pb2_encoder_layer* L, const Lin& w, const void* act, int T, voi
     d.alpha = 1.f;
     d.a_mn_major = w.a_mn;
     d.a_static = 1;       // weight shadows are only written by the optimizer kernel, never by a layer kernel
+    return d;
+}
+
+int linear(const pb2_encoder_layer* L, const Lin& w, const void* act, int T, void* out, const float* bias, int relu,
+           float drop_p, unsigned long long rng_stream, const void* mask_src, float mask_scale, const void* addend,
+           cudaStream_t stream) {
+    const pb2_gemm_desc d = linear_desc(L, w, act, T, out, bias, relu, drop_p, rng_stream, mask_src, mask_scale, addend);
     return pb2_gemm_bf16(&d, L->workspace, L->workspace_bytes, stream);
+}
+
+int attention_fwd(const pb2_encoder_layer* L, cudaStream_t stream) {
+    const int E = L->E;
+    const float p = L->drop_p;
+    if (pb2_attention_uses_flash(L->S, E / L->heads)) {
+        if (!L->attn_lse) { pb2::set_error("pb2_encoder_layer_fwd: this shape uses flash attention: attn_lse is required"); return -1; }
+        return pb2_flash_attention_fwd(L->qkv, L->a, L->attn_lse, L->NB, L->S, L->heads, E / L->heads, L->causal, p, L->seed, 0, stream);
+    }
+    return pb2_attention_fwd(L->qkv, L->a, L->NB, L->S, L->heads, E / L->heads, L->causal, p, L->seed, 0, stream);
+}
+
+pb2_chain_op gemm_op(const pb2_gemm_desc& d) {
+    pb2_chain_op op;
+    memset(&op, 0, sizeof(op));
+    op.kind = 0;
+    op.gemm = d;
+    return op;
+}
+pb2_chain_op ln_op(const void* x, const void* h, const float* gamma, const float* beta, void* y, float* mean, float* rstd,
+                   int rows, int E, float eps) {
+    pb2_chain_op op;
+    memset(&op, 0, sizeof(op));
+    op.kind = 1;
+    op.ln.x = x; op.ln.h = h; op.ln.gamma = gamma; op.ln.beta = beta; op.ln.y = y; op.ln.mean = mean; op.ln.rstd = rstd;
+    op.ln.rows = rows; op.ln.E = E; op.ln.eps = eps;
+    return op;
+}
+
+// Everything of a layer's forward after the attention core — out-projection, add + LayerNorm, the two feed-forward GEMMs,
+// add + LayerNorm — and, when `next` is given, the QKV projection of the following layer, as one persistent kernel.
+// Returns the number of ops, 0 if these shapes cannot run as a chain.
+int post_attention_chain(const pb2_encoder_layer* L, const pb2_encoder_layer* next, pb2_chain_op* ops) {
+    const int T = L->T, E = L->E, FF = L->FF;
+    const float p = L->drop_p;
+    int n = 0;
+    ops[n++] = gemm_op(linear_desc(L, Lin{L->w_o, E, E, E}, L->a, T, L->o, L->b_o, 0, p, 1, nullptr, 0.f, nullptr));
+    ops[n++] = ln_op(L->x, L->o, L->g1, L->be1, L->x1, L->mean1, L->rstd1, T, E, L->eps);
+    ops[n++] = gemm_op(linear_desc(L, Lin{L->w_1, E, FF, E}, L->x1, T, L->hmid, L->b_1, 1, p, 2, nullptr, 0.f, nullptr));
+    ops[n++] = gemm_op(linear_desc(L, Lin{L->w_2, FF, E, FF}, L->hmid, T, L->f, L->b_2, 0, p, 3, nullptr, 0.f, nullptr));
+    ops[n++] = ln_op(L->x1, L->f, L->g2, L->be2, L->y, L->mean2, L->rstd2, T, E, L->eps);
+    if (next)
+        ops[n++] = gemm_op(linear_desc(next, Lin{next->w_qkv, next->E, 3 * next->E, next->E}, next->x, T, next->qkv, next->b_qkv, 0,
+                                       0.f, 0, nullptr, 0.f, nullptr));
+    return pb2_chain_supported(ops, n) ? n : 0;
+}
+
+// PB2_CHAIN=1 runs everything after the attention core (and the next layer's QKV projection) as one persistent op-chain
+// kernel.  Off by default: measured on config 3 (75 tokens, E = 4096) the chain takes 71 us where the same six ops as separate
+// programmatically-launched kernels take about as long, and a stack forward came out at 95 us per layer against 86 us
+// (profiles/chain_kernel_r2.txt) — each op is bound by the same serial phases either way (operand load after the producer is
+// complete, a DRAM-bound main loop, split-K exchange, epilogue) and a grid barrier costs what a dependent launch costs.
+// Read on every call: tests compare the two paths in one process.
+bool chain_enabled() {
+    const char* e = getenv("PB2_CHAIN");
+    return e && e[0] == '1';
 }
 
 }  // namespace
@@ -60,12 +124,7 @@ extern "C" int pb2_encoder_layer_fwd(const pb2_encoder_layer* L, cudaStream_t st
     if (pf && pb2_l2_prefetch(L->w_o, w_ee, stream)) return -1;
     if (linear(L, Lin{L->w_qkv, E, 3 * E, E}, L->x, T, L->qkv, L->b_qkv, 0, 0.f, 0, nullptr, 0.f, nullptr, stream)) return -1;
     if (pf && pb2_l2_prefetch(L->w_1, w_ef, stream)) return -1;
-    if (pb2_attention_uses_flash(L->S, E / L->heads)) {
-        if (!L->attn_lse) { pb2::set_error("pb2_encoder_layer_fwd: this shape uses flash attention: attn_lse is required"); return -1; }
-        if (pb2_flash_attention_fwd(L->qkv, L->a, L->attn_lse, L->NB, L->S, L->heads, E / L->heads, L->causal, p, L->seed, 0, stream)) return -1;
-    } else if (pb2_attention_fwd(L->qkv, L->a, L->NB, L->S, L->heads, E / L->heads, L->causal, p, L->seed, 0, stream)) {
-        return -1;
-    }
+    if (attention_fwd(L, stream)) return -1;
     if (linear(L, Lin{L->w_o, E, E, E}, L->a, T, L->o, L->b_o, 0, p, 1, nullptr, 0.f, nullptr, stream)) return -1;
     if (pb2_add_layernorm_fwd(L->x, L->o, L->g1, L->be1, L->x1, L->mean1, L->rstd1, T, E, L->eps, stream)) return -1;
     if (pf && pb2_l2_prefetch(L->w_2, w_ef, stream)) return -1;
@@ -196,25 +255,45 @@ extern "C" size_t pb2_encoder_stack_tmp_elems(const pb2_encoder_layer* layers, i
 
 extern "C" int pb2_encoder_stack_fwd(const pb2_encoder_stack* s, cudaStream_t stream) {
     if (check_stack(s, "pb2_encoder_stack_fwd")) return -1;
-    const int T = s->T;
+    const int T = s->T, n = s->n_layers;
     const size_t E = s->layers[0].E;
+    if (n > PB2_MAX_STACK_LAYERS) { pb2::set_error("pb2_encoder_stack_fwd: more than %d layers", PB2_MAX_STACK_LAYERS); return -1; }
     char* act = static_cast<char*>(s->act);
     char* y = static_cast<char*>(s->y);
-    for (int l = 0; l < s->n_layers; ++l) {
-        pb2_encoder_layer d = s->layers[l];
-        d.T = T; d.NB = s->NB; d.S = s->S;
-        d.drop_p = s->drop_p;
-        d.seed = s->seeds ? s->seeds[l] : 0ull;
-        d.x = l == 0 ? s->x : y + static_cast<size_t>(l - 1) * T * E * 2;
-        d.y = y + static_cast<size_t>(l) * T * E * 2;
-        carve_act(d, act, T);
-        act += act_elems(d, T) * 2;
+    // every layer's descriptor first: a chain reaches into the next layer (its QKV projection)
+    static thread_local pb2_encoder_layer d[PB2_MAX_STACK_LAYERS];
+    for (int l = 0; l < n; ++l) {
+        d[l] = s->layers[l];
+        d[l].T = T; d[l].NB = s->NB; d[l].S = s->S;
+        d[l].drop_p = s->drop_p;
+        d[l].seed = s->seeds ? s->seeds[l] : 0ull;
+        d[l].x = l == 0 ? s->x : y + static_cast<size_t>(l - 1) * T * E * 2;
+        d[l].y = y + static_cast<size_t>(l) * T * E * 2;
+        carve_act(d[l], act, T);
+        act += act_elems(d[l], T) * 2;
         float* st = s->stats + static_cast<size_t>(l) * stats_stride(s->layers[0], s->S, T);
-        d.mean1 = st; d.rstd1 = st + T; d.mean2 = st + 2 * T; d.rstd2 = st + 3 * T;
-        d.attn_lse = st + 4 * T;
-        d.workspace = s->workspace; d.workspace_bytes = s->workspace_bytes;
-        d.prefetch = 0; d.next_weight = nullptr; d.next_weight_bytes = 0;
-        if (pb2_encoder_layer_fwd(&d, stream)) return -1;
+        d[l].mean1 = st; d[l].rstd1 = st + T; d[l].mean2 = st + 2 * T; d[l].rstd2 = st + 3 * T;
+        d[l].attn_lse = st + 4 * T;
+        d[l].workspace = s->workspace; d[l].workspace_bytes = s->workspace_bytes;
+        d[l].prefetch = 0; d[l].next_weight = nullptr; d[l].next_weight_bytes = 0;
+    }
+    pb2_chain_op ops[PB2_CHAIN_MAX_OPS];
+    bool have_qkv = false;          // layer l's QKV projection was part of layer l - 1's chain
+    for (int l = 0; l < n; ++l) {
+        const pb2_encoder_layer* L = &d[l];
+        const int n_ops = chain_enabled() ? post_attention_chain(L, l + 1 < n ? &d[l + 1] : nullptr, ops) : 0;
+        if (n_ops == 0) {
+            if (have_qkv) { pb2::set_error("pb2_encoder_stack_fwd: chain support changed inside a stack"); return -1; }
+            if (pb2_encoder_layer_fwd(L, stream)) return -1;
+            continue;
+        }
+        if (!have_qkv &&
+            linear(L, Lin{L->w_qkv, static_cast<long long>(E), 3 * L->E, L->E}, L->x, T, L->qkv, L->b_qkv, 0, 0.f, 0, nullptr, 0.f,
+                   nullptr, stream))
+            return -1;
+        if (attention_fwd(L, stream)) return -1;
+        if (pb2_chain_run(ops, n_ops, s->workspace, s->workspace_bytes, stream)) return -1;
+        have_qkv = l + 1 < n;
     }
     return 0;
 }

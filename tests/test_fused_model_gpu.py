@@ -182,11 +182,14 @@ def test_skip_connection_across_fused_stages_and_inline_toggle():
 
 
 @pytest.mark.parametrize("dropout", [0.0, 0.2])
-def test_layer_stack_is_bit_identical_to_per_layer_calls(dropout):
+def test_layer_stack_is_bit_identical_to_per_layer_calls(dropout, monkeypatch):
     """A run of layers through ``pb2_encoder_stack_*`` (one native call per pass) launches the same
     kernels in the same order as per-layer calls: outputs, input gradient and every parameter
     gradient must be bit-identical, over two steps (the second reuses cached descriptors and the
-    grown wgrad stashes), also with the extra pass-through input used for fused-loss targets."""
+    grown wgrad stashes), also with the extra pass-through input used for fused-loss targets.
+    (With the opt-in op-chain kernel off: it splits every reduction four ways, the one-GEMM kernel picks per shape —
+    ``tests/test_chain_gpu.py`` compares the two.)"""
+    monkeypatch.setenv("PB2_CHAIN", "0")
     from pipe_b200.models.fused import EncoderStack, FusedEncoderLayer
     from pipe_b200.ops import wgrad
     from pipe_b200.partition import PipeSequential
