@@ -212,11 +212,6 @@ int pb2_mailbox_send(const void* src, size_t bytes, void* remote_slot, unsigned 
 int pb2_mailbox_recv(void* dst, size_t bytes, const void* local_slot, const unsigned int* local_flags,
                      unsigned int* remote_acks, unsigned int seq, int slot, int ctas, cudaStream_t stream);
 
-/* ---- asynchronous L2 prefetch of [ptr, ptr + bytes) (16-byte aligned) -----------------------
- * Returns at once; the lines arrive in L2 in the background.  Used to pull the next GEMM's weights
- * while kernels that do not touch HBM are running. */
-int pb2_l2_prefetch(const void* ptr, size_t bytes, cudaStream_t stream);
-
 /* ---- *out += sum(x^2)  (gradient-norm partial; x fp32, 16-byte aligned) ---------------------- */
 int pb2_sumsq(const float* x, size_t n, float* out, cudaStream_t stream);
 
@@ -343,11 +338,10 @@ typedef struct pb2_encoder_layer {
     /* split-K workspace of pb2_gemm_workspace_bytes() bytes (see pb2_gemm_bf16) */
     void* workspace;
     size_t workspace_bytes;
-    /* optional: the first weight the NEXT layer call on this stream will stream (forward: the next
-     * layer's w_qkv, backward: the previous layer's wt_2); prefetched into L2 during this call's tail */
+    /* unused (kept for layout compatibility; a measured-slower L2 prefetch experiment lived here) */
     const void* next_weight;
     size_t next_weight_bytes;
-    int prefetch;                    /* 1: prefetch each GEMM's weights one GEMM ahead */
+    int prefetch;
     /* optional (backward): a second stream for the launch that stacks x^T / dy^T for the deferred weight
      * gradients.  Nothing in backward reads those stacks, so the launch leaves the critical path: it waits
      * (event) for this call's attention backward and then runs next to the remaining kernels.  The caller

@@ -116,20 +116,11 @@ extern "C" int pb2_encoder_layer_fwd(const pb2_encoder_layer* L, cudaStream_t st
     const float p = L->drop_p;
     if (T != L->S * L->NB || E % L->heads) { pb2::set_error("pb2_encoder_layer_fwd: inconsistent shape"); return -1; }
 
-    // Weight prefetch runs one GEMM ahead: while a GEMM (or the attention / LayerNorm kernel after it)
-    // executes, the next GEMM's weights are already on their way into L2, so DRAM does not idle during
-    // prologues, epilogues and the kernels that never touch HBM.
-    const bool pf = L->prefetch != 0;
-    const size_t w_ee = static_cast<size_t>(E) * E * 2, w_ef = static_cast<size_t>(E) * FF * 2;
-    if (pf && pb2_l2_prefetch(L->w_o, w_ee, stream)) return -1;
     if (linear(L, Lin{L->w_qkv, E, 3 * E, E}, L->x, T, L->qkv, L->b_qkv, 0, 0.f, 0, nullptr, 0.f, nullptr, stream)) return -1;
-    if (pf && pb2_l2_prefetch(L->w_1, w_ef, stream)) return -1;
     if (attention_fwd(L, stream)) return -1;
     if (linear(L, Lin{L->w_o, E, E, E}, L->a, T, L->o, L->b_o, 0, p, 1, nullptr, 0.f, nullptr, stream)) return -1;
     if (pb2_add_layernorm_fwd(L->x, L->o, L->g1, L->be1, L->x1, L->mean1, L->rstd1, T, E, L->eps, stream)) return -1;
-    if (pf && pb2_l2_prefetch(L->w_2, w_ef, stream)) return -1;
     if (linear(L, Lin{L->w_1, E, FF, E}, L->x1, T, L->hmid, L->b_1, 1, p, 2, nullptr, 0.f, nullptr, stream)) return -1;
-    if (pf && L->next_weight && pb2_l2_prefetch(L->next_weight, L->next_weight_bytes, stream)) return -1;
     if (linear(L, Lin{L->w_2, FF, E, FF}, L->hmid, T, L->f, L->b_2, 0, p, 3, nullptr, 0.f, nullptr, stream)) return -1;
     if (pb2_add_layernorm_fwd(L->x1, L->f, L->g2, L->be2, L->y, L->mean2, L->rstd2, T, E, L->eps, stream)) return -1;
     return 0;
@@ -141,22 +132,16 @@ extern "C" int pb2_encoder_layer_bwd(const pb2_encoder_layer* L, cudaStream_t st
     const float p = L->drop_p;
     const float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
 
-    const bool pf = L->prefetch != 0;
-    const size_t w_ee = static_cast<size_t>(E) * L->ldt_o * 2, w_1t = static_cast<size_t>(E) * L->ldt_1 * 2,
-                 w_qt = static_cast<size_t>(E) * L->ldt_qkv * 2;
-    if (pf && pb2_l2_prefetch(L->wt_1, w_1t, stream)) return -1;
     // y = LN2(x1 + drop(f))
     if (pb2_add_layernorm_bwd(L->dy, L->x1, L->f, L->g2, L->mean2, L->rstd2, L->dr2, L->df, L->dg2, L->dbe2, T, E, p,
                               L->seed, 3, stream)) return -1;
     // through linear2, then ReLU + dropout (mask recovered from the saved activation)
     if (linear(L, dgrad_weight(L->wt_2, L->ldt_2, L->w_2, FF, E), L->df, T, L->dz1, nullptr, 0, 0.f, 0, L->hmid, inv_keep, nullptr, stream)) return -1;
-    if (pf && pb2_l2_prefetch(L->wt_o, w_ee, stream)) return -1;
     // through linear1, plus the residual branch
     if (linear(L, dgrad_weight(L->wt_1, L->ldt_1, L->w_1, E, FF), L->dz1, T, L->dx1, nullptr, 0, 0.f, 0, nullptr, 0.f, L->dr2, stream)) return -1;
     // x1 = LN1(x + drop(o))
     if (pb2_add_layernorm_bwd(L->dx1, L->x, L->o, L->g1, L->mean1, L->rstd1, L->dr1, L->do_, L->dg1, L->dbe1, T, E, p,
                               L->seed, 1, stream)) return -1;
-    if (pf && pb2_l2_prefetch(L->wt_qkv, w_qt, stream)) return -1;
     if (linear(L, dgrad_weight(L->wt_o, L->ldt_o, L->w_o, E, E), L->do_, T, L->da, nullptr, 0, 0.f, 0, nullptr, 0.f, nullptr, stream)) return -1;
     if (pb2_attention_uses_flash(L->S, E / L->heads)) {
         if (!L->attn_lse || !L->attn_scratch) { pb2::set_error("pb2_encoder_layer_bwd: this shape uses flash attention: attn_lse / attn_scratch are required"); return -1; }
@@ -172,7 +157,6 @@ extern "C" int pb2_encoder_layer_bwd(const pb2_encoder_layer* L, cudaStream_t st
         tstream = static_cast<cudaStream_t>(L->side_stream);
         if (pb2::record_and_wait(stream, tstream)) return -1;
     }
-    if (pf && L->next_weight && pb2_l2_prefetch(L->next_weight, L->next_weight_bytes, stream)) return -1;
     if (linear(L, dgrad_weight(L->wt_qkv, L->ldt_qkv, L->w_qkv, E, 3 * E), L->dqkv, T, L->dx, nullptr, 0, 0.f, 0, nullptr, 0.f, L->dr1, stream)) return -1;
 
     // stack every wgrad operand (and column-sum the bias gradients) in one launch
@@ -275,7 +259,6 @@ extern "C" int pb2_encoder_stack_fwd(const pb2_encoder_stack* s, cudaStream_t st
         d[l].mean1 = st; d[l].rstd1 = st + T; d[l].mean2 = st + 2 * T; d[l].rstd2 = st + 3 * T;
         d[l].attn_lse = st + 4 * T;
         d[l].workspace = s->workspace; d[l].workspace_bytes = s->workspace_bytes;
-        d[l].prefetch = 0; d[l].next_weight = nullptr; d[l].next_weight_bytes = 0;
     }
     pb2_chain_op ops[PB2_CHAIN_MAX_OPS];
     bool have_qkv = false;          // layer l's QKV projection was part of layer l - 1's chain
@@ -346,7 +329,6 @@ extern "C" int pb2_encoder_stack_bwd(const pb2_encoder_stack* s, cudaStream_t st
         d.dx = dx_here;
         d.stash_off_qkv = d.stash_off_o = d.stash_off_1 = d.stash_off_2 = s->stash_off;
         d.workspace = s->workspace; d.workspace_bytes = s->workspace_bytes;
-        d.prefetch = 0; d.next_weight = nullptr; d.next_weight_bytes = 0;
         d.side_stream = s->side_stream;
         if (pb2_encoder_layer_bwd(&d, stream)) return -1;
     }

@@ -577,25 +577,6 @@ transpose_multi_kernel(const pb2_transpose_jobs jobs) {
     }
 }
 
-// Fire-and-forget L2 prefetch of a byte range: each thread asks the memory system for one 16 KB
-// piece with a bulk prefetch and exits.  Launched ahead of a kernel that does not use HBM (attention,
-// LayerNorm) or ahead of a GEMM for the *next* GEMM's weights, it keeps DRAM busy during the prologue /
-// epilogue / launch gaps of the kernels in between: weight-streaming GEMMs then find their operand in
-// the 126 MB L2.
-__global__ void __launch_bounds__(128)
-l2_prefetch_kernel(const char* __restrict__ base, size_t bytes) {
-    pdl_launch_dependents();
-    constexpr size_t kPiece = 16 * 1024;
-    const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-    const size_t off = i * kPiece;
-    if (off >= bytes) return;
-    size_t n = bytes - off;
-    if (n > kPiece) n = kPiece;
-    n &= ~static_cast<size_t>(15);
-    if (n == 0) return;
-    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(base + off), "r"(static_cast<uint32_t>(n)) : "memory");
-}
-
 __global__ void __launch_bounds__(256)
 sumsq_kernel(const float* __restrict__ x, size_t n, float* __restrict__ out) {
     pdl_wait();          // launched programmatically; it does not release its own dependents early (the optimizer follows)
@@ -734,16 +715,6 @@ extern "C" int pb2_transpose_multi(const pb2_transpose_jobs* jobs, cudaStream_t 
     dim3 grid((max_c + 31) / 32, jobs->count);
     PB2_CUDA(launch_pdl(transpose_multi_kernel, grid, dim3(256), 0, stream, *jobs));
     PB2_LAUNCHED("transpose_multi_kernel");
-    return 0;
-}
-
-extern "C" int pb2_l2_prefetch(const void* ptr, size_t bytes, cudaStream_t stream) {
-    if (!ptr || bytes < 16) return 0;
-    if (reinterpret_cast<uintptr_t>(ptr) & 15) { set_error("pb2_l2_prefetch: pointer must be 16-byte aligned"); return -1; }
-    const size_t pieces = (bytes + 16 * 1024 - 1) / (16 * 1024);
-    const unsigned blocks = static_cast<unsigned>((pieces + 127) / 128);
-    l2_prefetch_kernel<<<blocks, 128, 0, stream>>>(static_cast<const char*>(ptr), bytes);
-    PB2_LAUNCHED("l2_prefetch_kernel");
     return 0;
 }
 
