@@ -221,13 +221,13 @@ __device__ __forceinline__ void ln_row(const ChainLn& L, size_t row, float* red,
 __global__ void __launch_bounds__(kChainThreads, 1)
 chain_kernel(const __grid_constant__ ChainParams P) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
-    // carve: [stages][A 16 KB][B bn*128 B] | split-K staging (3 sources x local_chunks x 128 rows x 80 B) | control
+    // carve: [stages][A 16 KB][B bn*128 B] | split-K staging (3 sources x local_chunks x 128 rows x 64 B) | control
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     const uint32_t a_bytes = kBlockM * kBlockK * 2;
     const uint32_t b_bytes = P.bn * kBlockK * 2;
     const uint32_t stage_bytes = a_bytes + b_bytes;
     const uint32_t ring_bytes = P.stages * stage_bytes;
-    const uint32_t staging_bytes = (kChainCluster - 1) * P.local_chunks * kBlockM * kStagePitch * 4;
+    const uint32_t staging_bytes = (kChainCluster - 1) * P.local_chunks * kBlockM * 64;
     float* staging = reinterpret_cast<float*>(smem + ring_bytes);
     ChainCtl* ctl = reinterpret_cast<ChainCtl*>(smem + ring_bytes + staging_bytes);
 
@@ -456,14 +456,16 @@ chain_kernel(const __grid_constant__ ChainParams P) {
                         tmem_ld_32x16(t_lane + k * 16, r);
                         tmem_ld_wait();
                         const uint32_t si = rank < owner ? rank : rank - 1;           // my slot among the owner's sources
-                        const uint32_t local = staging_u32 +
-                            ((si * P.local_chunks + (k / kChainCluster)) * kBlockM + m_local) * (kStagePitch * 4u);
+                        // staging block of (source, chunk): [4 column quads][128 rows][16 B] — a warp's store instruction
+                        // covers 512 contiguous bytes (the row-major form with one 16-byte piece per row every 80 bytes
+                        // moved the same data as 32 separate remote writes per instruction)
+                        const uint32_t local = staging_u32 + (si * P.local_chunks + (k / kChainCluster)) * (kBlockM * 64u) + m_local * 16u;
                         const uint32_t remote = dsmem_addr(local, owner);
                         const uint32_t recv_remote = dsmem_addr(smem_u32(&ctl->recv), owner);
 #pragma unroll
                         for (int j = 0; j < 16; j += 4)
-                            dsmem_st_async_f32x4(remote + j * 4, recv_remote, __uint_as_float(r[j]), __uint_as_float(r[j + 1]),
-                                                 __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
+                            dsmem_st_async_f32x4(remote + (j / 4) * (kBlockM * 16u), recv_remote, __uint_as_float(r[j]),
+                                                 __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
                     }
                     if (ep_tid == 0 && t == cluster_id) chain_ts(P.ts, op, 4);
                     if (ep_tid == 0 && t == cluster_id) chain_ts(P.ts, op, 5);
@@ -481,11 +483,11 @@ chain_kernel(const __grid_constant__ ChainParams P) {
                         for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
 #pragma unroll
                         for (int si = 0; si < kChainCluster - 1; ++si) {
-                            const float4* p = reinterpret_cast<const float4*>(
-                                staging + ((static_cast<size_t>(si) * P.local_chunks + kl) * kBlockM + m_local) * kStagePitch);
+                            const float4* p = reinterpret_cast<const float4*>(staging) +
+                                              (static_cast<size_t>(si) * P.local_chunks + kl) * (kBlockM * 4) + m_local;
 #pragma unroll
                             for (int q = 0; q < 4; ++q) {
-                                const float4 x4 = p[q];
+                                const float4 x4 = p[q * kBlockM];
                                 v[4 * q] += x4.x; v[4 * q + 1] += x4.y; v[4 * q + 2] += x4.z; v[4 * q + 3] += x4.w;
                             }
                         }
@@ -632,7 +634,7 @@ extern "C" int pb2_chain_run(const pb2_chain_op* ops, int n_ops, void* workspace
         }
     }
     const size_t stage_bytes = static_cast<size_t>(kBlockM + bn) * kBlockK * 2;
-    const size_t staging = static_cast<size_t>(kChainCluster - 1) * P.local_chunks * kBlockM * kStagePitch * 4;
+    const size_t staging = static_cast<size_t>(kChainCluster - 1) * P.local_chunks * kBlockM * 64;
     const size_t fixed = staging + sizeof(ChainCtl) + 1024;
     int stages = static_cast<int>((227 * 1024 - fixed) / stage_bytes);
     if (stages > kMaxStages) stages = kMaxStages;

@@ -246,9 +246,9 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         // ---- split-K reduction inside the cluster, through distributed shared memory ----
         // Chunk k (16 accumulator columns) is owned by cluster rank k % splits.  Every CTA sends its
         // partial of each foreign chunk into the owner's staging area (the now idle TMA ring):
-        //   staging[src rank][owner-local chunk][row 0..127][16 columns, row pitch 20 floats]  fp32
-        // (a thread owns an accumulator row, so it ships 64 contiguous bytes as four 16-byte DSMEM
-        // stores; the 80-byte pitch keeps the owner's 16-byte reads free of bank conflicts)
+        //   staging[src rank][owner-local chunk][column quad 0..3][row 0..127][4 columns]  fp32
+        // (a thread owns an accumulator row and ships its 16 columns as four 16-byte DSMEM stores; rows are
+        // contiguous within a column quad, so each store instruction of a warp is one 512-byte run)
         // and each owner then finishes only its own chunks, so the fix-up and the epilogue are
         // spread over all CTAs of the tile and no partial tile ever goes to global memory.
         const uint32_t rank = cluster_ctarank();
@@ -261,12 +261,15 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                 uint32_t r[16];
                 tmem_ld_32x16(t_lane + k * 16, r);
                 tmem_ld_wait();
-                const uint32_t local = stage_base +
-                    ((rank * g.local_chunks + (k / g.splits)) * kBlockM + m_local) * (kStagePitch * 4u);
+                // block of (source rank, chunk): [4 column quads][128 rows][16 B], so one store instruction of a warp
+                // covers 512 contiguous bytes of the owner's shared memory.  (Row-major rows of 80 bytes made every
+                // instruction 32 separate 16-byte remote writes: 1.8 us to ship 30 KB instead of 0.6,
+                // profiles/chain_kernel_r2.txt.)
+                const uint32_t local = stage_base + (rank * g.local_chunks + (k / g.splits)) * (kBlockM * 64u) + m_local * 16u;
                 const uint32_t remote = dsmem_addr(local, owner);
 #pragma unroll
                 for (int j = 0; j < 16; j += 4)
-                    dsmem_st_f32x4(remote + j * 4, __uint_as_float(r[j]), __uint_as_float(r[j + 1]),
+                    dsmem_st_f32x4(remote + (j / 4) * (kBlockM * 16u), __uint_as_float(r[j]), __uint_as_float(r[j + 1]),
                                    __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
             }
         }
@@ -298,11 +301,11 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                 for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
                 for (int src = 0; src < g.splits; ++src) {
                     if (src == static_cast<int>(rank)) continue;
-                    const float4* p = reinterpret_cast<const float4*>(
-                        staging + ((static_cast<size_t>(src) * g.local_chunks + kl) * kBlockM + m_local) * kStagePitch);
+                    const float4* p = reinterpret_cast<const float4*>(staging) +
+                                      (static_cast<size_t>(src) * g.local_chunks + kl) * (kBlockM * 4) + m_local;
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
-                        const float4 t = p[q];
+                        const float4 t = p[q * kBlockM];
                         v[4 * q] += t.x; v[4 * q + 1] += t.y; v[4 * q + 2] += t.z; v[4 * q + 3] += t.w;
                     }
                 }
@@ -779,7 +782,7 @@ static int gemm_launch(const pb2_gemm_desc* d, float* partials, unsigned int* co
     // staging area fits the idle TMA ring; otherwise through the global scratch workspace
     const int n_chunks = bn / 16;
     g.local_chunks = (n_chunks + splits - 1) / splits;
-    const size_t staging = static_cast<size_t>(splits) * g.local_chunks * kStagePitch * kBlockM * sizeof(float);
+    const size_t staging = static_cast<size_t>(splits) * g.local_chunks * kBlockM * 64;
     const bool pow2 = (splits & (splits - 1)) == 0;
     g.cluster_reduce = (splits > 1 && splits <= 8 && pow2 && !force_scratch && d->reduce_mode != 1 &&
                         staging <= static_cast<size_t>(stages) * stage_bytes) ? 1 : 0;
