@@ -99,17 +99,6 @@ __device__ __forceinline__ void chain_ts(unsigned long long* ts, int op, int slo
     }
 }
 
-// Remote arrival without a fence: used for "I have read what you sent" (the loads it orders have returned their values by
-// program order), never to publish data.
-__device__ __forceinline__ void mbar_arrive_remote_relaxed(uint32_t cluster_addr) {
-    asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
-}
-// 16 bytes into a peer's shared memory, completing 16 bytes of a transaction on the peer's mbarrier: data and signal travel
-// together, so neither side needs a fence (a release at cluster scope costs a MEMBAR.GPU per arrival: 3.7 us per tile measured).
-__device__ __forceinline__ void dsmem_st_async_f32x4(uint32_t addr, uint32_t mbar, float a, float b, float c, float d) {
-    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.f32 [%0], {%2, %3, %4, %5}, [%1];"
-                 ::"r"(addr), "r"(mbar), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
-}
 __device__ __forceinline__ void tma_prefetch_l2_2d(const CUtensorMap* m, int32_t c0, int32_t c1) {
     asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];"
                  ::"l"(reinterpret_cast<uint64_t>(m)), "r"(c0), "r"(c1) : "memory");

@@ -56,6 +56,7 @@ struct __align__(8) SmemCtl {
     uint64_t full[kMaxStages];
     uint64_t empty[kMaxStages];
     uint64_t tmem_full;
+    uint64_t recv;          // cluster split-K: the peers' partials of this CTA's chunks have landed (transaction bytes)
     uint32_t tmem_base;
     uint32_t is_last;
 };
@@ -154,6 +155,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
             mbar_init(&ctl->empty[s], 1);
         }
         mbar_init(&ctl->tmem_full, 1);
+        mbar_init(&ctl->recv, 1);
         fence_mbar_init();
     }
     if (warp == 1) {
@@ -252,7 +254,13 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         // and each owner then finishes only its own chunks, so the fix-up and the epilogue are
         // spread over all CTAs of the tile and no partial tile ever goes to global memory.
         const uint32_t rank = cluster_ctarank();
-        cluster_sync_all();                                   // (1) every CTA's ring is idle
+        if (ep_tid == 0) {
+            // bytes about to arrive here: this CTA's chunks from every other rank
+            int own = 0;
+            for (int k = static_cast<int>(rank); k < n_chunks; k += g.splits) ++own;
+            mbar_expect_tx(&ctl->recv, static_cast<uint32_t>(own) * (g.splits - 1) * kBlockM * 64u);
+        }
+        cluster_sync_relaxed();                               // (1) every CTA's ring is idle (and its barrier armed)
         if (is_epi) {
             const uint32_t stage_base = smem_u32(smem);
             for (int k = half; k < n_chunks; k += 2) {
@@ -267,10 +275,13 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                 // profiles/chain_kernel_r2.txt.)
                 const uint32_t local = stage_base + (rank * g.local_chunks + (k / g.splits)) * (kBlockM * 64u) + m_local * 16u;
                 const uint32_t remote = dsmem_addr(local, owner);
+                const uint32_t recv_remote = dsmem_addr(smem_u32(&ctl->recv), owner);
+                // data and completion signal travel together (st.async): no release / acquire cluster barrier, which
+                // would put a MEMBAR.GPU and an L1 invalidation into every thread's path
 #pragma unroll
                 for (int j = 0; j < 16; j += 4)
-                    dsmem_st_f32x4(remote + (j / 4) * (kBlockM * 16u), __uint_as_float(r[j]), __uint_as_float(r[j + 1]),
-                                   __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
+                    dsmem_st_async_f32x4(remote + (j / 4) * (kBlockM * 16u), recv_remote, __uint_as_float(r[j]),
+                                         __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
             }
         }
         // While the partials are in flight: everything of this thread's first owned chunk that does not
@@ -286,8 +297,8 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                 (g.drop_p > 0.f || g.mask_src || g.addend))
                 epilogue_prefetch(g, e, m_glob, n0 + k_first * 16, pre);
         }
-        cluster_sync_all();                                   // (2) all partials delivered
         if (is_epi) {
+            mbar_wait(&ctl->recv, 0);                         // (2) all partials of my chunks delivered
             float ss = 0.f;
             const float* staging = reinterpret_cast<const float*>(smem);
             for (int kl = half; kl < g.local_chunks; kl += 2) {
