@@ -168,6 +168,21 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     const uint32_t tmem_base = ctl->tmem_base;
     if (threadIdx.x == 0) PB2_TS(1);
 
+    const bool is_epi = warp >= 2;
+    const int quarter = warp & 3;                 // TMEM lane quarter this warp may read
+    const int half = is_epi ? (warp - 2) >> 2 : 0;  // which of the two warps of that quarter
+    const int m_local = quarter * 32 + lane;
+    const int m_glob = m0 + m_local;
+    const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
+    const int ep_tid = threadIdx.x - 64;          // 0..255 for epilogue threads
+    const int tile = blockIdx.y * gridDim.x + blockIdx.x;
+    const size_t tile_elems = static_cast<size_t>(g.block_n) * kBlockM;
+    const int n_chunks = g.block_n >> 4;
+    EpiCtx e{CounterRng(g.seed), static_cast<uint32_t>(fminf(g.drop_p, 0.999999f) * 4294967296.0f),
+             g.drop_p > 0.f ? 1.f / (1.f - g.drop_p) : 1.f, 0.f, m_glob < g.M};
+    ChunkPre pre;
+    pre.have = false;
+
     if (warp == 0) {
         // ===================== TMA producer =====================
         if (elect_one()) {
@@ -227,22 +242,22 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
             __syncwarp();
         }
     } else {
-        // ===================== epilogue (warps 2..9): wait for the accumulator =====================
+        // ===================== epilogue (warps 2..9) =====================
+        // Cluster split-K: while the main loop runs, everything of this thread's first owned chunk that does not depend
+        // on the accumulator — dropout bits, mask / residual operands (the predecessor's output: wait for it first), bias.
+        if (g.cluster_reduce) {
+            pdl_wait();
+            const uint32_t rank_e = cluster_ctarank();
+            if (g.bias && g.bias_along_m && e.row_ok) e.bias_m = g.bias[m_glob];
+            const int k_first = half * g.splits + static_cast<int>(rank_e);
+            if (half < g.local_chunks && k_first < n_chunks && n0 + k_first * 16 < g.N &&
+                (g.drop_p > 0.f || g.mask_src || g.addend))
+                epilogue_prefetch(g, e, m_glob, n0 + k_first * 16, pre);
+        }
         mbar_wait(&ctl->tmem_full, 0);
         tc_fence_after();
         if (threadIdx.x == 64) PB2_TS(4);
     }
-
-    const bool is_epi = warp >= 2;
-    const int quarter = warp & 3;                 // TMEM lane quarter this warp may read
-    const int half = is_epi ? (warp - 2) >> 2 : 0;  // which of the two warps of that quarter
-    const int m_local = quarter * 32 + lane;
-    const int m_glob = m0 + m_local;
-    const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
-    const int ep_tid = threadIdx.x - 64;          // 0..255 for epilogue threads
-    const int tile = blockIdx.y * gridDim.x + blockIdx.x;
-    const size_t tile_elems = static_cast<size_t>(g.block_n) * kBlockM;
-    const int n_chunks = g.block_n >> 4;
 
     if (g.cluster_reduce) {
         // ---- split-K reduction inside the cluster, through distributed shared memory ----
@@ -261,6 +276,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
             mbar_expect_tx(&ctl->recv, static_cast<uint32_t>(own) * (g.splits - 1) * kBlockM * 64u);
         }
         cluster_sync_relaxed();                               // (1) every CTA's ring is idle (and its barrier armed)
+        if (ep_tid == 0) PB2_TS(7);
         if (is_epi) {
             const uint32_t stage_base = smem_u32(smem);
             for (int k = half; k < n_chunks; k += 2) {
@@ -284,21 +300,11 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                                          __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
             }
         }
-        // While the partials are in flight: everything of this thread's first owned chunk that does not
-        // depend on them (dropout bits, mask / residual operands, bias).
-        EpiCtx e{CounterRng(g.seed), static_cast<uint32_t>(fminf(g.drop_p, 0.999999f) * 4294967296.0f),
-                 g.drop_p > 0.f ? 1.f / (1.f - g.drop_p) : 1.f, 0.f, m_glob < g.M};
-        ChunkPre pre;
-        pre.have = false;
-        if (is_epi) {
-            if (g.bias && g.bias_along_m && e.row_ok) e.bias_m = g.bias[m_glob];
-            const int k_first = half * g.splits + static_cast<int>(rank);
-            if (half < g.local_chunks && k_first < n_chunks && n0 + k_first * 16 < g.N &&
-                (g.drop_p > 0.f || g.mask_src || g.addend))
-                epilogue_prefetch(g, e, m_glob, n0 + k_first * 16, pre);
-        }
+        if (ep_tid == 0) PB2_TS(8);
+        if (ep_tid == 0) PB2_TS(9);
         if (is_epi) {
             mbar_wait(&ctl->recv, 0);                         // (2) all partials of my chunks delivered
+            if (ep_tid == 0) PB2_TS(10);
             float ss = 0.f;
             const float* staging = reinterpret_cast<const float*>(smem);
             for (int kl = half; kl < g.local_chunks; kl += 2) {
