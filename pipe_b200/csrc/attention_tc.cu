@@ -144,15 +144,21 @@ __device__ __forceinline__ void tc_abt(const __nv_bfloat16* A0, const __nv_bfloa
 }
 
 // Push `count` floats (a multiple of 4, 16-byte aligned) of this CTA's shared memory to the same
-// location in every other CTA of the cluster.
-__device__ __forceinline__ void tc_push(const float* local, int count, int cs, uint32_t rank) {
-    const uint32_t base = smem_u32(local);
+// location in every other CTA of the cluster.  Each 16-byte store completes 16 bytes of the transaction the
+// receiver armed on its `recv` barrier (st.async): the receiver waits for its bytes, nobody executes a
+// release / acquire cluster barrier (a MEMBAR.GPU per thread with the remote stores outstanding).
+__device__ __forceinline__ void tc_push(const float* local, int count, int cs, uint32_t rank, uint64_t* recv) {
+    const uint32_t base = smem_u32(local), bar = smem_u32(recv);
     for (int v = threadIdx.x * 4; v < count; v += kTcThreads * 4) {
         const float4 x = *reinterpret_cast<const float4*>(local + v);
 #pragma unroll 4
         for (int peer = 0; peer < cs; ++peer)
-            if (peer != static_cast<int>(rank)) dsmem_st_f32x4(dsmem_addr(base + v * 4u, peer), x.x, x.y, x.z, x.w);
+            if (peer != static_cast<int>(rank))
+                dsmem_st_async_f32x4(dsmem_addr(base + v * 4u, peer), dsmem_addr(bar, peer), x.x, x.y, x.z, x.w);
     }
+}
+__device__ __forceinline__ void cluster_arrive_relaxed() {
+    asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
 }
 
 // Softmax over the first S columns of the first S rows of the scores (scaled by `scale`).  The scores
@@ -288,7 +294,6 @@ attn_tc_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restr
     attn_ts(0);
     constexpr int cs = CS;
     const uint32_t rank = cs > 1 ? cluster_ctarank() : 0u;
-    if (cs > 1) cluster_arrive();            // waited for right before the first DSMEM store: every peer is running by then
     extern __shared__ __align__(128) uint8_t smem[];
     // Query rows are processed in blocks of RB <= 64: the score block [RB x SP] is the only S^2-sized
     // buffer, so S = 128 needs ~100 KB instead of ~170 KB and two CTAs share an SM (256 CTAs = one wave).
@@ -300,6 +305,16 @@ attn_tc_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restr
     float* sc = reinterpret_cast<float*>(v + SP * dpad);                     // cs partial score blocks
     const __nv_bfloat16* pb = reinterpret_cast<const __nv_bfloat16*>(sc);    // probabilities, written over slot 0
     float* stage = sc + cs * slot + (threadIdx.x >> 5) * (16 * 24);
+    // peers' partial scores of the current row block have landed (transaction bytes); lives behind the staging tiles
+    uint64_t& recv = *reinterpret_cast<uint64_t*>(sc + cs * slot + kTcWarps * (16 * 24));
+    if (cs > 1) {
+        if (threadIdx.x == 0) {
+            mbar_init(&recv, 1);
+            fence_mbar_init();
+            mbar_expect_tx(&recv, static_cast<uint32_t>(cs - 1) * slot * 4u);
+        }
+        cluster_arrive_relaxed();            // waited for right before the first DSMEM store: every peer is running (and armed) by then
+    }
     const int pair = blockIdx.x / cs;
     const int n = pair / a.H, h = pair - n * a.H;
     const long long ld = 3LL * a.E;
@@ -316,8 +331,9 @@ attn_tc_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restr
         __syncthreads();
         if (cs > 1) {
             if (rb0 == 0) cluster_wait();
-            tc_push(sc + rank * slot, slot, cs, rank);
-            cluster_sync_all();
+            tc_push(sc + rank * slot, slot, cs, rank, &recv);
+            mbar_wait(&recv, (rb0 / RB) & 1);
+            __syncthreads();                 // slower threads are still reading this CTA's own partial (it is overwritten next)
         }
         attn_ts(2);
         tc_softmax_drop<CS>(sc, slot, rb0, rows, a, n, h);
@@ -360,8 +376,15 @@ attn_tc_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restr
             }
         }
         if (rb0 + RB < SP) {
-            if (cs > 1) cluster_sync_all();      // peers may still be reading nothing of ours, but they push into sc next
-            else __syncthreads();                // the next block's scores overwrite the probabilities
+            if (cs > 1) {
+                // the peers push the next block's scores into sc: everybody is done with this block first, and the
+                // barrier is armed again before that (execution barrier only: the data is published by the transaction)
+                if (threadIdx.x == 0) mbar_expect_tx(&recv, static_cast<uint32_t>(cs - 1) * slot * 4u);
+                cluster_arrive_relaxed();
+                cluster_wait();
+            } else {
+                __syncthreads();                 // the next block's scores overwrite the probabilities
+            }
         }
     }
     attn_ts(5);
@@ -376,7 +399,6 @@ attn_tc_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* _
     attn_ts(8);
     constexpr int cs = CS;
     const uint32_t rank = cs > 1 ? cluster_ctarank() : 0u;
-    if (cs > 1) cluster_arrive();
     extern __shared__ __align__(128) uint8_t smem[];
     const int S = a.S, SP = a.SP, Dc = a.Dc, dpad = Dc + 8, cpad = SP + 8, slot = SP * cpad;
     __nv_bfloat16* q = reinterpret_cast<__nv_bfloat16*>(smem);
@@ -392,6 +414,16 @@ attn_tc_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* _
     __nv_bfloat16* dS = reinterpret_cast<__nv_bfloat16*>(dP);                 // score gradients
     const int bpad = 2 * cpad;
     float* stage = dP + cs * slot + (threadIdx.x >> 5) * (16 * 24);
+    // peers' partial P and dP have landed (transaction bytes); lives behind the staging tiles
+    uint64_t& recv = *reinterpret_cast<uint64_t*>(dP + cs * slot + kTcWarps * (16 * 24));
+    if (cs > 1) {
+        if (threadIdx.x == 0) {
+            mbar_init(&recv, 1);
+            fence_mbar_init();
+            mbar_expect_tx(&recv, 2u * static_cast<uint32_t>(cs - 1) * slot * 4u);
+        }
+        cluster_arrive_relaxed();
+    }
     const int pair = blockIdx.x / cs;
     const int n = pair / a.H, h = pair - n * a.H;
     const long long ld = 3LL * a.E;
@@ -405,9 +437,10 @@ attn_tc_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* _
     __syncthreads();
     if (cs > 1) {
         cluster_wait();
-        tc_push(P + rank * slot, slot, cs, rank);
-        tc_push(dP + rank * slot, slot, cs, rank);
-        cluster_sync_all();
+        tc_push(P + rank * slot, slot, cs, rank, &recv);
+        tc_push(dP + rank * slot, slot, cs, rank, &recv);
+        mbar_wait(&recv, 0);
+        __syncthreads();                     // slower threads are still reading this CTA's own partials (overwritten next)
     }
     attn_ts(10);
     tc_softmax<CS>(P, slot, S, SP, a.scale, a.causal);
@@ -513,6 +546,7 @@ size_t attn_tc_smem(int SP, int Dc, int cs, bool bwd) {
     b += (bwd ? 2 : 1) * cs * rows * cpad * 4;             // fp32 partial score matrices, one per cluster rank
                                                            // (the bf16 copies alias the first)
     b += kTcWarps * 16 * 24 * 4;                           // per-warp output staging
+    b += 16;                                               // the exchange's mbarrier
     return b + 128;
 }
 
