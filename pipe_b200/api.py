@@ -15,7 +15,7 @@ Parity: reference ``pipe.py:224-494``; SURVEY.md C1, C5 and Appendix B.
 """
 from __future__ import annotations
 
-from typing import Any, Iterable, Iterator, List, Optional, Sequence, Union
+from typing import Any, Iterable, Iterator, List, Optional, Union
 
 import torch
 from torch import Tensor, nn

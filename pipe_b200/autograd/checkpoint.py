@@ -35,7 +35,7 @@ from __future__ import annotations
 import threading
 from collections import deque
 from contextlib import contextmanager
-from typing import Any, Deque, Generator, List, Optional, Sequence, Tuple, Union
+from typing import Any, Deque, Generator, List, Optional, Sequence, Tuple
 
 import torch
 from torch import Tensor

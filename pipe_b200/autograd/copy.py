@@ -17,7 +17,7 @@ Parity: reference ``pipeline.py:51-60`` (call sites), ``README.md:185-237``
 from __future__ import annotations
 
 from collections import deque
-from typing import Any, Deque, List, Optional, Sequence, Tuple
+from typing import Any, Deque, List, Optional, Tuple
 
 import torch
 from torch import Tensor

@@ -12,10 +12,10 @@ from __future__ import annotations
 
 import copy
 import time
-from typing import Any, Generator, List, Sequence, Tuple, Union
+from typing import Any, Generator, List, Union
 
 import torch
-from torch import Tensor, nn
+from torch import nn
 
 from ..microbatch import Batch
 

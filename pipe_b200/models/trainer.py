@@ -13,8 +13,7 @@ sm_100a kernels, bf16 compute with fp32 master weights.
 """
 from __future__ import annotations
 
-import math
-from typing import Any, Dict, Iterable, List, Optional, Sequence, Tuple
+from typing import Dict, Iterable, List, Optional
 
 import torch
 import torch.distributed as dist

@@ -5,7 +5,7 @@ SURVEY.md §2.5 K1-K11): each wrapper here is the sm_100a replacement of one of 
 from __future__ import annotations
 
 import ctypes
-from typing import List, Optional, Sequence, Tuple
+from typing import Optional, Sequence, Tuple
 
 import torch
 from torch import Tensor

@@ -18,7 +18,7 @@ device that is cleared with one memset.
 from __future__ import annotations
 
 import ctypes
-from typing import Dict, Iterable, List, Optional
+from typing import Dict, List, Optional
 
 import numpy as np
 import torch

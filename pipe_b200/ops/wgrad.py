@@ -22,7 +22,7 @@ from __future__ import annotations
 import ctypes
 import threading
 from contextlib import contextmanager
-from typing import Dict, Iterator, List, Optional, Set, Tuple
+from typing import Iterator, List, Optional, Tuple
 
 import torch
 from torch import Tensor, nn

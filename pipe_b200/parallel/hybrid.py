@@ -21,7 +21,7 @@ first, so their reduction overlaps the backward of the earlier stages.
 """
 from __future__ import annotations
 
-from typing import List, Optional
+from typing import Optional
 
 import torch
 import torch.distributed as dist

@@ -19,7 +19,7 @@ Reference counterpart: ``Copy`` / ``Wait`` on copy streams inside one process (R
 from __future__ import annotations
 
 import ctypes
-from typing import Dict, List, Optional, Sequence, Tuple
+from typing import Dict, List, Sequence, Tuple
 
 import torch
 import torch.distributed as dist

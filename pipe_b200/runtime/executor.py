@@ -28,9 +28,8 @@ Parity: reference ``pipeline.py:43-60`` (helpers), ``82-117`` (``run``),
 from __future__ import annotations
 
 import sys
-from contextlib import nullcontext
 from queue import Queue
-from typing import TYPE_CHECKING, Callable, List, Optional, Sequence, Tuple
+from typing import Callable, List, Optional, Sequence, Tuple
 
 import torch
 from torch import nn

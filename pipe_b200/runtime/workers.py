@@ -20,7 +20,7 @@ import threading
 import weakref
 from queue import Queue
 from types import TracebackType
-from typing import Callable, Dict, List, Optional, Tuple, Type, Union
+from typing import Callable, Dict, List, Optional, Tuple, Type
 
 import torch
 

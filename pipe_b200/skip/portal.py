@@ -24,12 +24,11 @@ SURVEY.md §3.4, A8.
 """
 from __future__ import annotations
 
-from typing import List, Optional
+from typing import Optional
 
 import torch
 from torch import Tensor
 
-from ..autograd.copy import Context as CopyContext
 from ..autograd.copy import Copy
 from ..autograd.phony import get_phony
 from ..autograd.stream import AbstractStream, get_device

@@ -29,7 +29,6 @@ import inspect
 from typing import (Any, Callable, ClassVar, Dict, FrozenSet, Generator, Iterable, List,
                     Optional, Set, Tuple, Type, TypeVar, Union)
 
-import torch
 from torch import Tensor, nn
 
 from ..microbatch import Batch

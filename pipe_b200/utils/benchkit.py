@@ -11,7 +11,7 @@ import statistics
 import subprocess
 import tempfile
 import time
-from typing import Any, Callable, Dict, List, Optional, Tuple
+from typing import Any, Callable, Dict, List, Optional
 
 import torch
 import torch.distributed as dist
