@@ -33,10 +33,11 @@ def test_ctypes_struct_layouts_match_the_header():
         #include <stddef.h>
         #include "pipe_b200.h"
         int main(void) {
-            printf("%zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(pb2_gemm_desc), offsetof(pb2_gemm_desc, persistent),
+            printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(pb2_gemm_desc), offsetof(pb2_gemm_desc, persistent),
                    sizeof(pb2_encoder_layer), offsetof(pb2_encoder_layer, side_stream),
                    offsetof(pb2_encoder_layer, peer_delta), sizeof(pb2_encoder_stack),
-                   offsetof(pb2_encoder_stack, attn_scratch_bytes), sizeof(pb2_transpose_jobs));
+                   offsetof(pb2_encoder_stack, attn_scratch_bytes), sizeof(pb2_transpose_jobs),
+                   sizeof(pb2_chain_op), offsetof(pb2_chain_op, gemm), offsetof(pb2_chain_op, ln), offsetof(pb2_chain_ln, eps));
             return 0;
         }
     """)
@@ -48,7 +49,12 @@ def test_ctypes_struct_layouts_match_the_header():
                              capture_output=True, text=True)
         assert res.returncode == 0, res.stderr
         out = subprocess.run([exe], capture_output=True, text=True).stdout.split()
-    gemm_size, gemm_off, layer_size, layer_off, peer_off, stack_size, stack_off, jobs_size = map(int, out)
+    (gemm_size, gemm_off, layer_size, layer_off, peer_off, stack_size, stack_off, jobs_size,
+     chain_size, chain_gemm_off, chain_ln_off, ln_eps_off) = map(int, out)
+    from pipe_b200.ops import chain
+    assert ctypes.sizeof(chain.ChainOp) == chain_size
+    assert chain.ChainOp.gemm.offset == chain_gemm_off and chain.ChainOp.ln.offset == chain_ln_off
+    assert chain.ChainLn.eps.offset == ln_eps_off
     from pipe_b200.ops import functional as F2
     assert _lib.EncoderLayerDesc.peer_delta.offset == peer_off
     assert ctypes.sizeof(_lib.EncoderStackDesc) == stack_size
