@@ -1,5 +1,7 @@
 // Pieces of the tcgen05 GEMM shared by the one-GEMM kernels (gemm_sm100.cu) and the persistent op-chain kernel
 // (chain_sm100.cu): tile constants, the kernel argument block, operand-stage helpers and the fused epilogue.
+// Reference counterpart: none — bias, ReLU, dropout, residual add are separate ATen kernels behind nn.Linear /
+// nn.TransformerEncoderLayer there (main.py:45,148).  SURVEY.md K2/K4/K6.
 #pragma once
 
 #include "common.cuh"
